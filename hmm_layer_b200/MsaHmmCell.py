@@ -1,0 +1,128 @@
+"""HmmCell / MsaHmmCell with the reference's interface (reference: hmm_layer/MsaHmmCell.py).
+
+The cell owns an emitter (or list) and a transitioner plugin, exactly like the reference.  What differs:
+  * `make_reverse_direction_offspring` gives the reverse cell its own reversed *view* of the transitioner, so
+    building the pair no longer flips the forward cell to A^T (defect D1);
+  * the chunked initial state never multiplies the identity in place (defect D2);
+  * constants are created on the parameters' device (the reference is CPU-only)."""
+import torch
+import torch.nn as nn
+
+
+class HmmCell(nn.Module):
+    def __init__(self, num_states, dim, emitter, transitioner, use_step_counter=False, use_fake_step_counter=False, **kwargs):
+        super().__init__(**kwargs)
+        self.num_states = num_states
+        self.num_models = len(num_states)
+        self.max_num_states = max(num_states)
+        self.dim = dim
+        self.emitter = nn.ModuleList(emitter if isinstance(emitter, (list, tuple)) else [emitter])
+        self.transitioner = transitioner
+        self.epsilon = 1e-16
+        self.reverse = False
+        self.use_step_counter = use_step_counter
+        self.use_fake_step_counter = use_fake_step_counter
+        self.recurrent_init()
+
+    # ---- parameter -> matrices, once per call (reference :41-59) ----
+    def recurrent_init(self):
+        self.transitioner.recurrent_init()
+        for em in self.emitter:
+            em.recurrent_init()
+        self.log_A_dense = self.transitioner.make_log_A()
+        self.log_A_dense_t = self.log_A_dense.transpose(1, 2)
+        self.init_dist = self.make_initial_distribution()
+        if not self.reverse and self.use_step_counter:
+            self.step_counter = torch.tensor(-1, dtype=torch.int32)
+
+    def make_initial_distribution(self):
+        return self.transitioner.make_initial_distribution()
+
+    @property
+    def device(self):
+        return self.init_dist.device
+
+    def emission_probs(self, inputs, end_hints=None, training=False):
+        em_probs = self.emitter[0](inputs, end_hints=end_hints, training=training)
+        for em in self.emitter[1:]:
+            em_probs = em_probs * em(inputs, end_hints=end_hints, training=training)
+        return em_probs
+
+    # ---- one DP step (reference :73-106) ----
+    def forward(self, emission_probs, states, training=None, init=False):
+        from . import ops
+        A = self.transitioner.A_transposed if self.reverse else self.transitioner.A
+        out, scaled, loglik = ops.cell_step(emission_probs, states[0], states[1], A, self.num_models,
+                                            reverse=self.reverse, init=init)
+        if not self.reverse and self.use_step_counter:
+            self.step_counter += 1
+        return out, [scaled, loglik]
+
+    # ---- initial states (reference :108-142) ----
+    def get_initial_state(self, inputs=None, batch_size=None, parallel_factor=1):
+        k, q, dev = self.num_models, self.max_num_states, self.device
+        if parallel_factor == 1:
+            if self.reverse:
+                init = torch.ones((k * batch_size, q), dtype=torch.float32, device=dev)
+            else:
+                init = self.make_initial_distribution().detach().reshape(k, 1, q).expand(k, batch_size, q).reshape(-1, q).contiguous()
+            return [init, torch.zeros((k * batch_size, 1), dtype=torch.float32, device=dev)]
+        pf = parallel_factor
+        b = batch_size // pf
+        A = self.transitioner.A.detach()
+        eye = torch.eye(q, dtype=torch.float32, device=dev).expand(k, b, pf, q, q)
+        if self.reverse:
+            fe = inputs[:, 0, :].reshape(k, b, pf, q).roll(-1, dims=2)
+            rows = fe.unsqueeze(-1) * A.transpose(1, 2)[:, None, None]       # [i, j] = e_next(i) * A[j, i]
+            boundary = pf - 1
+        else:
+            rows = A[:, None, None].expand(k, b, pf, q, q)
+            boundary = 0
+        is_boundary = (torch.arange(pf, device=dev) == boundary).view(1, 1, pf, 1, 1)
+        init = torch.where(is_boundary, eye, rows).reshape(k * batch_size, q * q).contiguous()
+        return [init, torch.zeros((k * batch_size, q), dtype=torch.float32, device=dev)]
+
+    def get_aux_loss(self):
+        return sum(em.get_aux_loss() for em in self.emitter)
+
+    def get_prior_log_density(self):
+        em_priors = [torch.sum(em.get_prior_log_density(), dim=1) for em in self.emitter]
+        trans_priors = self.transitioner.get_prior_log_densities()
+        return sum(em_priors) + sum(trans_priors.values())
+
+    def make_reverse_direction_offspring(self):
+        rev = HmmCell.__new__(HmmCell)
+        nn.Module.__init__(rev)
+        rev.num_states, rev.num_models, rev.max_num_states, rev.dim = self.num_states, self.num_models, self.max_num_states, self.dim
+        rev.emitter = self.emitter
+        rev.transitioner = self.transitioner.reversed_view() if hasattr(self.transitioner, "reversed_view") else self.transitioner
+        rev.epsilon, rev.use_step_counter, rev.use_fake_step_counter = self.epsilon, False, False
+        rev.reverse = True
+        rev.recurrent_init()
+        return rev
+
+    def reverse_direction(self, reverse=True):
+        """Reference :160-162.  Only flips this cell; a transitioner shared with another cell is swapped for a
+        reversed view instead of being mutated."""
+        self.reverse = reverse
+        if reverse and hasattr(self.transitioner, "reversed_view"):
+            self.transitioner = self.transitioner.reversed_view()
+        elif not reverse and hasattr(self.transitioner, "base"):
+            self.transitioner = self.transitioner.base
+
+
+class MsaHmmCell(HmmCell):
+    """Profile-HMM cell, q = 2*length+3 (reference :164-182).  The reference's default ProfileHMMEmitter /
+    ProfileHMMTransitioner cannot be constructed as shipped; this class therefore requires explicit
+    plugins that follow the emitter / transitioner interface."""
+
+    def __init__(self, length, dim=24, emitter=None, transitioner=None, **kwargs):
+        if emitter is None or transitioner is None:
+            raise ValueError("MsaHmmCell needs an emitter and a transitioner (see hmm_layer_b200.dense_plugins)")
+        self.length = [length] if not isinstance(length, list) else length
+        super().__init__([2 * l + 3 for l in self.length], dim, emitter, transitioner, **kwargs)
+        for em in self.emitter:
+            if hasattr(em, "set_lengths"):
+                em.set_lengths(self.length)
+        if hasattr(self.transitioner, "set_lengths"):
+            self.transitioner.set_lengths(self.length)

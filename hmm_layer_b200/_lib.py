@@ -1,0 +1,51 @@
+"""ctypes binding of libhmm_b200.so (the C ABI declared in include/hmm_b200.h).
+
+There is no CPU or PyTorch fallback: if the shared library is missing the import of any hot-path function fails
+loudly, and every entry point requires CUDA tensors."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhmm_b200.so")
+
+EXPORTS = [
+    "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read",
+    "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_run", "hmm_b200_genepred_emission",
+]
+
+_lib = None
+
+
+class HmmB200Error(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `bash hmm_layer_b200/csrc/build.sh` "
+            "(or `python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    c_fp = ctypes.c_void_p
+    lib.hmm_b200_abi_version.restype = ctypes.c_int
+    lib.hmm_b200_last_error.restype = ctypes.c_char_p
+    lib.hmm_b200_set_tuning.argtypes = [ctypes.c_int] * 3
+    lib.hmm_b200_profile_enable.argtypes = [ctypes.c_int]
+    lib.hmm_b200_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_int]
+    lib.hmm_b200_genepred_workspace_size.restype = ctypes.c_size_t
+    lib.hmm_b200_genepred_workspace_size.argtypes = [ctypes.c_int] * 3
+    lib.hmm_b200_genepred_run.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp, c_fp, c_fp,
+                                          ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
+    lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,
+                                               ctypes.c_uint, c_fp, c_fp]
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load().hmm_b200_last_error().decode("utf-8", "replace")
+        raise HmmB200Error(f"libhmm_b200 error {rc}: {msg}")

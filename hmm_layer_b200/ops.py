@@ -1,0 +1,105 @@
+"""Tensor-level entry points over the C ABI: validate, allocate outputs/workspace as torch CUDA tensors, pass raw
+device pointers and the current CUDA stream.  PyTorch is plumbing here (memory + streams), not compute."""
+import torch
+
+from . import _lib
+
+TRAINING = 1
+NO_LOGLIK = 2
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _req(t, name, shape=None):
+    if not isinstance(t, torch.Tensor):
+        raise ValueError(f"{name} must be a torch.Tensor")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must live on a CUDA device (no CPU fallback)")
+    if t.dtype != torch.float32:
+        raise ValueError(f"{name} must be float32, got {t.dtype}")
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError(f"{name} must have shape {tuple(shape)}, got {tuple(t.shape)}")
+    return t.contiguous()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes, device):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def set_tuning(chunk_len=0, chunks_per_products_cta=0, chunks_per_finalize_cta=0):
+    _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, chunks_per_products_cta, chunks_per_finalize_cta))
+
+
+def profile_enable(on=True):
+    _lib.check(_lib.load().hmm_b200_profile_enable(1 if on else 0))
+
+
+def profile_read():
+    """Durations (ms) of the kernels of the last profiled call, in launch order."""
+    import ctypes
+    buf = (ctypes.c_float * 8)()
+    n = _lib.load().hmm_b200_profile_read(buf, 8)
+    if n < 0:
+        _lib.check(n)
+    return [buf[i] for i in range(n)]
+
+
+def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,
+                 want_post=True, want_alpha=False, want_beta=False, out=None):
+    """Fused 15-state gene-HMM evaluation.  inputs (k,B,T,20).  Returns dict with the requested tensors
+    ('post','alpha','beta' each (k,B,T,15)) and 'loglik' (k,B)."""
+    lib = _lib.load()
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    k, B, T, _ = inputs.shape
+    inputs = _req(inputs, "inputs")
+    dev = inputs.device
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _req(codon, "codon", (2, 9, 64))
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
+    with torch.cuda.device(dev):
+        res = {}
+        out = out or {}
+        for name, want in (("post", want_post), ("alpha", want_alpha), ("beta", want_beta)):
+            if want:
+                res[name] = out.get(name) if out.get(name) is not None else torch.empty((k, B, T, 15), dtype=torch.float32, device=dev)
+        res["loglik"] = torch.empty((k, B), dtype=torch.float32, device=dev)
+        nbytes = lib.hmm_b200_genepred_workspace_size(k, B, T)
+        ws = _workspace(nbytes, dev)
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        _lib.check(lib.hmm_b200_genepred_run(
+            _ptr(inputs), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints), flags,
+            _ptr(res.get("post")), _ptr(res.get("alpha")), _ptr(res.get("beta")), _ptr(res["loglik"]),
+            _ptr(ws), ws.numel(), _stream()))
+    return res
+
+
+def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
+    lib = _lib.load()
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    k, B, T, _ = inputs.shape
+    inputs = _req(inputs, "inputs")
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _req(codon, "codon", (2, 9, 64))
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
+    with torch.cuda.device(inputs.device):
+        E = torch.empty((k, B, T, 15), dtype=torch.float32, device=inputs.device)
+        _lib.check(lib.hmm_b200_genepred_emission(_ptr(inputs), k, B, T, _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+                                                  TRAINING if training else 0, _ptr(E), _stream()))
+    return E

@@ -1,0 +1,81 @@
+/* hmm_b200.h — C ABI of libhmm_b200.so: B200 (sm_100a) kernels for the hmm_layer forward / forward-backward path.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer unless stated otherwise; tensors are contiguous float32, row-major;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are stream-ordered,
+ *     stateless and re-entrant; inputs are never written (the reference's emitter mutates its input, defect D5);
+ *   - nothing is allocated inside: the caller owns inputs, outputs and the workspace whose size the matching
+ *     *_workspace_size call reports;
+ *   - return value 0 = success, negative = HMM_B200_E*; hmm_b200_last_error() gives a thread-local message.
+ *
+ * "reference" below = sukui-genomics-cn/hmm_layer; file:line cite the interface each entry point replaces.
+ */
+#ifndef HMM_B200_H
+#define HMM_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HMM_B200_OK 0
+#define HMM_B200_EINVAL (-1)     /* bad argument (shape, null pointer, alignment) */
+#define HMM_B200_EWORKSPACE (-2) /* workspace too small */
+#define HMM_B200_ECUDA (-3)      /* CUDA runtime error, see hmm_b200_last_error() */
+#define HMM_B200_EUNSUPPORTED (-4)
+
+/* flags */
+#define HMM_B200_TRAINING 1u  /* emitter `training=True`: +1e-7 on the codon factor (gene_pred_hmm_emitter.py:260-261) */
+#define HMM_B200_NO_LOGLIK 2u /* posterior without the "- loglik" (MsaHMMLayer.py:513-514) */
+
+int hmm_b200_abi_version(void);
+const char* hmm_b200_last_error(void);
+
+/* Optional tuning of the chunked scan (0 keeps the default): chunk length, chunks per products-CTA,
+ * chunks per finalize-CTA.  Process-wide; meant for benchmarking. */
+int hmm_b200_set_tuning(int chunk_len, int chunks_per_products_cta, int chunks_per_finalize_cta);
+
+/* Per-kernel timing for benchmarks: when enabled, hmm_b200_genepred_run records CUDA events around each of its
+ * launches (products, scan, finalize); hmm_b200_profile_read waits for the last profiled call and writes up to n
+ * durations in milliseconds to the HOST array ms_host, returning how many it wrote. */
+int hmm_b200_profile_enable(int on);
+int hmm_b200_profile_read(float* ms_host, int n);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * 15-state gene-structure HMM (Tiberius), emission fused.  Replaces, for GenePredHMMEmitter +
+ * GenePred(Multi)HMMTransitioner(k=1) cells:
+ *   _state_posterior_log_probs_impl  MsaHMMLayer.py:422-521   (out_post)
+ *   _forward_recursion_impl          MsaHMMLayer.py:227-282   (out_alpha, loglik)
+ *   _backward_recursion_impl         MsaHMMLayer.py:322-381   (out_beta)
+ *   HmmCell.emission_probs           MsaHmmCell.py:61-71  -> GenePredHMMEmitter.forward gene_pred_hmm_emitter.py:231-277
+ *   HmmCell.forward / BaseRNN loop   MsaHmmCell.py:73-106, BaseRNN.py:216-227
+ *   Bidirectional.forward            Bidirectional.py:113-164
+ *
+ *   inputs    (num_models, batch, T, 20)  15 class probabilities ‖ one-hot A,C,G,T,N
+ *   A         (num_models, 15, 15)        transition matrix; only the 23 gene-model edges are read
+ *                                         (gene_pred_hmm_transitioner.py:200-221)
+ *   pi        (num_models, 15)            initial distribution
+ *   Bfull     (num_models, 15, 15)        [state][class] = softmax(emission kernel), intron rows already repeated
+ *   codon     (2, 9, 64)                  left/right 3-mer tables for states E2,START,EI0-2,IE0-2,STOP
+ *   end_hints (num_models, batch, 2, 15)  or NULL
+ *   out_post / out_alpha / out_beta (num_models, batch, T, 15), each may be NULL
+ *   loglik    (num_models, batch)         may be NULL
+ * --------------------------------------------------------------------------------------------------------- */
+size_t hmm_b200_genepred_workspace_size(int num_models, int batch, int T);
+
+int hmm_b200_genepred_run(const float* inputs, int num_models, int batch, int T,
+                          const float* A, const float* pi, const float* Bfull, const float* codon,
+                          const float* end_hints, unsigned flags,
+                          float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* Stand-alone emission (cell.emission_probs API parity): out_E (num_models, batch, T, 15). */
+int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
+                               const float* Bfull, const float* codon, const float* end_hints,
+                               unsigned flags, float* out_E, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,177 @@
+"""GPU parity: the CUDA path through the C ABI against the fp64 oracle on identical seeded inputs.
+
+Tolerances (BASELINE.json north_star: log-likelihoods and posteriors within 1e-4 relative in fp32, argmax exact):
+  loglik  |d|/|ll| <= 1e-4 (we assert 2e-6);  posterior: softmax_q(log_post) within 1e-4 absolute, and in log space
+  where the oracle's p >= 1e-6;  argmax identical wherever the oracle's top-2 margin exceeds 1e-4;
+  log alpha / log beta: |d|/max(1,|x|) <= 1e-4 on entries within e^-14 of the per-position maximum."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import hmm_oracle as O
+from hmm_layer_b200 import ops, synthetic as syn
+from tests.helpers import gene_params, oracle_gene
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(x):
+    return torch.as_tensor(np.asarray(x, np.float32)).cuda()
+
+
+def run_gpu(x, A, pi, Bfull, tab, **kw):
+    hints = kw.pop("end_hints", None)
+    r = ops.genepred_run(x.cuda(), dev(A), dev(pi), dev(Bfull), dev(tab),
+                         end_hints=None if hints is None else dev(hints), **kw)
+    torch.cuda.synchronize()
+    return {k: v.cpu().numpy() for k, v in r.items()}
+
+
+def check_post(got, ref, tol_ll=2e-6):
+    rep = O.parity_report(got["post"], got["loglik"], ref["log_post"], ref["loglik"])
+    assert rep["loglik_rel"] < tol_ll, rep
+    assert rep["max_abs_dp"] < 1e-4, rep
+    assert rep["argmax_mismatch"] == 0, rep
+    assert rep["max_abs_dlog_big"] < 2e-3, rep
+    return rep
+
+
+def check_ab(got, ref):
+    for name, key in (("alpha", "log_alpha"), ("beta", "log_beta")):
+        r = ref[key]
+        big = r - r.max(-1, keepdims=True) > -14
+        d = np.abs(got[name] - r) / np.maximum(1.0, np.abs(r))
+        assert d[big].max() < 1e-4, (name, d[big].max())
+        assert np.isfinite(got[name]).all()
+
+
+@pytest.mark.parametrize("B,T", [(2, 1000), (3, 999), (1, 64), (2, 65), (4, 7), (1, 1), (2, 2), (5, 333)])
+def test_posterior_alpha_beta(B, T):
+    x = syn.gene_inputs(1, B, T, seed=77 + T)
+    A, pi, Bfull, tab = gene_params()
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+    rep = check_post(got, ref)
+    assert rep["max_norm_dev"] < 1e-4
+    check_ab(got, ref)
+
+
+def test_emission_kernel_matches_oracle_and_reference_fixture(golden):
+    g = golden("ref_genepred.npz")
+    Bfull = O.expand_class_rows(O.softmax(g["emission_kernel"], -1))
+    x = torch.as_tensor(g["inputs"])
+    for kw, key in ((dict(), "E"), (dict(end_hints=dev(g["end_hints"])), "E_hints"), (dict(training=True), "E_training")):
+        E = ops.genepred_emission(x.cuda(), dev(Bfull), dev(g["codon_probs"]), **kw).cpu().numpy()
+        np.testing.assert_allclose(E, g[key], rtol=3e-6, atol=1e-12)
+    # soft / N / boundary handling against the oracle (the reference's torch port is wrong at N, defect D5)
+    xs = syn.gene_inputs(1, 3, 200, seed=5, p_n=0.2)
+    xs[0, 1, :, 15:] = torch.softmax(torch.randn(200, 5), -1)          # fully soft nucleotides
+    A, pi, Bf, tab = gene_params()
+    E = ops.genepred_emission(xs.cuda(), dev(Bf), dev(tab)).cpu().numpy()
+    np.testing.assert_allclose(E, O.genepred_emission(xs.numpy(), Bf, tab), rtol=5e-6, atol=1e-12)
+    assert np.array_equal(xs.numpy(), syn.gene_inputs(1, 3, 200, seed=5, p_n=0.2).numpy()) is False  # sanity: we edited xs
+
+
+def test_reference_fixture_forward_backward(golden):
+    """The reference's own HmmCell+BaseRNN outputs (float32) on the committed fixture."""
+    g = golden("ref_genepred.npz")
+    Bfull = O.expand_class_rows(O.softmax(g["emission_kernel"], -1))
+    got = run_gpu(torch.as_tensor(g["inputs"]), g["A"], g["pi"], Bfull, g["codon_probs"], want_alpha=True, want_beta=True)
+    ref_alpha = g["fwd_out"][..., :15] + g["fwd_out"][..., 15:]
+    ref_beta = g["bwd_out"][..., :15] + g["bwd_out"][..., 15:]
+    np.testing.assert_allclose(got["loglik"], g["loglik"], rtol=2e-6)
+    for gotv, refv in ((got["alpha"][0], ref_alpha), (got["beta"][0], ref_beta)):
+        big = refv - refv.max(-1, keepdims=True) > -14
+        assert (np.abs(gotv - refv) / np.maximum(1, np.abs(refv)))[big].max() < 1e-5
+
+
+def test_flags_hints_models():
+    B, T = 3, 500
+    x = syn.gene_inputs(2, B, T, seed=11, p_n=0.01)
+    A, pi, Bfull, tab = gene_params(num_models=2, pi_random=True)
+    hints = np.random.RandomState(0).rand(2, B, 2, 15) + 0.01
+    for kw in (dict(training=True), dict(no_loglik=True), dict(end_hints=hints), dict(end_hints=hints, training=True, no_loglik=True)):
+        ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, **kw)
+        got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True, **kw)
+        if kw.get("no_loglik"):
+            np.testing.assert_allclose(got["post"] - got["loglik"][..., None, None], ref["log_post"] - ref["loglik"][..., None, None],
+                                       rtol=0, atol=5e-3)
+            got = dict(got, post=got["post"] - got["loglik"][..., None, None])
+            ref = dict(ref, log_post=ref["log_post"] - ref["loglik"][..., None, None])
+        check_post(got, ref)
+        check_ab(got, ref)
+
+
+def test_loglik_only_and_determinism():
+    x = syn.gene_inputs(1, 4, 2000, seed=3)
+    A, pi, Bfull, tab = gene_params()
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    a = run_gpu(x, A, pi, Bfull, tab, want_post=False)
+    np.testing.assert_allclose(a["loglik"], ref["loglik"], rtol=2e-6)
+    b = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    c = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    assert np.array_equal(b["post"], c["post"]) and np.array_equal(a["loglik"], b["loglik"])
+
+
+@pytest.mark.parametrize("L,GA,GC", [(16, 2, 4), (32, 8, 16), (128, 4, 4), (100, 6, 3)])
+def test_tuning_does_not_change_results(L, GA, GC):
+    x = syn.gene_inputs(1, 2, 1500, seed=9)
+    A, pi, Bfull, tab = gene_params()
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    try:
+        ops.set_tuning(L, GA, GC)
+        got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+    finally:
+        ops.set_tuning(64, 8, 8)
+    check_post(got, ref)
+    check_ab(got, ref)
+
+
+def test_degenerate_inputs_stay_finite():
+    """One-hot class probabilities, all-N sequences and garbage (negative) inputs: no NaN/inf, rows normalised."""
+    A, pi, Bfull, tab = gene_params()
+    B, T = 3, 400
+    x = syn.gene_inputs(1, B, T, seed=21)
+    x[0, 0, :, :15] = torch.nn.functional.one_hot(torch.randint(0, 15, (T,)), 15).float()
+    x[0, 1, :, 15:] = torch.tensor([0., 0, 0, 0, 1])
+    x[0, 2] = torch.randn(T, 20)
+    got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+    for k in ("post", "alpha", "beta", "loglik"):
+        assert np.isfinite(got[k]).all(), k
+    np.testing.assert_allclose(np.exp(got["post"].astype(np.float64)).sum(-1), 1.0, atol=1e-4)
+    ref = oracle_gene(x.numpy()[:, :2], A, pi, Bfull, tab)
+    check_post({k: v[:, :2] for k, v in got.items()}, ref)
+
+
+def test_config2_full_size_properties():
+    """BASELINE config 2 shape (B=32, T=9999): size-independent properties + oracle on a slice of the batch."""
+    x = syn.gene_inputs(1, 32, 9999, seed=1234)
+    A, pi, Bfull, tab = gene_params()
+    got = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    assert np.isfinite(got["post"]).all()
+    np.testing.assert_allclose(np.exp(got["post"].astype(np.float64)).sum(-1), 1.0, atol=1e-4)
+    sl = slice(0, 3)
+    ref = oracle_gene(x.numpy()[:, sl], A, pi, Bfull, tab)
+    check_post({k: v[:, sl] for k, v in got.items()}, ref)
+    # batch independence: a sequence evaluated alone gives the same bits
+    alone = run_gpu(x[:, 5:6].contiguous(), A, pi, Bfull, tab, want_post=True)
+    assert np.array_equal(alone["post"][0, 0], got["post"][0, 5])
+    # reversal symmetry of the recursion is not available for this model; instead: concatenation consistency
+    # loglik(seq) computed with chunk length 64 equals chunk length 37
+    try:
+        ops.set_tuning(37, 8, 8)
+        g2 = run_gpu(x[:, :4].contiguous(), A, pi, Bfull, tab, want_post=False)
+    finally:
+        ops.set_tuning(64, 8, 8)
+    np.testing.assert_allclose(g2["loglik"], got["loglik"][:, :4], rtol=1e-6)
+
+
+def test_argument_validation():
+    A, pi, Bfull, tab = gene_params()
+    x = syn.gene_inputs(1, 2, 50)
+    with pytest.raises(ValueError):
+        ops.genepred_run(x, dev(A), dev(pi), dev(Bfull), dev(tab))             # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        ops.genepred_run(x.cuda()[..., :19], dev(A), dev(pi), dev(Bfull), dev(tab))
+    with pytest.raises(ValueError):
+        ops.genepred_run(x.cuda().double(), dev(A), dev(pi), dev(Bfull), dev(tab))
