@@ -27,10 +27,10 @@ def run_gpu(x, A, pi, Bfull, tab, **kw):
     return {k: v.cpu().numpy() for k, v in r.items()}
 
 
-def check_post(got, ref, tol_ll=2e-6):
+def check_post(got, ref, tol_ll=2e-6, tol_dp=1e-4):
     rep = O.parity_report(got["post"], got["loglik"], ref["log_post"], ref["loglik"])
     assert rep["loglik_rel"] < tol_ll, rep
-    assert rep["max_abs_dp"] < 1e-4, rep
+    assert rep["max_abs_dp"] < tol_dp, rep
     assert rep["argmax_mismatch"] == 0, rep
     assert rep["max_abs_dlog_big"] < 2e-3, rep
     return rep
@@ -93,12 +93,16 @@ def test_flags_hints_models():
     for kw in (dict(training=True), dict(no_loglik=True), dict(end_hints=hints), dict(end_hints=hints, training=True, no_loglik=True)):
         ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, **kw)
         got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True, **kw)
+        tol_dp = 1e-4
         if kw.get("no_loglik"):
+            # log_post + loglik is ~ -5500 here: float32 resolves that to 4.9e-4, so the un-normalised output
+            # carries that quantisation (the reference's own output format has the same property)
             np.testing.assert_allclose(got["post"] - got["loglik"][..., None, None], ref["log_post"] - ref["loglik"][..., None, None],
                                        rtol=0, atol=5e-3)
             got = dict(got, post=got["post"] - got["loglik"][..., None, None])
             ref = dict(ref, log_post=ref["log_post"] - ref["loglik"][..., None, None])
-        check_post(got, ref)
+            tol_dp = 5e-4
+        check_post(got, ref, tol_dp=tol_dp)
         check_ab(got, ref)
 
 
