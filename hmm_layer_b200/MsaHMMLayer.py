@@ -33,7 +33,7 @@ def _check_inputs(inputs, cell, parallel_factor):
 def _gene_run(inputs, cell, end_hints, training, **want):
     em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
     return ops.genepred_run(inputs, tr.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1),
-                            em.make_B_full().detach(), em.codon_probs, end_hints=end_hints, training=training, **want)
+                            em.make_B_full().detach(), em.codon5(inputs.device), end_hints=end_hints, training=training, **want)
 
 
 def _priors(cell, result, return_prior):

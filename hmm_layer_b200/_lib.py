@@ -6,11 +6,12 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhmm_b200.so")
+LIB_PATH = os.environ.get("HMM_B200_LIB", os.path.join(_HERE, "libhmm_b200.so"))   # override: build-variant experiments
 
 EXPORTS = [
-    "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read",
-    "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_run", "hmm_b200_genepred_emission",
+    "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read", "hmm_b200_debug_phases",
+    "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_prepare_codon", "hmm_b200_genepred_run",
+    "hmm_b200_genepred_emission",
 ]
 
 _lib = None
@@ -34,9 +35,11 @@ def load():
     lib.hmm_b200_last_error.restype = ctypes.c_char_p
     lib.hmm_b200_set_tuning.argtypes = [ctypes.c_int] * 3
     lib.hmm_b200_profile_enable.argtypes = [ctypes.c_int]
+    lib.hmm_b200_debug_phases.argtypes = [ctypes.c_void_p]
     lib.hmm_b200_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_int]
     lib.hmm_b200_genepred_workspace_size.restype = ctypes.c_size_t
     lib.hmm_b200_genepred_workspace_size.argtypes = [ctypes.c_int] * 3
+    lib.hmm_b200_genepred_prepare_codon.argtypes = [c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_run.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp, c_fp, c_fp,
                                           ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
     lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,

@@ -1,19 +1,35 @@
 // 15-state gene-structure HMM: fused emission + chunked scaled forward / backward / posterior for sm_100a.
 //
-// Three kernels per call:
-//   products_kernel  K_A  per chunk of L positions: emission (never written to HBM) and the chunk's transfer
-//                         matrix prod_t (A diag(e_t)) as 15 conditional forward rows, row-normalised
-//                         (the reference's parallel_factor>1 form, MsaHmmCell.py:121-142, keeping only the
-//                         chunk-end matrix);
-//   scan_kernel      K_B  per sequence: prefix (forward) and suffix (backward) boundary vectors over the chunk
-//                         matrices (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49, done in
-//                         scaled probability space), log-likelihood;
-//   finalize_kernel  K_C  per chunk: the exact sequential recursions of MsaHmmCell.py:73-106 (same floors, same
-//                         order) started from the boundary vectors, both directions concurrently, then
-//                         log posterior / log alpha / log beta written once.
+// Two kernels per call (plus a boundary-scan kernel for long sequences / sequence sharding), see DESIGN.md §3:
+//
+//   products_kernel  K1  one CTA per tile = G(32) chunks x L positions of one sequence.  Emission (never written
+//                        to HBM), then the chunk transfer matrices prod_t (A diag(e_t)) as 15 conditional rows
+//                        (the reference's parallel_factor>1 form, MsaHmmCell.py:121-142, keeping only the
+//                        chunk-end matrix).  The 8 single-in/single-out states (START, EI*, IE*, STOP) are
+//                        eliminated algebraically, so a row step is a 15-FMA two-step recurrence over the 7 core
+//                        states instead of a 23-edge product; scaling is lazy and by exact powers of two.
+//                        A 5-level in-CTA product tree (all threads per level) over the 32 chunk matrices is kept
+//                        whole (heap order): its root is the tile matrix, its inner nodes let K2 reach every
+//                        chunk boundary in 5 parallel steps.
+//   boundary_kernel  K_B only when a sequence has more tiles than K2 scans inline, when only the log-likelihood
+//                        is wanted, or when the sequence is sharded over GPUs: prefix / suffix boundary vectors
+//                        over the tile matrices (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49,
+//                        in scaled probability space).
+//   finalize_kernel  K2  one CTA per tile: emission again (registers/smem only), boundary vectors by a scan over
+//                        the tile matrices and a 5-step down-sweep of the tile's tree, then the exact recursions of
+//                        MsaHmmCell.py:73-106 (same floors, same order) inside every chunk, both directions
+//                        concurrently meeting in the middle, then log posterior / log alpha / log beta written
+//                        once, coalesced.
 //
 // State order (gene_pred_hmm_transitioner.py:187-188): 0 Ir | 1-3 I0-2 | 4-6 E0-2 | 7 START | 8-10 EI0-2 |
 // 11-13 IE0-2 | 14 STOP.  Only the 23 structural edges of A are read (gene_pred_hmm_transitioner.py:200-221).
+// "core" = states 0..6, "pass" = states 7..14 (one predecessor, one successor, both core).
+//
+// Stored matrix block (16x16 floats): rows 0-14 = [row-normalised transfer row M-hat | relative row scale s'],
+// row 15 = [column sums of diag(s') M-hat | block exponent E as int bits]; true matrix = 2^E diag(s') M-hat.
+// All scales are exact powers of two (integer bookkeeping), so no log/exp rounding enters the posteriors.
+//
+// The numpy model tests/chunk_algo_model.py mirrors the arithmetic and is checked against the oracle.
 #include "common.cuh"
 
 namespace hmm {
@@ -23,30 +39,56 @@ constexpr int Q = 15;      // states
 constexpr int QP = 16;     // padded row
 constexpr int SIN = 20;    // input floats per position: 15 class probabilities + 5 nucleotide one-hot
 constexpr int NEDGE = 23;
-constexpr int MAT = QP * QP;  // floats per stored chunk matrix
+constexpr int MAT = QP * QP;  // floats per stored matrix block
+constexpr int BST = 20;       // row stride of blocks staged for the scans (16-byte rows; <= 2-way bank conflicts)
+constexpr int BSZ = QP * BST; // floats per staged block
+constexpr int G = 32;         // chunks per tile
+constexpr int HEAP = 2 * G;   // blocks per tile in heap order: [1] tile product, [2..G) inner nodes, [G..2G) chunks
+constexpr int MAX_INLINE_TILES = 16;  // K2 scans up to this many tile matrices itself
+constexpr int K1_THREADS = G * 16;
+#ifndef HMM_K1_BLOCKS
+#define HMM_K1_BLOCKS 2               // CTAs of K1 per SM the register budget is sized for (1: 128 regs, 2: 64 regs)
+#endif
+constexpr int K1_NP = HMM_K1_BLOCKS == 2 ? 1 : 2;   // positions per thread and emission round in K1
+constexpr int MAX_L = 48;             // longest chunk (shared memory bound)
+constexpr int DIV_SHIFT = 21;         // i / L == (i * mL) >> 21 for i < 4096, L <= 48
+constexpr double LN2D = 0.69314718055994531;
+constexpr int T5_FLOATS = 2 * 125 * 12;
 
 // edges in the reference's kernel order (from, to)
 __device__ constexpr int ESRC[NEDGE] = {0, 0, 14, 7, 5, 4, 4, 8, 1, 1, 11, 5, 5, 9, 2, 2, 12, 6, 6, 10, 3, 3, 13};
 __device__ constexpr int EDST[NEDGE] = {0, 7, 0, 5, 14, 5, 8, 1, 1, 11, 4, 6, 9, 2, 2, 12, 5, 4, 10, 3, 3, 13, 6};
+// core predecessor of core state j; predecessor / successor of pass state 7+p
+__device__ constexpr int SRC1[7] = {0, 1, 2, 3, 6, 4, 5};
+__device__ constexpr int PRED[8] = {0, 4, 5, 6, 1, 2, 3, 5};
+__device__ constexpr int SUCC[8] = {5, 1, 2, 3, 4, 5, 6, 0};
 
 struct Args {
   const float* inputs;
   const float* A;
   const float* pi;
   const float* Bfull;
-  const float* codon;
+  const float* codon5;  // [2][125][12] 5-symbol codon tables (prepare_codon)
   const float* hints;
   int num_models, batch, T;
   unsigned flags;
-  int L, C;  // chunk length, chunks per sequence
-  int GA, GC;
-  float* Mn;    // [NB*C][16][16] row-normalised chunk matrices, common-scaled so the largest row scale is 1
-  float* gsc;   // [NB*C]         log of the common scale
-  float* fvec;  // [NB*C][16]     normalised alpha entering chunk c (pi for c = 0)
-  float* rvec;  // [NB*C][16]     normalised R (backward variable) at the last position of chunk c
-  float* fcum;  // [NB*C]         log scale belonging to fvec
-  float* rcum;  // [NB*C]         log scale belonging to rvec
-  float* llws;  // [NB]
+  int L;           // chunk length
+  unsigned mL;     // (1 << DIV_SHIFT) / L + 1
+  int C;           // chunks per sequence = ceil(T / L)
+  int P;           // tiles per sequence  = ceil(C / G)
+  int top_inline;  // K2 scans the tile matrices itself (no boundary_kernel)
+  // sequence sharding (multi-GPU): this rank holds positions [seq_off, seq_off + T) of sequences of total length
+  // seq_total; halo nucleotides and boundary vectors come from the neighbours.
+  int seq_off, seq_total;
+  const float* halo;   // [NB][4][5] nucleotide flags of positions -2,-1 (left) and T,T+1 (right) or NULL
+  float* Mh;   // [NB][P][HEAP][256] per tile: product tree in heap order (node k = node 2k . node 2k+1)
+  float* Mt;   // [NB][P][256] tile matrices (= heap node 1), contiguous per sequence for the top-level scan
+  float* bvf;  // [NB][P][16] forward boundary vector entering tile p, slot 15 = exponent (int bits)
+  float* bvr;  // [NB][P][16] backward boundary vector leaving tile p, slot 15 = exponent (int bits)
+  const float* in_f;  // [NB][16] boundary entering this shard, slot 15 = exponent bits (NULL: pi)     multi-GPU
+  const float* in_r;  // [NB][16] boundary leaving this shard (NULL: ones)
+  float* llws;        // [NB] log-likelihood
+  long long* dbg;     // optional phase timestamps (tools/phase_times.py), normally NULL
   float* out_post;
   float* out_alpha;
   float* out_beta;
@@ -54,146 +96,21 @@ struct Args {
 };
 
 // ------------------------------------------------------------------------------------------------------------
-// emission (gene_pred_hmm_emitter.py:93-121 class part, :231-263 3-mer part, kmer.py:3-47 soft 3-mers)
+// small helpers
 // ------------------------------------------------------------------------------------------------------------
-struct EmisParams {
-  float B[Q][QP];          // [state][class], column 15 = 0
-  float codon[2][9][64];   // [left|right][E2,START,EI0-2,IE0-2,STOP][3-mer]
-};
+#define HMM_MARK(base, k) do { if (a.dbg && threadIdx.x == 0) a.dbg[(size_t)(base) * 16 + (k)] = clock64(); } while (0)
 
-__device__ __forceinline__ void load_emis_params(EmisParams& sp, const float* __restrict__ Bm,
-                                                 const float* __restrict__ codon) {
-  for (int i = threadIdx.x; i < Q * QP; i += blockDim.x) {
-    const int q = i >> 4, s = i & 15;
-    sp.B[q][s] = (s < Q) ? __ldg(Bm + q * Q + s) : 0.f;
-  }
-  float* cd = &sp.codon[0][0][0];
-  for (int i = threadIdx.x; i < 2 * 9 * 64; i += blockDim.x) cd[i] = __ldg(codon + i);
-}
+__device__ __forceinline__ int fexp(float x) { return ((__float_as_int(x) >> 23) & 0xff) - 127; }
+__device__ __forceinline__ int clamp_exp(int e) { return max(-126, min(126, e)); }
+// 2^(-e), e clamped to [-126, 126]
+__device__ __forceinline__ float pow2neg(int e) { return __int_as_float((127 - clamp_exp(e)) << 23); }
+// exponent of a positive float, 0 for non-positive input
+__device__ __forceinline__ int pexp(float x) { return x > 0.f ? fexp(x) : 0; }
 
-// distribution over A,C,G,T at position t; N (flag exactly 1) and out-of-range positions count 1/4 each
-__device__ __forceinline__ float4 nuc_dist(const float* __restrict__ seq, int t, int T) {
-  if (t < 0 || t >= T) return make_float4(.25f, .25f, .25f, .25f);
-  const float* p = seq + (size_t)t * SIN + Q;
-  const float add = (__ldg(p + 4) == 1.0f) ? 0.25f : 0.f;
-  return make_float4(__ldg(p) + add, __ldg(p + 1) + add, __ldg(p + 2) + add, __ldg(p + 3) + add);
-}
-
-// 0..3 when p is exactly one-hot, -1 otherwise
-__device__ __forceinline__ int hard_code(const float4 p) {
-  const int ones = (p.x == 1.f) + (p.y == 1.f) + (p.z == 1.f) + (p.w == 1.f);
-  const int zeros = (p.x == 0.f) + (p.y == 0.f) + (p.z == 0.f) + (p.w == 0.f);
-  if (ones != 1 || zeros != 3) return -1;
-  return (p.y == 1.f) ? 1 : (p.z == 1.f) ? 2 : (p.w == 1.f) ? 3 : 0;
-}
-
-__device__ __forceinline__ float comp(const float4 p, int i) { return i == 0 ? p.x : i == 1 ? p.y : i == 2 ? p.z : p.w; }
-
-// <soft 3-mer, table[s]> for the 9 constrained states. flat 3-mer index = (near*4 + far)*4 + pivot
-__device__ __forceinline__ void codon_side(const float (*tab)[64], const float4 pv, const float4 nr, const float4 fr,
-                                           float (&out)[9]) {
-  const int c0 = hard_code(pv), c1 = hard_code(nr), c2 = hard_code(fr);
-  if ((c0 | c1 | c2) >= 0) {
-    const int idx = (c1 * 4 + c2) * 4 + c0;
+__device__ __forceinline__ int half_max_int(int v) {
 #pragma unroll
-    for (int s = 0; s < 9; ++s) out[s] = tab[s][idx];
-  } else {
-#pragma unroll
-    for (int s = 0; s < 9; ++s) out[s] = 0.f;
-#pragma unroll 1
-    for (int i = 0; i < 64; ++i) {
-      const float w = comp(nr, i >> 4) * comp(fr, (i >> 2) & 3) * comp(pv, i & 3);
-      if (w != 0.f) {
-#pragma unroll
-        for (int s = 0; s < 9; ++s) out[s] = fmaf(w, tab[s][i], out[s]);
-      }
-    }
-  }
-}
-
-// emission probabilities of one position, floored at eps when FLOOR; dst[0..15] (slot 15 = 0)
-template <bool FLOOR>
-__device__ __forceinline__ void emit_position(const EmisParams& sp, const float* __restrict__ seq, int t, int T,
-                                              const float4* __restrict__ P /* P[-2..2] around t */,
-                                              const float* __restrict__ hints, unsigned flags, float* dst) {
-  const float* row = seq + (size_t)t * SIN;
-  const float4 x0 = ldg4(row), x1 = ldg4(row + 4), x2 = ldg4(row + 8), x3 = ldg4(row + 12);
-  float fl[9], fr[9];
-  codon_side(sp.codon[0], P[0], P[1], P[2], fl);
-  codon_side(sp.codon[1], P[0], P[-1], P[-2], fr);
-  const float train = (flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
-  float e[QP];
-#pragma unroll
-  for (int q = 0; q < Q; ++q) {
-    const float4* b = reinterpret_cast<const float4*>(sp.B[q]);
-    float acc = dot4(x0, b[0], 0.f);
-    acc = dot4(x1, b[1], acc);
-    acc = dot4(x2, b[2], acc);
-    acc = dot4(x3, b[3], acc);  // b[3].w == 0 removes x3.w (a nucleotide flag)
-    const float cod = ((q < 6) ? (1.0f / 4096.0f) : fl[q - 6] * fr[q - 6]) + train;
-    e[q] = acc * cod;
-  }
-  if (hints != nullptr) {
-    if (t == 0) {
-#pragma unroll
-      for (int q = 0; q < Q; ++q) e[q] *= __ldg(hints + q);
-    }
-    if (t == T - 1) {
-#pragma unroll
-      for (int q = 0; q < Q; ++q) e[q] *= __ldg(hints + Q + q);
-    }
-  }
-  e[15] = 0.f;
-  const float lo = FLOOR ? kEps : -INFINITY;
-  float4* d4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-  for (int v = 0; v < 4; ++v)
-    d4[v] = make_float4(fmaxf(e[4 * v], lo), fmaxf(e[4 * v + 1], lo), fmaxf(e[4 * v + 2], lo),
-                        v == 3 ? 0.f : fmaxf(e[4 * v + 3], lo));
-}
-
-// emission of every position of the G chunks [c_base, c_base+G) of sequence n into Es (chunk stride CS floats)
-template <bool FLOOR>
-__device__ __forceinline__ void emission_stage(const Args& a, const EmisParams& sp, float4* Ps, float* Es, int n,
-                                               int c_base, int G, int CS) {
-  const int L = a.L, T = a.T;
-  const float* seq = a.inputs + (size_t)n * T * SIN;
-  const float* hints = a.hints ? a.hints + (size_t)n * 2 * Q : nullptr;
-  const int LH = L + 4;
-  for (int i = threadIdx.x; i < G * LH; i += blockDim.x) {
-    const int ci = i / LH, u = i - ci * LH;
-    const int c = c_base + ci;
-    Ps[i] = (c < a.C) ? nuc_dist(seq, c * L - 2 + u, T) : make_float4(.25f, .25f, .25f, .25f);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < G * L; i += blockDim.x) {
-    const int ci = i / L, u = i - ci * L;
-    const int c = c_base + ci, t = c * L + u;
-    if (c < a.C && t < T) emit_position<FLOOR>(sp, seq, t, T, Ps + ci * LH + u + 2, hints, a.flags, Es + ci * CS + u * QP);
-  }
-  __syncthreads();
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// sparse 15-state transition products
-// ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void load_edges(const float* __restrict__ Am, float (&w)[NEDGE]) {
-#pragma unroll
-  for (int e = 0; e < NEDGE; ++e) w[e] = __ldg(Am + ESRC[e] * Q + EDST[e]);
-}
-// R = a . A   (forward, MsaHmmCell.py:80 with transitioner.reverse == False)
-__device__ __forceinline__ void vec_A(const float (&a)[Q], const float (&w)[NEDGE], float (&R)[Q]) {
-#pragma unroll
-  for (int j = 0; j < Q; ++j) R[j] = 0.f;
-#pragma unroll
-  for (int e = 0; e < NEDGE; ++e) R[EDST[e]] = fmaf(a[ESRC[e]], w[e], R[EDST[e]]);
-}
-// R = A . b   (backward: b . A^T, transitioner.reverse == True)
-__device__ __forceinline__ void A_vec(const float (&b)[Q], const float (&w)[NEDGE], float (&R)[Q]) {
-#pragma unroll
-  for (int i = 0; i < Q; ++i) R[i] = 0.f;
-#pragma unroll
-  for (int e = 0; e < NEDGE; ++e) R[ESRC[e]] = fmaf(w[e], b[EDST[e]], R[ESRC[e]]);
+  for (int o = 8; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o, 16));
+  return v;
 }
 
 __device__ __forceinline__ void load_row16(const float* p, float (&v)[QP]) {
@@ -215,333 +132,1100 @@ __device__ __forceinline__ float sum15(const float (&v)[Q]) {
   return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7])) + (((v[8] + v[9]) + (v[10] + v[11])) +
          ((v[12] + v[13]) + v[14]));
 }
+__device__ __forceinline__ float sum15p(const float* v) {
+  return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7])) + (((v[8] + v[9]) + (v[10] + v[11])) +
+         ((v[12] + v[13]) + v[14]));
+}
+__device__ __forceinline__ float sum7(const float (&v)[7]) { return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + v[6]); }
 
-// one scaled step: a <- normalise(E ⊙ max(R, eps)), returns the scale S   (MsaHmmCell.py:87-92)
-__device__ __forceinline__ float scaled_step(const float* Erow, const float (&R)[Q], float (&a)[Q]) {
-  float e[QP];
-  load_row16(Erow, e);
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+// ------------------------------------------------------------------------------------------------------------
+// emission (gene_pred_hmm_emitter.py:93-121 class part, :231-263 3-mer part, kmer.py:3-47 soft 3-mers)
+// ------------------------------------------------------------------------------------------------------------
+struct EmisSmem {
+  float B[Q][QP];          // [state][class], column 15 = 0
+  float T5[2][125][12];    // [left|right][5-symbol 3-mer][E2,START,EI0-2,IE0-2,STOP, pad]; symbol 4 = uniform
+};
+
+// Builds the 5-symbol tables from the reference's (2,9,64) codon tables: symbol 4 (N / outside the sequence) is the
+// average over the four bases (kmer.py:21-33).  One CTA; run once per parameter set.
+__global__ void __launch_bounds__(256) prepare_codon_kernel(const float* __restrict__ codon, float* __restrict__ out) {
+  __shared__ float T5[2][125][12];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int i = tid; i < T5_FLOATS; i += nt) (&T5[0][0][0])[i] = 0.f;
+  __syncthreads();
+  for (int i = tid; i < 2 * 9 * 64; i += nt) {
+    const int side = i / 576, r = i - side * 576, s = r >> 6, k = r & 63;
+    const int nr = k >> 4, fr = (k >> 2) & 3, pv = k & 3;
+    T5[side][(nr * 5 + fr) * 5 + pv][s] = codon[i];
+  }
+  __syncthreads();
+  for (int i = tid; i < 2 * 16 * 9; i += nt) {  // pivot = 4
+    const int side = i / 144, r = i - side * 144, hi = r / 9, s = r - hi * 9;
+    const int base = ((hi >> 2) * 5 + (hi & 3)) * 5;
+    const float* t = &T5[side][base][s];
+    T5[side][base + 4][s] = 0.25f * ((t[0] + t[12]) + (t[24] + t[36]));
+  }
+  __syncthreads();
+  for (int i = tid; i < 2 * 20 * 9; i += nt) {  // far = 4
+    const int side = i / 180, r = i - side * 180, hi = r / 9, s = r - hi * 9;
+    const int nr = hi / 5, pv = hi - nr * 5;
+    const float* t = &T5[side][nr * 25 + pv][s];
+    T5[side][nr * 25 + 20 + pv][s] = 0.25f * ((t[0] + t[60]) + (t[120] + t[180]));
+  }
+  __syncthreads();
+  for (int i = tid; i < 2 * 25 * 9; i += nt) {  // near = 4
+    const int side = i / 225, r = i - side * 225, lo = r / 9, s = r - lo * 9;
+    const float* t = &T5[side][lo][s];
+    T5[side][100 + lo][s] = 0.25f * ((t[0] + t[300]) + (t[600] + t[900]));
+  }
+  __syncthreads();
+  for (int i = tid; i < T5_FLOATS; i += nt) out[i] = (&T5[0][0][0])[i];
+}
+
+// B rows and the 5-symbol codon tables into shared memory (no barrier inside)
+__device__ __forceinline__ void load_emis_params(EmisSmem& sp, const float* __restrict__ Bm, const float* __restrict__ codon5) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int i = tid; i < Q * QP; i += nt) {
+    const int q = i >> 4, s = i & 15;
+    sp.B[q][s] = (s < Q) ? __ldg(Bm + q * Q + s) : 0.f;
+  }
+  const float4* src = reinterpret_cast<const float4*>(codon5);
+  float4* dst = reinterpret_cast<float4*>(&sp.T5[0][0][0]);
+  for (int i = tid; i < T5_FLOATS / 4; i += nt) dst[i] = __ldg(src + i);
+}
+
+// pointer to the 5 nucleotide flags of (shard-local) position t, or nullptr when t lies outside the whole sequence
+__device__ __forceinline__ const float* nuc_ptr(const Args& a, int n, int t) {
+  if (t >= 0 && t < a.T) return a.inputs + ((size_t)n * a.T + t) * SIN + Q;
+  if (a.halo == nullptr) return nullptr;
+  const int gt = a.seq_off + t;
+  if (gt < 0 || gt >= a.seq_total) return nullptr;
+  if (t < 0 && t >= -2) return a.halo + ((size_t)n * 4 + (t + 2)) * 5;
+  if (t >= a.T && t < a.T + 2) return a.halo + ((size_t)n * 4 + 2 + (t - a.T)) * 5;
+  return nullptr;
+}
+
+// 0..3 exactly one-hot base, 4 uniform (N flag exactly 1 with no base set), -1 anything else
+__device__ __forceinline__ int code_of(float x, float y, float z, float w, float f) {
+  const int zeros = (x == 0.f) + (y == 0.f) + (z == 0.f) + (w == 0.f);
+  if (f == 1.f) return zeros == 4 ? 4 : -1;
+  const int ones = (x == 1.f) + (y == 1.f) + (z == 1.f) + (w == 1.f);
+  if (ones != 1 || zeros != 3) return -1;
+  return (y == 1.f) ? 1 : (z == 1.f) ? 2 : (w == 1.f) ? 3 : 0;
+}
+__device__ __forceinline__ int nuc_code(const Args& a, int n, int t) {
+  const float* p = nuc_ptr(a, n, t);
+  if (p == nullptr) return 4;   // outside the sequence: 1/4 each (kmer.py:27-33)
+  return code_of(__ldg(p), __ldg(p + 1), __ldg(p + 2), __ldg(p + 3), __ldg(p + 4));
+}
+
+// distribution over A,C,G,T at position t (kmer.py:21-33)
+__device__ __forceinline__ float4 nuc_dist(const Args& a, int n, int t) {
+  const float* p = nuc_ptr(a, n, t);
+  if (p == nullptr) return make_float4(.25f, .25f, .25f, .25f);
+  const float add = (__ldg(p + 4) == 1.0f) ? 0.25f : 0.f;
+  return make_float4(__ldg(p) + add, __ldg(p + 1) + add, __ldg(p + 2) + add, __ldg(p + 3) + add);
+}
+__device__ __forceinline__ float comp(const float4 p, int i) { return i == 0 ? p.x : i == 1 ? p.y : i == 2 ? p.z : p.w; }
+
+// generic soft 3-mer contraction (rare: a nucleotide row that is neither one-hot nor N)
+__device__ __noinline__ void codon_side_soft(const EmisSmem& sp, int side, const float4 pv, const float4 nr, const float4 fr,
+                                             float* out) {
+  for (int s = 0; s < 9; ++s) out[s] = 0.f;
+  for (int i = 0; i < 64; ++i) {
+    const int a = i >> 4, b = (i >> 2) & 3, c = i & 3;
+    const float w = comp(nr, a) * comp(fr, b) * comp(pv, c);
+    if (w != 0.f) {
+      const float* t = sp.T5[side][(a * 5 + b) * 5 + c];
+      for (int s = 0; s < 9; ++s) out[s] = fmaf(w, t[s], out[s]);
+    }
+  }
+}
+
+// codon factors of the 9 constrained states at position t; cd points at the code of t (cd[-2..2] valid)
+__device__ __forceinline__ void codon_factors(const Args& a, const EmisSmem& sp, int n, int t, const signed char* cd, float (&cod)[9]) {
+  float fl[12], fr[12];
+  const int c0 = cd[0], l1 = cd[1], l2 = cd[2], r1 = cd[-1], r2 = cd[-2];
+  if ((c0 | l1 | l2) >= 0) {
+    const float4* t4 = reinterpret_cast<const float4*>(sp.T5[0][(l1 * 5 + l2) * 5 + c0]);
+    const float4 u0 = t4[0], u1 = t4[1], u2 = t4[2];
+    fl[0] = u0.x; fl[1] = u0.y; fl[2] = u0.z; fl[3] = u0.w; fl[4] = u1.x; fl[5] = u1.y; fl[6] = u1.z; fl[7] = u1.w; fl[8] = u2.x;
+  } else {
+    codon_side_soft(sp, 0, nuc_dist(a, n, t), nuc_dist(a, n, t + 1), nuc_dist(a, n, t + 2), fl);
+  }
+  if ((c0 | r1 | r2) >= 0) {
+    const float4* t4 = reinterpret_cast<const float4*>(sp.T5[1][(r1 * 5 + r2) * 5 + c0]);
+    const float4 u0 = t4[0], u1 = t4[1], u2 = t4[2];
+    fr[0] = u0.x; fr[1] = u0.y; fr[2] = u0.z; fr[3] = u0.w; fr[4] = u1.x; fr[5] = u1.y; fr[6] = u1.z; fr[7] = u1.w; fr[8] = u2.x;
+  } else {
+    codon_side_soft(sp, 1, nuc_dist(a, n, t), nuc_dist(a, n, t - 1), nuc_dist(a, n, t - 2), fr);
+  }
 #pragma unroll
-  for (int j = 0; j < Q; ++j) a[j] = e[j] * fmaxf(R[j], kEps);
-  const float S = sum15(a);
-  const float inv = __frcp_rn(S);
+  for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
+}
+
+// Emission probabilities of NP (shard-local) positions t[0..NP) of sequence n, computed together so that every B row
+// fetched from shared memory serves all of them.  FLOOR: max(e, eps) as the recursion applies it (MsaHmmCell.py:87).
+template <bool FLOOR, int NP>
+__device__ __forceinline__ void emit_n(const Args& a, const EmisSmem& sp, int n, const int (&t)[NP],
+                                       const signed char* const (&cd)[NP], float (&e)[NP][Q]) {
+  float4 x[NP][4];
+  float cod[NP][9];
 #pragma unroll
-  for (int j = 0; j < Q; ++j) a[j] *= inv;
-  return S;
+  for (int k = 0; k < NP; ++k) {
+    const float* row = a.inputs + ((size_t)n * a.T + t[k]) * SIN;
+    x[k][0] = ldg4(row); x[k][1] = ldg4(row + 4); x[k][2] = ldg4(row + 8); x[k][3] = ldg4(row + 12);
+  }
+#pragma unroll
+  for (int k = 0; k < NP; ++k) codon_factors(a, sp, n, t[k], cd[k], cod[k]);
+  const float train = (a.flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
+  const float free_cod = (1.0f / 4096.0f) + train;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const float4* b = reinterpret_cast<const float4*>(sp.B[q]);
+    const float4 b0 = b[0], b1 = b[1], b2 = b[2], b3 = b[3];   // b3.w == 0 removes x3.w (a nucleotide flag)
+#pragma unroll
+    for (int k = 0; k < NP; ++k) {
+      const float s = dot4(x[k][3], b3, dot4(x[k][2], b2, dot4(x[k][1], b1, dot4(x[k][0], b0, 0.f))));
+      e[k][q] = s * ((q < 6) ? free_cod : cod[k][q < 6 ? 0 : q - 6] + train);
+    }
+  }
+  if (a.hints != nullptr) {
+    const float* h = a.hints + (size_t)n * 2 * Q;
+#pragma unroll
+    for (int k = 0; k < NP; ++k) {
+      const int g = a.seq_off + t[k];
+      if (g == 0) {
+#pragma unroll
+        for (int q = 0; q < Q; ++q) e[k][q] *= __ldg(h + q);
+      }
+      if (g == a.seq_total - 1) {
+#pragma unroll
+        for (int q = 0; q < Q; ++q) e[k][q] *= __ldg(h + Q + q);
+      }
+    }
+  }
+  if (FLOOR) {
+#pragma unroll
+    for (int k = 0; k < NP; ++k) {
+#pragma unroll
+      for (int q = 0; q < Q; ++q) e[k][q] = fmaxf(e[k][q], kEps);
+    }
+  }
+}
+
+// two positions i0 (valid) and i1 (valid iff two) of the tile
+template <bool FLOOR>
+__device__ __forceinline__ void emit_pair(const Args& a, const EmisSmem& sp, int n, int t0, int t1, bool two,
+                                          const signed char* cd0, const signed char* cd1, float (&e0)[Q], float (&e1)[Q]) {
+  if (!two) { t1 = t0; cd1 = cd0; }
+  const int t[2] = {t0, t1};
+  const signed char* const cd[2] = {cd0, cd1};
+  float e[2][Q];
+  emit_n<FLOOR, 2>(a, sp, n, t, cd, e);
+#pragma unroll
+  for (int q = 0; q < Q; ++q) { e0[q] = e[0][q]; e1[q] = e[1][q]; }
+}
+
+// codes of positions [t_lo - 2, t_lo + npos + 2) -> codes[0 .. npos + 4); up to 4 positions per thread with all
+// loads in flight at once (npos <= G * MAX_L = 1536, blockDim >= 512 in the kernels that matter)
+__device__ __forceinline__ void codes_stage(const Args& a, signed char* codes, int n, int t_lo, int npos) {
+  const int nt = blockDim.x;
+  for (int base = threadIdx.x; base < npos + 4; base += 4 * nt) {
+    float4 u[4], v[4];
+    int t[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      t[k] = t_lo - 2 + base + k * nt;
+      if (base + k * nt < npos + 4 && t[k] >= 0 && t[k] < a.T) {
+        const float* p = a.inputs + ((size_t)n * a.T + t[k]) * SIN + 12;
+        u[k] = ldg4(p); v[k] = ldg4(p + 4);   // u.w = A flag, v = C,G,T,N flags
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = base + k * nt;
+      if (i < npos + 4) {
+        const int c = (t[k] >= 0 && t[k] < a.T) ? code_of(u[k].w, v[k].x, v[k].y, v[k].z, v[k].w) : nuc_code(a, n, t[k]);
+        codes[i] = (signed char)c;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ int divL(const Args& a, int i) { return (int)(((unsigned)i * a.mL) >> DIV_SHIFT); }
+__device__ __forceinline__ int tile_row_offset(const Args& a, int i, int CS) {
+  const int ci = divL(a, i);
+  return ci * CS + (i - ci * a.L) * QP;
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// K_A: chunk transfer matrices
+// matrix blocks
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) products_kernel(const Args a) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int G = blockDim.x >> 4, L = a.L;
-  const int CS = L * QP + 4;
-  EmisParams& sp = *reinterpret_cast<EmisParams*>(smem);
-  float4* Ps = reinterpret_cast<float4*>(smem + sizeof(EmisParams));
-  float* Es = reinterpret_cast<float*>(Ps + G * (L + 4));
-  const int n = blockIdx.y, m = n / a.batch, c_base = blockIdx.x * G;
-  load_emis_params(sp, a.Bfull + (size_t)m * Q * Q, a.codon);
-  __syncthreads();
-  emission_stage<true>(a, sp, Ps, Es, n, c_base, G, CS);
 
-  const int ci = threadIdx.x >> 4, row = threadIdx.x & 15, c = c_base + ci;
-  const bool valid = (row < Q) && (c < a.C);
-  float av[Q];
-  float ls = 0.f;
-  if (valid) {
-    float w[NEDGE];
-    load_edges(a.A + (size_t)m * Q * Q, w);
-    const int len = min(L, a.T - c * L);
-    const float* Ep = Es + ci * CS;
+// Row 15 of a block whose rows 0-14 hold [M-hat | s'] (row stride QP); one half warp, lane hl.
+__device__ __forceinline__ void finish_block(float* blk, int hl, float sp /* s'[hl], 0 for hl = 15 */, int E) {
+  const int col = min(hl, Q - 1);
+  float cs = 0.f;
 #pragma unroll
-    for (int j = 0; j < Q; ++j) av[j] = (j == row) ? 1.f : 0.f;
-    for (int u = 0; u < len; ++u) {
-      float R[Q];
-      if (c == 0 && u == 0) {
+  for (int i = 0; i < Q; ++i) cs = fmaf(__shfl_sync(0xffffffffu, sp, i, 16), blk[i * QP + col], cs);
+  blk[15 * QP + hl] = (hl < Q) ? cs : __int_as_float(E);
+}
+
+// strip (row r, columns 4 jq .. 4 jq + 3) of C' = A-hat . diag(s'_B) B-hat, normalised by the row sum; the last
+// strip's .w carries the un-normalised relative scale of the row, s'_A[r] * rowsum
+__device__ __forceinline__ void mm_strip(const float* __restrict__ Ab, const float* __restrict__ Bb, float* __restrict__ Cb, int r, int jq) {
+  float ar[QP];
+  load_row16(Ab + r * QP, ar);   // ar[15] = s'_A[r]
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float rs = 0.f;
 #pragma unroll
-        for (int j = 0; j < Q; ++j) R[j] = av[j];  // init step: no transition (MsaHmmCell.py:77-78)
+  for (int k = 0; k < Q; ++k) {
+    const float4 b = *reinterpret_cast<const float4*>(Bb + k * QP + 4 * jq);
+    const float ak = ar[k] * Bb[k * QP + 15];
+    rs += ak;
+    acc.x = fmaf(ak, b.x, acc.x); acc.y = fmaf(ak, b.y, acc.y); acc.z = fmaf(ak, b.z, acc.z); acc.w = fmaf(ak, b.w, acc.w);
+  }
+  const float inv = __frcp_rn(fmaxf(rs, 1e-37f));
+  float4 o = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+  if (jq == 3) o.w = ar[15] * rs;
+  *reinterpret_cast<float4*>(Cb + r * QP + 4 * jq) = o;
+}
+
+// second half of a product, by one half warp (all 32 lanes of the warp must call): common power of two out of
+// the row scales, column sums, exponent.  `write` = false computes but stores nothing.
+__device__ __forceinline__ void mm_finish(const float* __restrict__ Ab, const float* __restrict__ Bb, float* __restrict__ Cb, int hl, bool write) {
+  const float t = (hl < Q) ? Cb[hl * QP + 15] : 0.f;
+  const int emax = half_max_int((hl < Q && t > 0.f) ? fexp(t) : -100000);
+  const int e = emax == -100000 ? 0 : emax;
+  const float sp = t * pow2neg(e);
+  const int E = __float_as_int(Ab[255]) + __float_as_int(Bb[255]) + clamp_exp(e);
+  const int col = min(hl, Q - 1);
+  float cs = 0.f;
+#pragma unroll
+  for (int i = 0; i < Q; ++i) cs = fmaf(__shfl_sync(0xffffffffu, sp, i, 16), Cb[i * QP + col], cs);
+  __syncwarp();
+  if (write) {
+    if (hl < Q) Cb[hl * QP + 15] = sp;
+    Cb[15 * QP + hl] = (hl < Q) ? cs : __int_as_float(E);
+  }
+}
+
+// One level of the product tree: dst[pr] = src[2 pr] . src[2 pr + 1] for pr < np, all threads of the CTA.
+// Ends with a barrier.
+__device__ __forceinline__ void tree_level(const float* __restrict__ src, float* __restrict__ dst, int np) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int item = tid; item < np * 64; item += nt) {
+    const int pr = item >> 6, r = (item >> 2) & 15, jq = item & 3;
+    if (r < Q) mm_strip(src + (2 * pr) * MAT, src + (2 * pr + 1) * MAT, dst + pr * MAT, r, jq);
+  }
+  __syncthreads();
+  const int hw = tid >> 4, hl = tid & 15, nhw = nt >> 4;
+  for (int base = (hw & ~1); base < np; base += nhw) {
+    const int pr = base + (hw & 1);
+    const bool valid = pr < np;
+    const int prc = valid ? pr : np - 1;
+    mm_finish(src + (2 * prc) * MAT, src + (2 * prc + 1) * MAT, dst + prc * MAT, hl, valid);
+  }
+  __syncthreads();
+}
+
+// Boundary vectors during scans: lane hl of a half warp holds v[hl]; e = power-of-two exponent (replicated):
+// true vector = v * 2^e.
+struct HV {
+  float v;
+  int e;
+};
+
+// One scan step for both half warps of a warp at once (no divergence: the shuffles are warp-wide).
+//   bwd == 0 (row vector):    v <- v . M;   bwd == 1 (column vector):  r <- M . r,   M = 2^E diag(s') M-hat.
+// blk: staged block (row stride BST).  ones: 16 floats of 1.0 in shared memory.
+// `commit` == false leaves h untouched (the two half warps may need different trip counts).
+__device__ __forceinline__ void matvec(const float* __restrict__ blk, const float* __restrict__ ones, int hl, int bwd,
+                                       bool commit, HV& h) {
+  const int row = min(hl, Q - 1);
+  const float sp = blk[row * BST + 15];
+  const int Eb = __float_as_int(blk[15 * BST + 15]);
+  const float u = (hl < Q) ? (bwd ? h.v : h.v * sp) : 0.f;
+  const float* mp = blk + (bwd ? row * BST : row);
+  const int st = bwd ? 1 : BST;
+  const float* dp = bwd ? blk + 15 * BST : ones;
+  float acc0 = 0.f, acc1 = 0.f, s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < Q; ++k) {
+    const float uk = __shfl_sync(0xffffffffu, u, k, 16);
+    const float c = mp[k * st];
+    const float d = dp[k];
+    if (k & 1) { acc1 = fmaf(uk, c, acc1); s1 = fmaf(uk, d, s1); } else { acc0 = fmaf(uk, c, acc0); s0 = fmaf(uk, d, s0); }
+  }
+  const int ex = pexp(s0 + s1);
+  const float out = (bwd ? sp : 1.f) * (acc0 + acc1) * pow2neg(ex);
+  if (commit) {
+    h.v = (hl < Q) ? out : 0.f;
+    h.e += clamp_exp(ex) + Eb;
+  }
+}
+
+// stage nblk stored blocks (row stride QP, global) into shared memory with row stride BST, asynchronously
+__device__ __forceinline__ void stage_blocks_async(float* dst, const float* __restrict__ src, int nblk) {
+  for (int i = threadIdx.x; i < nblk * (MAT / 4); i += blockDim.x) {
+    const int b = i >> 6, r = (i >> 2) & 15, c = i & 3;
+    cp_async16(dst + b * BSZ + r * BST + 4 * c, src + 4 * i);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K1: chunk transfer matrices, group and tile products
+// ------------------------------------------------------------------------------------------------------------
+struct K1Smem {
+  EmisSmem sp;
+  float Aw[24];        // [0..6] A[src1(j)][j], [7..14] A[pred p][p], [15..22] A[p][succ p]
+  float EF[G][QP];     // emission at every chunk's first transition step
+  float EL[G][QP];     // emission at every chunk's last position
+  float carry[8];      // pass-state emissions of the last position of the previous emission round
+};
+
+__host__ __device__ inline size_t k1_union_bytes(int L) {
+  const size_t es = (size_t)G * (L * QP + 4) * sizeof(float);
+  const size_t tree = (size_t)HEAP * MAT * sizeof(float);
+  return es > tree ? es : tree;
+}
+__host__ __device__ inline size_t k1_smem_bytes(int L) {
+  return ((sizeof(K1Smem) + 15) / 16) * 16 + k1_union_bytes(L) + (((size_t)G * L + 4 + 15) / 16) * 16;
+}
+
+__global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(const Args a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  K1Smem& S = *reinterpret_cast<K1Smem*>(smem);
+  float* U = reinterpret_cast<float*>(smem + ((sizeof(K1Smem) + 15) / 16) * 16);
+  signed char* codes = reinterpret_cast<signed char*>(U) + k1_union_bytes(a.L);
+  const int L = a.L, T = a.T, CS = L * QP + 4;
+  const int tid = threadIdx.x;
+  const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
+  const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
+  const bool seq_start = (a.seq_off == 0);  // chunk 0 of this shard is the start of the whole sequence
+  const float* Am = a.A + (size_t)m * Q * Q;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  HMM_MARK(cta, 0);
+
+  if (tid < 7) S.Aw[tid] = __ldg(Am + SRC1[tid] * Q + tid);
+  else if (tid < 15) S.Aw[tid] = __ldg(Am + PRED[tid - 7] * Q + tid);
+  else if (tid < 23) S.Aw[tid] = __ldg(Am + (tid - 8) * Q + SUCC[tid - 15]);
+  codes_stage(a, codes, n, t_lo, npos);
+  HMM_MARK(cta, 7);
+  load_emis_params(S.sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
+  HMM_MARK(cta, 8);
+  __syncthreads();
+  HMM_MARK(cta, 1);
+
+  // ---- emission + per-position coefficients of the two-step recurrence ----
+  // slots 0-6: k1[j] = E_t[j] A[src1(j)][j];  slots 7-14: k2[p] = E_t[succ p] A[p][succ p] * E_{t-1}[p] A[pred p][p].
+  // Every chunk's first transition step uses the full 23-edge form, so k2 is never read at a chunk's first
+  // position and no emission from outside the tile is needed.  E_{t-1}[pass] travels through slots 8-15 of row t-1.
+  for (int ib = 0; ib < npos; ib += K1_NP * K1_THREADS) {   // uniform trip count: the body holds barriers
+    const int i0 = ib + tid, i1 = i0 + K1_THREADS;
+    const bool one = i0 < npos, two = (K1_NP == 2) && i1 < npos;
+    float e0[Q], e1[Q];
+    float* r0 = U;
+    float* r1 = U;
+    int ci0 = 0, ci1 = 0;
+    if (one) {
+      if (K1_NP == 2) {
+        emit_pair<true>(a, S.sp, n, t_lo + i0, t_lo + i1, two, codes + 2 + i0, codes + 2 + i1, e0, e1);
       } else {
-        vec_A(av, w, R);
+        const int t[1] = {t_lo + i0};
+        const signed char* const cd[1] = {codes + 2 + i0};
+        float e[1][Q];
+        emit_n<true, 1>(a, S.sp, n, t, cd, e);
+#pragma unroll
+        for (int q = 0; q < Q; ++q) { e0[q] = e[0][q]; e1[q] = 0.f; }
       }
-      ls += logf(scaled_step(Ep + u * QP, R, av));
-    }
-  }
-  const float g = half_max(valid ? ls : -INFINITY);
-  if (c < a.C) {
-    float* dst = a.Mn + ((size_t)n * a.C + c) * MAT + row * QP;
-    if (row < Q) {
-      const float sc = expf(ls - g);
-#pragma unroll
-      for (int j = 0; j < Q; ++j) av[j] *= sc;
-      store_row16(dst, av, 0.f);
-      if (row == 0) a.gsc[(size_t)n * a.C + c] = g;
-    } else {
-      float4* d4 = reinterpret_cast<float4*>(dst);
-      d4[0] = d4[1] = d4[2] = d4[3] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-  }
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// K_B: boundary scan over the chunk matrices of one sequence
-// ------------------------------------------------------------------------------------------------------------
-constexpr int SCAN_WARPS = 16;
-
-// v'_l = sum_k v_k * coef[k]; lanes of a half warp hold v; returns the un-normalised result
-__device__ __forceinline__ float half_matvec(float v, const float (&coef)[Q]) {
-  float acc = 0.f;
-#pragma unroll
-  for (int k = 0; k < Q; ++k) acc = fmaf(__shfl_sync(0xffffffffu, v, k, 16), coef[k], acc);
-  return acc;
-}
-
-__global__ void __launch_bounds__(SCAN_WARPS * 32) scan_kernel(const Args a) {
-  __shared__ __align__(16) float Xs[SCAN_WARPS][QP][QP];
-  __shared__ float Pg[SCAN_WARPS];
-  __shared__ float fseg[SCAN_WARPS + 1][QP], rseg[SCAN_WARPS][QP];
-  __shared__ double fcs[SCAN_WARPS + 1], rcs[SCAN_WARPS];
-  const int n = blockIdx.x, m = n / a.batch, C = a.C;
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, hl = lane & 15, hi = lane >> 4;
-  const int SL = (C + SCAN_WARPS - 1) / SCAN_WARPS;
-  const int c_lo = min(C, w * SL), c_hi = min(C, c_lo + SL);
-  const float* Mb = a.Mn + (size_t)n * C * MAT;
-  const float* gb = a.gsc + (size_t)n * C;
-
-  // phase 1: ordered product of the segment's matrices, X <- X . M_c, rescaled by its largest entry
-  {
-    float(*X)[QP] = Xs[w];
-    for (int i = lane; i < MAT; i += 32) X[i >> 4][i & 15] = ((i >> 4) == (i & 15)) ? 1.f : 0.f;
-    __syncwarp();
-    float gs = 0.f;
-    for (int c = c_lo; c < c_hi; ++c) {
-      float col[Q];
-#pragma unroll
-      for (int k = 0; k < Q; ++k) col[k] = __ldg(Mb + (size_t)c * MAT + k * QP + hl);
-      float acc[8];
-      float mx = 0.f;
-#pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        float x[QP];
-        load_row16(&X[hi * 8 + r][0], x);
-        float s = 0.f;
-#pragma unroll
-        for (int k = 0; k < Q; ++k) s = fmaf(x[k], col[k], s);
-        acc[r] = s;
-        mx = fmaxf(mx, s);
-      }
-      mx = fmaxf(warp_max(mx), 1e-37f);
-      const float inv = __frcp_rn(mx);
-      __syncwarp();
-#pragma unroll
-      for (int r = 0; r < 8; ++r) X[hi * 8 + r][hl] = (hl < Q && hi * 8 + r < Q) ? acc[r] * inv : 0.f;
-      __syncwarp();
-      gs += __ldg(gb + c) + logf(mx);
-    }
-    if (lane == 0) Pg[w] = gs;
-  }
-  __syncthreads();
-
-  // phase 2: warp 0 scans the segment products; lanes 0-15 forward (row vector), lanes 16-31 backward (column)
-  if (w == 0) {
-    float v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + m * Q + hl) : 1.f) : 0.f;
-    double cs = 0.0;
-    for (int it = 0; it < SCAN_WARPS; ++it) {
-      const int s = hi == 0 ? it : SCAN_WARPS - 1 - it;
-      if (hi == 0) { fseg[s][hl] = v; if (hl == 0) fcs[s] = cs; }
-      else         { rseg[s][hl] = v; if (hl == 0) rcs[s] = cs; }
-      float coef[Q];
-#pragma unroll
-      for (int k = 0; k < Q; ++k) coef[k] = hi == 0 ? Xs[s][k][hl] : Xs[s][hl][k];
-      float nv = half_matvec(v, coef);
-      const float S = fmaxf(half_sum(nv), 1e-37f);
-      v = nv * __frcp_rn(S);
-      cs += (double)Pg[s] + (double)logf(S);
-    }
-    if (hi == 0) { fseg[SCAN_WARPS][hl] = v; if (hl == 0) fcs[SCAN_WARPS] = cs; }
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const float ll = (float)fcs[SCAN_WARPS];
-    a.llws[n] = ll;
-    if (a.loglik) a.loglik[n] = ll;
-  }
-
-  // phase 3: every warp replays its segment from the segment boundary, emitting per-chunk boundary vectors
-  {
-    float v = hi == 0 ? fseg[w][hl] : rseg[w][hl];
-    double cs = hi == 0 ? fcs[w] : rcs[w];
-    float* vout = (hi == 0 ? a.fvec : a.rvec) + (size_t)n * C * QP;
-    float* cout = (hi == 0 ? a.fcum : a.rcum) + (size_t)n * C;
-    for (int it = 0; it < c_hi - c_lo; ++it) {
-      const int c = hi == 0 ? c_lo + it : c_hi - 1 - it;
-      vout[(size_t)c * QP + hl] = v;
-      if (hl == 0) cout[c] = (float)cs;
-      float coef[Q];
-      const float* Mc = Mb + (size_t)c * MAT;
-#pragma unroll
-      for (int k = 0; k < Q; ++k) coef[k] = hi == 0 ? __ldg(Mc + k * QP + hl) : __ldg(Mc + hl * QP + k);
-      float nv = half_matvec(v, coef);
-      const float S = fmaxf(half_sum(nv), 1e-37f);
-      v = nv * __frcp_rn(S);
-      cs += (double)__ldg(gb + c) + (double)logf(S);
-    }
-  }
-}
-
-// ------------------------------------------------------------------------------------------------------------
-// K_C: exact in-chunk recursions from the boundary vectors + outputs
-// ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) finalize_kernel(const Args a) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int G = a.GC, L = a.L, T = a.T, C = a.C;
-  const int CS = L * QP + 4;
-  EmisParams& sp = *reinterpret_cast<EmisParams*>(smem);
-  float4* Ps = reinterpret_cast<float4*>(smem + sizeof(EmisParams));
-  float* Es = reinterpret_cast<float*>(Ps + G * (L + 4));
-  float* Fa = Es + G * CS;
-  float* Rb = Fa + G * CS;
-  const int n = blockIdx.y, m = n / a.batch, c_base = blockIdx.x * G;
-  const bool want_f = a.out_post || a.out_alpha, want_b = a.out_post || a.out_beta;
-  load_emis_params(sp, a.Bfull + (size_t)m * Q * Q, a.codon);
-  __syncthreads();
-  emission_stage<true>(a, sp, Ps, Es, n, c_base, G, CS);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp < 2 && lane < G && c_base + lane < C) {
-    const int c = c_base + lane, t0 = c * L, len = min(L, T - t0);
-    const float* Ep = Es + lane * CS;
-    float w[NEDGE];
-    load_edges(a.A + (size_t)m * Q * Q, w);
-    float bv[QP];
-    if (warp == 0 && want_f) {
-      // forward: alpha-hat_t, MsaHmmCell.py:73-106 with reverse == False
-      load_row16((a.fvec + ((size_t)n * C + c) * QP), bv);
-      float av[Q], R[Q];
-#pragma unroll
-      for (int j = 0; j < Q; ++j) av[j] = bv[j];
-      float* out = Fa + lane * CS;
-      for (int u = 0; u < len; ++u) {
-        if (c == 0 && u == 0) {
-#pragma unroll
-          for (int j = 0; j < Q; ++j) R[j] = av[j];
-        } else {
-          vec_A(av, w, R);
-        }
-        const float S = scaled_step(Ep + u * QP, R, av);
-        store_row16(out + u * QP, av, S);
-      }
-    } else if (warp == 1 && want_b) {
-      // backward: R_t = beta_t before the emission at t, MsaHmmCell.py:96-100 with reverse == True
-      load_row16((a.rvec + ((size_t)n * C + c) * QP), bv);
-      float R[Q], b[Q];
-#pragma unroll
-      for (int j = 0; j < Q; ++j) R[j] = bv[j];
-      float* out = Rb + lane * CS;
-      for (int u = len - 1; u >= 0; --u) {
-        float Rf[Q];
-#pragma unroll
-        for (int j = 0; j < Q; ++j) Rf[j] = fmaxf(R[j], kEps);
-        const float S = scaled_step(Ep + u * QP, Rf, b);
-        store_row16(out + u * QP, Rf, S);
-        A_vec(b, w, R);
-      }
-    }
-  }
-  __syncthreads();
-
-  // running log scales for log alpha / log beta (slot 15 of each row: S_t -> cumulative log scale)
-  if (a.out_alpha || a.out_beta) {
-    const int ci = threadIdx.x >> 1, dir = threadIdx.x & 1;
-    if (ci < G && c_base + ci < C) {
-      const int c = c_base + ci, len = min(L, T - c * L);
-      if (dir == 0 && a.out_alpha) {
-        double cs = (double)a.fcum[(size_t)n * C + c];
-        float* p = Fa + ci * CS + 15;
-        for (int u = 0; u < len; ++u) { cs += (double)logf(p[u * QP]); p[u * QP] = (float)cs; }
-      } else if (dir == 1 && a.out_beta) {
-        double cs = (double)a.rcum[(size_t)n * C + c];
-        float* p = Rb + ci * CS + 15;
-        for (int u = len - 1; u >= 0; --u) { const float S = p[u * QP]; p[u * QP] = (float)cs; cs += (double)logf(S); }
+      ci0 = divL(a, i0);
+      r0 = U + ci0 * CS + (i0 - ci0 * L) * QP;
+      reinterpret_cast<float4*>(r0)[2] = make_float4(e0[7], e0[8], e0[9], e0[10]);
+      reinterpret_cast<float4*>(r0)[3] = make_float4(e0[11], e0[12], e0[13], e0[14]);
+      if (two) {
+        ci1 = divL(a, i1);
+        r1 = U + ci1 * CS + (i1 - ci1 * L) * QP;
+        reinterpret_cast<float4*>(r1)[2] = make_float4(e1[7], e1[8], e1[9], e1[10]);
+        reinterpret_cast<float4*>(r1)[3] = make_float4(e1[11], e1[12], e1[13], e1[14]);
       }
     }
     __syncthreads();
+    float ep0[8], ep1[8];
+    if (one) {
+      const float* q0 = (i0 == 0) ? r0 + 8 : (tid == 0) ? S.carry : U + tile_row_offset(a, i0 - 1, CS) + 8;
+      const float* q1 = two ? U + tile_row_offset(a, i1 - 1, CS) + 8 : q0;
+      const float4 u0 = reinterpret_cast<const float4*>(q0)[0], u1 = reinterpret_cast<const float4*>(q0)[1];
+      const float4 v0 = reinterpret_cast<const float4*>(q1)[0], v1 = reinterpret_cast<const float4*>(q1)[1];
+      ep0[0] = u0.x; ep0[1] = u0.y; ep0[2] = u0.z; ep0[3] = u0.w; ep0[4] = u1.x; ep0[5] = u1.y; ep0[6] = u1.z; ep0[7] = u1.w;
+      ep1[0] = v0.x; ep1[1] = v0.y; ep1[2] = v0.z; ep1[3] = v0.w; ep1[4] = v1.x; ep1[5] = v1.y; ep1[6] = v1.z; ep1[7] = v1.w;
+    }
+    __syncthreads();
+    if (one) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (h == 1 && !two) break;
+        const int i = h ? i1 : i0, ci = h ? ci1 : ci0, t = t_lo + i, c = c0 + ci;
+        const float (&e)[Q] = h ? e1 : e0;
+        const float (&ep)[8] = h ? ep1 : ep0;
+        float* rowp = h ? r1 : r0;
+        const int ts = c * L + ((c == 0 && seq_start) ? 1 : 0);
+        const int t1 = min(T, (c + 1) * L) - 1;
+        if (t == ts) store_row16(S.EF[ci], e, 0.f);
+        if (t == t1) store_row16(S.EL[ci], e, 0.f);
+        if (h == K1_NP - 1 && tid == K1_THREADS - 1) {
+#pragma unroll
+          for (int q = 0; q < 8; ++q) S.carry[q] = e[7 + q];
+        }
+        if (t == 0 && seq_start) {
+          store_row16(rowp, e, 0.f);   // position 0 keeps its emission row (no transition into it)
+        } else {
+          float kc[Q];
+#pragma unroll
+          for (int j = 0; j < 7; ++j) kc[j] = e[j] * S.Aw[j];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) kc[7 + q] = (e[SUCC[q]] * S.Aw[15 + q]) * (ep[q] * S.Aw[7 + q]);
+          store_row16(rowp, kc, 0.f);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  HMM_MARK(cta, 2);
+
+  // ---- conditional rows: thread = (chunk, row) ----
+  const int ci = tid >> 4, row = tid & 15, c = c0 + ci;
+  float vec[Q];
+  float sm = 1.f;
+  int esum = 0;
+#pragma unroll
+  for (int j = 0; j < Q; ++j) vec[j] = (j == row) ? 1.f : 0.f;   // chunks beyond the sequence: identity
+  if (c < a.C && row < Q) {
+    const bool first = (c == 0 && seq_start);
+    const int t0 = c * L, t1 = min(T, t0 + L) - 1, ts = t0 + (first ? 1 : 0);
+    const float* Kp = U + ci * CS;
+    const float init = first ? Kp[row] : 1.f;   // E_0[row]
+    float xm[7], ym[8];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) xm[j] = (row == j) ? init : 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) ym[q] = (row == 7 + q) ? init : 0.f;
+    if (ts > t1) {
+#pragma unroll
+      for (int j = 0; j < 7; ++j) vec[j] = xm[j];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) vec[7 + q] = ym[q];
+    } else {
+      float x[7], xp[7];
+      {
+        float k1[QP];
+        load_row16(Kp + (ts - t0) * QP, k1);
+#pragma unroll
+        for (int j = 0; j < 7; ++j) x[j] = k1[j] * xm[SRC1[j]];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) x[SUCC[q]] = fmaf(S.EF[ci][SUCC[q]] * S.Aw[15 + q], ym[q], x[SUCC[q]]);
+#pragma unroll
+        for (int j = 0; j < 7; ++j) xp[j] = xm[j];
+      }
+      int cnt = 0;
+#pragma unroll 4
+      for (int t = ts + 1; t <= t1; ++t) {
+        float k[QP];
+        load_row16(Kp + (t - t0) * QP, k);
+        float xn[7];
+        xn[0] = fmaf(k[7 + 7], xp[5], k[0] * x[0]);
+        xn[1] = fmaf(k[7 + 1], xp[4], k[1] * x[1]);
+        xn[2] = fmaf(k[7 + 2], xp[5], k[2] * x[2]);
+        xn[3] = fmaf(k[7 + 3], xp[6], k[3] * x[3]);
+        xn[4] = fmaf(k[7 + 4], xp[1], k[4] * x[6]);
+        xn[5] = fmaf(k[7 + 5], xp[2], fmaf(k[7 + 0], xp[0], k[5] * x[4]));
+        xn[6] = fmaf(k[7 + 6], xp[3], k[6] * x[5]);
+#pragma unroll
+        for (int j = 0; j < 7; ++j) { xp[j] = x[j]; x[j] = xn[j]; }
+        if ((++cnt & 3) == 0) {
+          const float s = sum7(x) + sum7(xp);
+          const int ex = pexp(s);
+          const float sc = pow2neg(ex);
+#pragma unroll
+          for (int j = 0; j < 7; ++j) { x[j] *= sc; xp[j] *= sc; }
+          esum += clamp_exp(ex);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 7; ++j) vec[j] = x[j];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) vec[7 + q] = (S.EL[ci][7 + q] * S.Aw[7 + q]) * xp[PRED[q]];
+    }
+    sm = fmaxf(sum15(vec), 1e-37f);
+    const float inv = __frcp_rn(sm);
+#pragma unroll
+    for (int j = 0; j < Q; ++j) vec[j] *= inv;
+  }
+  // relative row scales: common power of two = the largest row exponent of the chunk
+  const int erow = (row < Q) ? esum + fexp(sm) : -100000;
+  const int emax = half_max_int(erow);
+  const float sprime = (row < Q) ? sm * pow2neg(emax - esum) : 0.f;
+  __syncthreads();   // every row is done with the coefficient rows: U becomes the block / tree scratch
+  HMM_MARK(cta, 3);
+
+  float* H = U;   // product tree in heap order: chunk blocks at [G, 2G), node k = node 2k . node 2k+1, root at 1
+  {
+    float* b = H + (G + ci) * MAT;
+    if (row < Q) store_row16(b + row * QP, vec, sprime);
+    __syncwarp();
+    finish_block(b, row, sprime, emax);
+  }
+  __syncthreads();
+  HMM_MARK(cta, 4);
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level(H + 2 * np * MAT, H + np * MAT, np);
+  HMM_MARK(cta, 5);
+
+  // coalesced stores of the tree (nodes 1 .. 2G-1) and of the tile matrix
+  {
+    const size_t tile = (size_t)n * a.P + p;
+    float4* dh = reinterpret_cast<float4*>(a.Mh + tile * HEAP * MAT);
+    const float4* sh = reinterpret_cast<const float4*>(H);
+    for (int i = MAT / 4 + tid; i < HEAP * MAT / 4; i += K1_THREADS) dh[i] = sh[i];
+    float4* dt = reinterpret_cast<float4*>(a.Mt + tile * MAT);
+    if (tid < MAT / 4) dt[tid] = sh[MAT / 4 + tid];
+  }
+  HMM_MARK(cta, 6);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K_B: boundary vectors over the tile matrices of one sequence (long sequences / log-likelihood only / sharding)
+// ------------------------------------------------------------------------------------------------------------
+constexpr int KB_WARPS = 16;
+
+struct KBSmem {
+  float seg[2][KB_WARPS][MAT];   // segment products (ping-pong for the in-warp chain), row stride QP
+  float st[KB_WARPS][2][BSZ];    // per half warp staging of one block (row stride BST)
+  float fseg[KB_WARPS + 1][QP], rseg[KB_WARPS][QP];
+  int fse[KB_WARPS + 1], rse[KB_WARPS];
+  int which[KB_WARPS];
+  float ones[QP];
+};
+
+// C = A . B by one warp (blocks with row stride QP in shared memory)
+__device__ __forceinline__ void warp_block_mm(const float* __restrict__ Ab, const float* __restrict__ Bb, float* __restrict__ Cb, int lane) {
+  for (int item = lane; item < 64; item += 32) {
+    const int r = item >> 2, jq = item & 3;
+    if (r < Q) mm_strip(Ab, Bb, Cb, r, jq);
+  }
+  __syncwarp();
+  mm_finish(Ab, Bb, Cb, lane & 15, lane < 16);   // both half warps hold identical values; one writes
+  __syncwarp();
+}
+
+__device__ __forceinline__ void identity_block(float* blk, int lane) {
+  for (int i = lane; i < MAT; i += 32) {
+    const int r = i >> 4, c = i & 15;
+    float v;
+    if (r < Q) v = (c == r || c == 15) ? 1.f : 0.f;          // e_r | s' = 1
+    else v = (c < Q) ? 1.f : __int_as_float(0);              // column sums 1 | E = 0
+    blk[i] = v;
+  }
+}
+
+// copy one stored block (global, stride QP) into a staged block (shared, stride BST) by one half warp
+__device__ __forceinline__ void hw_stage_block(float* dst, const float* __restrict__ src, int hl) {
+#pragma unroll
+  for (int r = 0; r < QP; ++r) dst[r * BST + hl] = __ldg(src + r * QP + hl);
+}
+
+// mode 0: full scan (writes bvf/bvr for every tile and the log-likelihood)
+// mode 1: reduce only: the ordered product of all tile matrices of the sequence -> total_out[n] (multi-GPU exchange)
+__global__ void __launch_bounds__(KB_WARPS * 32) boundary_kernel(const Args a, int mode, float* __restrict__ total_out) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  KBSmem& S = *reinterpret_cast<KBSmem*>(smem);
+  const int n = blockIdx.x, m = n / a.batch, P = a.P;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, hl = lane & 15, hi = lane >> 4;
+  const int SL = (P + KB_WARPS - 1) / KB_WARPS;
+  const int s_lo = min(P, w * SL), s_hi = min(P, s_lo + SL);
+  const float* Mt = a.Mt + (size_t)n * P * MAT;
+  if (threadIdx.x < QP) S.ones[threadIdx.x] = 1.f;
+
+  // phase 1: ordered product of the segment's tile matrices
+  {
+    int cur = 0;
+    float* acc = S.seg[0][w];
+    if (s_lo < s_hi) {
+      for (int i = lane; i < MAT / 4; i += 32) reinterpret_cast<float4*>(acc)[i] = __ldg(reinterpret_cast<const float4*>(Mt + (size_t)s_lo * MAT) + i);
+    } else {
+      identity_block(acc, lane);
+    }
+    __syncwarp();
+    float* stg = &S.st[w][0][0];   // 2*BSZ floats >= MAT: scratch for the right operand (16-byte aligned)
+    for (int s = s_lo + 1; s < s_hi; ++s) {
+      for (int i = lane; i < MAT / 4; i += 32) reinterpret_cast<float4*>(stg)[i] = __ldg(reinterpret_cast<const float4*>(Mt + (size_t)s * MAT) + i);
+      __syncwarp();
+      warp_block_mm(S.seg[cur][w], stg, S.seg[cur ^ 1][w], lane);
+      cur ^= 1;
+    }
+    if (lane == 0) S.which[w] = cur;
+  }
+  __syncthreads();
+
+  if (mode == 1) {
+    if (w == 0) {
+      float* accA = &S.st[0][0][0];
+      float* accB = &S.st[1][0][0];
+      for (int i = lane; i < MAT; i += 32) accA[i] = S.seg[S.which[0]][0][i];
+      __syncwarp();
+      for (int s = 1; s < KB_WARPS; ++s) {
+        warp_block_mm(accA, S.seg[S.which[s]][s], accB, lane);
+        float* t = accA; accA = accB; accB = t;
+      }
+      for (int i = lane; i < MAT / 4; i += 32) reinterpret_cast<float4*>(total_out + (size_t)n * MAT)[i] = reinterpret_cast<const float4*>(accA)[i];
+    }
+    return;
   }
 
-  // posterior normaliser per position: log sum_q alpha-hat * R-hat, kept in Es[.][0]
-  if (a.out_post) {
-    const float shift = (a.flags & HMM_B200_NO_LOGLIK) ? a.llws[n] : 0.f;
-    for (int i = threadIdx.x; i < G * L; i += blockDim.x) {
-      const int ci = i / L, u = i - ci * L, c = c_base + ci;
-      if (c < C && c * L + u < T) {
+  // phase 2: warp 0 scans the segment products; lanes 0-15 forward, lanes 16-31 backward
+  if (w == 0) {
+    HV h;
+    const float* inb = hi == 0 ? a.in_f : a.in_r;
+    if (inb) {
+      h.v = (hl < Q) ? __ldg(inb + (size_t)n * QP + hl) : 0.f;
+      h.e = __float_as_int(__ldg(inb + (size_t)n * QP + 15));
+    } else {
+      h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + m * Q + hl) : 1.f) : 0.f;
+      h.e = 0;
+    }
+    float* stg = S.st[0][hi];
+    for (int it = 0; it < KB_WARPS; ++it) {
+      const int s = hi == 0 ? it : KB_WARPS - 1 - it;
+      if (hi == 0) { S.fseg[s][hl] = h.v; if (hl == 0) S.fse[s] = h.e; }
+      else         { S.rseg[s][hl] = h.v; if (hl == 0) S.rse[s] = h.e; }
+      const float* sb = S.seg[S.which[s]][s];
+#pragma unroll
+      for (int r = 0; r < QP; ++r) stg[r * BST + hl] = sb[r * QP + hl];
+      __syncwarp();
+      matvec(stg, S.ones, hl, hi, true, h);
+      __syncwarp();
+    }
+    const float tot = half_sum(h.v);
+    if (lane == 0) {
+      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+      a.llws[n] = ll;
+      if (a.loglik) a.loglik[n] = ll;
+    }
+  }
+  __syncthreads();
+
+  // phase 3: every warp replays its segment, emitting the boundary vector of every tile
+  {
+    HV h;
+    h.v = hi == 0 ? S.fseg[w][hl] : S.rseg[w][hl];
+    h.e = hi == 0 ? S.fse[w] : S.rse[w];
+    float* vout = (hi == 0 ? a.bvf : a.bvr) + (size_t)n * P * QP;
+    float* stg = S.st[w][hi];
+    for (int it = 0; it < s_hi - s_lo; ++it) {
+      const int s = hi == 0 ? s_lo + it : s_hi - 1 - it;
+      vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+      hw_stage_block(stg, Mt + (size_t)s * MAT, hl);
+      __syncwarp();
+      matvec(stg, S.ones, hl, hi, true, h);
+      __syncwarp();
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K2: boundary vectors of every chunk, exact in-chunk recursions, outputs
+// ------------------------------------------------------------------------------------------------------------
+struct K2Smem {
+  EmisSmem sp;
+  float Aw[24];            // the 23 edge weights in the reference's kernel order
+  float ones[QP];
+  float hvf[HEAP][QP], hvr[HEAP][QP];   // forward vector entering / backward vector leaving every tree node
+  int hef[HEAP], her[HEAP];             // their power-of-two exponents
+  float ll;
+};
+
+__host__ __device__ inline size_t k2_blocks_bytes() { return (size_t)(MAX_INLINE_TILES + HEAP) * BSZ * sizeof(float); }
+__host__ __device__ inline size_t k2_y_bytes(int L, bool full) { return (size_t)(full ? 2 : 1) * G * (L * QP + 4) * sizeof(float); }
+__host__ __device__ inline size_t k2_union_bytes(int L, bool full) {
+  const size_t y = k2_y_bytes(L, full), b = k2_blocks_bytes();
+  return y > b ? y : b;
+}
+__host__ __device__ inline size_t k2_smem_bytes(int L, bool full) {
+  return ((sizeof(K2Smem) + 15) / 16) * 16 + (size_t)G * (L * QP + 4) * sizeof(float) + k2_union_bytes(L, full) +
+         (((size_t)G * L + 4 + 15) / 16) * 16;
+}
+
+__device__ __forceinline__ void load_edges(const float* Aw, float (&w)[NEDGE]) {
+#pragma unroll
+  for (int e = 0; e < NEDGE; ++e) w[e] = Aw[e];
+}
+// R = a . A   (forward, MsaHmmCell.py:80 with transitioner.reverse == False)
+__device__ __forceinline__ void vec_A(const float (&a)[Q], const float (&w)[NEDGE], float (&R)[Q]) {
+#pragma unroll
+  for (int j = 0; j < Q; ++j) R[j] = 0.f;
+#pragma unroll
+  for (int e = 0; e < NEDGE; ++e) R[EDST[e]] = fmaf(a[ESRC[e]], w[e], R[EDST[e]]);
+}
+// R = A . b   (backward: b . A^T, transitioner.reverse == True)
+__device__ __forceinline__ void A_vec(const float (&b)[Q], const float (&w)[NEDGE], float (&R)[Q]) {
+#pragma unroll
+  for (int i = 0; i < Q; ++i) R[i] = 0.f;
+#pragma unroll
+  for (int e = 0; e < NEDGE; ++e) R[ESRC[e]] = fmaf(w[e], b[EDST[e]], R[ESRC[e]]);
+}
+
+__device__ __forceinline__ void named_barrier_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+template <bool FULL>
+__global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  K2Smem& S = *reinterpret_cast<K2Smem*>(smem);
+  const int L = a.L, T = a.T, C = a.C, P = a.P, CS = L * QP + 4;
+  float* X = reinterpret_cast<float*>(smem + ((sizeof(K2Smem) + 15) / 16) * 16);   // G*CS emissions
+  float* U = X + (size_t)G * CS;                                                    // blocks, then Y (and Yr)
+  signed char* codes = reinterpret_cast<signed char*>(U) + k2_union_bytes(L, FULL);
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
+  const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
+  const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
+  const int nch = min(G, C - c0);                      // chunks in this tile
+  const bool seq_start = (a.seq_off == 0);
+  const size_t tile = (size_t)n * P + p;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x + gridDim.x * gridDim.y;
+  HMM_MARK(cta, 0);
+
+  // ---- warps 0-1 stage the matrices this tile needs (asynchronously) ----
+  float* Bt = U;                                   // tile blocks [P] (inline top-level scan only)
+  float* Bh = U + MAX_INLINE_TILES * BSZ;          // this tile's tree in heap order (nodes 2 .. 2G-1 staged)
+  constexpr int SCAN_THREADS = 64;
+  if (tid < SCAN_THREADS) {
+    for (int i = tid; i < (HEAP - 2) * (MAT / 4); i += SCAN_THREADS) {
+      const int b = i >> 6, r = (i >> 2) & 15, c = i & 3;
+      cp_async16(Bh + (2 + b) * BSZ + r * BST + 4 * c, a.Mh + (tile * HEAP + 2) * MAT + 4 * i);
+    }
+    if (a.top_inline) {
+      for (int i = tid; i < P * (MAT / 4); i += SCAN_THREADS) {
+        const int b = i >> 6, r = (i >> 2) & 15, c = i & 3;
+        cp_async16(Bt + b * BSZ + r * BST + 4 * c, a.Mt + (size_t)n * P * MAT + 4 * i);
+      }
+    }
+    cp_async_commit();
+  }
+  {
+    const float* Am = a.A + (size_t)m * Q * Q;
+    if (tid < NEDGE) S.Aw[tid] = __ldg(Am + ESRC[tid] * Q + EDST[tid]);
+    if (tid < QP) S.ones[tid] = 1.f;
+  }
+  codes_stage(a, codes, n, t_lo, npos);
+  load_emis_params(S.sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
+  __syncthreads();
+  HMM_MARK(cta, 1);
+
+  const bool need_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
+  if (tid >= SCAN_THREADS) {
+    // ---- emission: all warps but the two scan warps ----
+    const int et = tid - SCAN_THREADS, ent = nt - SCAN_THREADS;
+    for (int i0 = et; i0 < npos; i0 += 2 * ent) {
+      const int i1 = i0 + ent;
+      const bool two = i1 < npos;
+      float e0[Q], e1[Q];
+      emit_pair<true>(a, S.sp, n, t_lo + i0, t_lo + i1, two, codes + 2 + i0, codes + 2 + i1, e0, e1);
+      store_row16(X + tile_row_offset(a, i0, CS), e0, 0.f);
+      if (two) store_row16(X + tile_row_offset(a, i1, CS), e1, 0.f);
+    }
+  } else {
+    // ---- boundary vectors, concurrently with the emission: scan over the tile matrices (warp 0), then a
+    // down-sweep of the tile's tree (warps 0-1).  Lanes 0-15 of a warp run the forward direction, lanes 16-31 the
+    // backward direction, in one instruction stream.
+    cp_async_wait_all();
+    named_barrier_sync(2, SCAN_THREADS);
+    if (warp == 0) {
+      HV h;
+      if (a.top_inline) {
+        h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + m * Q + hl) : 1.f) : 0.f;
+        h.e = 0;
+        const int nf = p, nb = P - 1 - p, nmax = max(nf, nb);
+        for (int it = 0; it < nmax; ++it) {
+          const bool act = it < (hi == 0 ? nf : nb);
+          const int s = act ? (hi == 0 ? it : P - 1 - it) : p;
+          matvec(Bt + s * BSZ, S.ones, hl, hi, act, h);
+        }
+      } else {
+        const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
+        h.v = (hl < Q) ? __ldg(bv + hl) : 0.f;
+        h.e = __float_as_int(__ldg(bv + 15));
+      }
+      if (hi == 0) { S.hvf[1][hl] = h.v; if (hl == 0) S.hef[1] = h.e; }
+      else         { S.hvr[1][hl] = h.v; if (hl == 0) S.her[1] = h.e; }
+    }
+    named_barrier_sync(2, SCAN_THREADS);
+    // down-sweep: node k hands its forward vector to child 2k and (through child 2k's matrix) to child 2k+1;
+    // its backward vector to child 2k+1 and (through child 2k+1's matrix) to child 2k
+    for (int lo = 1; lo < G; lo <<= 1) {
+      for (int k = lo + warp; k < 2 * lo; k += SCAN_THREADS / 32) {
+        HV h;
+        h.v = hi == 0 ? S.hvf[k][hl] : S.hvr[k][hl];
+        h.e = hi == 0 ? S.hef[k] : S.her[k];
+        if (hi == 0) { S.hvf[2 * k][hl] = h.v; if (hl == 0) S.hef[2 * k] = h.e; }
+        else         { S.hvr[2 * k + 1][hl] = h.v; if (hl == 0) S.her[2 * k + 1] = h.e; }
+        matvec(Bh + (2 * k + hi) * BSZ, S.ones, hl, hi, true, h);
+        if (hi == 0) { S.hvf[2 * k + 1][hl] = h.v; if (hl == 0) S.hef[2 * k + 1] = h.e; }
+        else         { S.hvr[2 * k][hl] = h.v; if (hl == 0) S.her[2 * k] = h.e; }
+      }
+      named_barrier_sync(2, SCAN_THREADS);
+    }
+    // log-likelihood = scale of the forward vector after the last tile: produced by the last tile's CTA, and by
+    // every CTA when the caller wants the un-normalised posterior (NO_LOGLIK)
+    if (warp == 0) {
+      if (a.top_inline) {
+        if (p == P - 1 || need_ll) {
+          HV h;
+          h.v = S.hvf[1][hl];
+          h.e = S.hef[1];
+          for (int s = p; s < P; ++s) matvec(Bt + s * BSZ, S.ones, hl, 0, true, h);
+          const float tot = half_sum(h.v);
+          if (lane == 0) {
+            const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+            S.ll = ll;
+            if (p == P - 1) {
+              a.llws[n] = ll;
+              if (a.loglik) a.loglik[n] = ll;
+            }
+          }
+        }
+      } else if (lane == 0) {
+        S.ll = a.llws[n];
+      }
+    }
+  }
+  __syncthreads();   // emissions complete, boundary vectors complete, blocks dead: U becomes Y (and Yr)
+  HMM_MARK(cta, 2); HMM_MARK(cta, 3); HMM_MARK(cta, 4);
+
+  // ---- exact recursions: warp 0 forward, warp 1 backward, lane = chunk ----
+  float* Yf = U;
+  float* Yr = FULL ? U + (size_t)G * CS : U;
+  if (warp < 2) {
+    const int ci = lane, c = c0 + ci;
+    const bool act = ci < nch;
+    const int t0 = c * L, len = act ? min(L, T - t0) : 0, h = (len + 1) >> 1;
+    const float* Xc = X + ci * CS;
+    float w[NEDGE];
+    load_edges(S.Aw, w);
+    if (warp == 0) {
+      // forward: state av = kappa * alpha-hat (lazily scaled), R = av.A, b = E * max(R, eps*kappa)  (MsaHmmCell.py:77-92)
+      float av[Q];
+      {
+        float t[QP];
+        load_row16(S.hvf[G + ci], t);
+#pragma unroll
+        for (int j = 0; j < Q; ++j) av[j] = t[j];
+      }
+      float kap = sum15(av);
+      int nsum = 0, gprev_ex = 0;
+      float* Yc = Yf + ci * CS;
+      const bool first = (c == 0 && seq_start);
+      for (int ph = 0; ph < 2; ++ph) {
+        const int u_lo = ph == 0 ? 0 : h, u_hi = ph == 0 ? h : len;
+        for (int u = u_lo; u < u_hi; ++u) {
+          float e[QP], R[Q];
+          load_row16(Xc + u * QP, e);
+          if (first && u == 0) {
+#pragma unroll
+            for (int j = 0; j < Q; ++j) R[j] = av[j];
+          } else {
+            vec_A(av, w, R);
+          }
+          const float fl = kEps * kap;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) av[j] = e[j] * fmaxf(R[j], fl);
+          kap = sum15(av);
+          // rescale the propagated state by an exact power of two so that its sum stays in [1,2): stored rows never
+          // come near the denormal range, whatever the emissions were
+          {
+            gprev_ex = pexp(kap);
+            const float sc = pow2neg(gprev_ex);
+            nsum += clamp_exp(gprev_ex);
+#pragma unroll
+            for (int j = 0; j < Q; ++j) av[j] *= sc;
+            kap *= sc;
+            gprev_ex = 0;
+          }
+          if (FULL || ph == 0) {
+            // own row; slot 15: FULL -> exponent of the true value relative to the chunk boundary, else the row sum
+            store_row16(Yc + u * QP, av, FULL ? __int_as_float(nsum) : kap);
+          } else {
+            float o[QP];
+            load_row16(Yc + u * QP, o);
+            const float so = pow2neg(pexp(o[15])) * pow2neg(gprev_ex);
+            float gm[Q];
+#pragma unroll
+            for (int j = 0; j < Q; ++j) gm[j] = av[j] * (o[j] * so);
+            store_row16(Yc + u * QP, gm, 0.f);
+          }
+        }
+        if (ph == 0) named_barrier_sync(1, 64);
+      }
+    } else {
+      // backward: state bh = kappa * b-hat, output R = max(A.bh, eps*kappa), b = E * R  (MsaHmmCell.py:96-100)
+      float R[Q];
+      {
+        float t[QP];
+        load_row16(S.hvr[G + ci], t);
+#pragma unroll
+        for (int j = 0; j < Q; ++j) R[j] = t[j];
+      }
+      float kap = 1.f;           // the boundary vector is all-ones (sequence end, exact) or has its sum in [1,2)
+      int nsum = 0, gprev_ex = 0;
+      float* Yc = Yr + ci * CS;
+      for (int ph = 0; ph < 2; ++ph) {
+        const int u_hi = ph == 0 ? len : h, u_lo = ph == 0 ? h : 0;
+        for (int u = u_hi - 1; u >= u_lo; --u) {
+          float e[QP], Rf[Q], b[Q];
+          load_row16(Xc + u * QP, e);
+          const float fl = kEps * kap;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) Rf[j] = fmaxf(R[j], fl);
+#pragma unroll
+          for (int j = 0; j < Q; ++j) b[j] = e[j] * Rf[j];
+          if (FULL) {
+            store_row16(Yc + u * QP, Rf, __int_as_float(nsum));
+          } else if (ph == 0) {
+            store_row16(Yc + u * QP, Rf, sum15(Rf));
+          } else {
+            float o[QP];
+            load_row16(Yc + u * QP, o);
+            const float so = pow2neg(pexp(o[15])) * pow2neg(pexp(sum15(Rf)));
+            float gm[Q];
+#pragma unroll
+            for (int j = 0; j < Q; ++j) gm[j] = Rf[j] * (o[j] * so);
+            store_row16(Yc + u * QP, gm, 0.f);
+          }
+          kap = sum15(b);
+          {
+            gprev_ex = pexp(kap);
+            const float sc = pow2neg(gprev_ex);
+            nsum += clamp_exp(gprev_ex);
+#pragma unroll
+            for (int j = 0; j < Q; ++j) b[j] *= sc;
+            kap *= sc;
+          }
+          A_vec(b, w, R);
+        }
+        if (ph == 0) named_barrier_sync(1, 64);
+      }
+    }
+  }
+  __syncthreads();
+  HMM_MARK(cta, 5);
+
+  // ---- outputs: thread = (position, state) element, coalesced ----
+  const size_t obase = ((size_t)n * T + t_lo) * Q;
+  const int nel = npos * Q;
+  if (!FULL) {
+    // Y holds alpha-hat * R (any positive scale); -log z (+ log-likelihood) per position into X slot 0
+    for (int i = tid; i < npos; i += nt) {
+      float g[QP];
+      const int off = tile_row_offset(a, i, CS);
+      load_row16(Yf + off, g);
+      float z = 0.f;
+#pragma unroll
+      for (int j = 0; j < Q; ++j) z += fmaxf(g[j], 1e-37f);
+      X[off] = (need_ll ? S.ll : 0.f) - __logf(z);
+    }
+    __syncthreads();
+    HMM_MARK(cta, 6);
+    for (int i = tid; i < nel; i += nt) {
+      const int pos = i / Q, j = i - pos * Q;
+      const int off = tile_row_offset(a, pos, CS);
+      a.out_post[obase + i] = __logf(fmaxf(Yf[off + j], 1e-37f)) + X[off];
+    }
+  } else {
+    if (a.out_post) {
+      for (int i = tid; i < npos; i += nt) {
         float f[QP], r[QP];
-        load_row16(Fa + ci * CS + u * QP, f);
-        load_row16(Rb + ci * CS + u * QP, r);
+        const int off = tile_row_offset(a, i, CS);
+        load_row16(Yf + off, f);
+        load_row16(Yr + off, r);
+        const float sf = pow2neg(pexp(sum15p(f))), sr = pow2neg(pexp(sum15p(r)));
         float z = 0.f;
 #pragma unroll
-        for (int j = 0; j < Q; ++j) z = fmaf(f[j], r[j], z);
-        Es[ci * CS + u * QP] = shift - logf(z);
+        for (int j = 0; j < Q; ++j) z += fmaxf((f[j] * sf) * (r[j] * sr), 1e-37f);
+        // X slot 0: -log z + log-likelihood shift; slots 1,2: the two power-of-two scales
+        X[off] = (need_ll ? S.ll : 0.f) - __logf(z);
+        X[off + 1] = sf;
+        X[off + 2] = sr;
       }
+      __syncthreads();
     }
-    __syncthreads();
-  }
-
-  for (int ci = 0; ci < G; ++ci) {
-    const int c = c_base + ci;
-    if (c >= C) break;
-    const int t0 = c * L, len = min(L, T - t0);
-    const size_t obase = ((size_t)n * T + t0) * Q;
-    const float* f = Fa + ci * CS;
-    const float* r = Rb + ci * CS;
-    const float* z = Es + ci * CS;
-    for (int i = threadIdx.x; i < len * Q; i += blockDim.x) {
-      const int u = i / Q, j = i - u * Q;
-      float lf = 0.f, lr = 0.f;
-      if (want_f) lf = logf(f[u * QP + j]);
-      if (want_b) lr = logf(r[u * QP + j]);
-      if (a.out_post) a.out_post[obase + i] = lf + lr + z[u * QP];
-      if (a.out_alpha) a.out_alpha[obase + i] = lf + f[u * QP + 15];
-      if (a.out_beta) a.out_beta[obase + i] = lr + r[u * QP + 15];
+    HMM_MARK(cta, 6);
+    for (int i = tid; i < nel; i += nt) {
+      const int pos = i / Q, j = i - pos * Q;
+      const int ci = divL(a, pos);
+      const int off = ci * CS + (pos - ci * L) * QP;
+      const float f = Yf[off + j], r = Yr[off + j];
+      if (a.out_post) a.out_post[obase + i] = __logf(fmaxf((f * X[off + 1]) * (r * X[off + 2]), 1e-37f)) + X[off];
+      if (a.out_alpha)
+        a.out_alpha[obase + i] = (float)((double)__logf(fmaxf(f, 1e-37f)) + (double)(__float_as_int(Yf[off + 15]) + S.hef[G + ci]) * LN2D);
+      if (a.out_beta)
+        a.out_beta[obase + i] = (float)((double)__logf(fmaxf(r, 1e-37f)) + (double)(__float_as_int(Yr[off + 15]) + S.her[G + ci]) * LN2D);
     }
   }
+  HMM_MARK(cta, 7);
 }
 
 // stand-alone emission (cell.emission_probs API parity); unfloored
-__global__ void __launch_bounds__(256) emission_kernel(const Args a, float* __restrict__ out) {
+__global__ void __launch_bounds__(512) emission_kernel(const Args a, float* __restrict__ out) {
   extern __shared__ __align__(16) unsigned char smem[];
-  const int G = a.GC, L = a.L, T = a.T;
-  const int CS = L * QP + 4;
-  EmisParams& sp = *reinterpret_cast<EmisParams*>(smem);
-  float4* Ps = reinterpret_cast<float4*>(smem + sizeof(EmisParams));
-  float* Es = reinterpret_cast<float*>(Ps + G * (L + 4));
-  const int n = blockIdx.y, m = n / a.batch, c_base = blockIdx.x * G;
-  load_emis_params(sp, a.Bfull + (size_t)m * Q * Q, a.codon);
+  EmisSmem& sp = *reinterpret_cast<EmisSmem*>(smem);
+  const int L = a.L, T = a.T, CS = L * QP + 4;
+  float* X = reinterpret_cast<float*>(smem + ((sizeof(EmisSmem) + 15) / 16) * 16);
+  signed char* codes = reinterpret_cast<signed char*>(X + (size_t)G * CS);
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
+  const int t_lo = p * G * L, npos = min(T, t_lo + G * L) - t_lo;
+  codes_stage(a, codes, n, t_lo, npos);
+  load_emis_params(sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
   __syncthreads();
-  emission_stage<false>(a, sp, Ps, Es, n, c_base, G, CS);
-  for (int ci = 0; ci < G; ++ci) {
-    const int c = c_base + ci;
-    if (c >= a.C) break;
-    const int t0 = c * L, len = min(L, T - t0);
-    const size_t obase = ((size_t)n * T + t0) * Q;
-    for (int i = threadIdx.x; i < len * Q; i += blockDim.x) {
-      const int u = i / Q, j = i - u * Q;
-      out[obase + i] = Es[ci * CS + u * QP + j];
-    }
+  for (int i0 = tid; i0 < npos; i0 += 2 * nt) {
+    const int i1 = i0 + nt;
+    const bool two = i1 < npos;
+    float e0[Q], e1[Q];
+    emit_pair<false>(a, sp, n, t_lo + i0, t_lo + i1, two, codes + 2 + i0, codes + 2 + i1, e0, e1);
+    store_row16(X + tile_row_offset(a, i0, CS), e0, 0.f);
+    if (two) store_row16(X + tile_row_offset(a, i1, CS), e1, 0.f);
+  }
+  __syncthreads();
+  const size_t obase = ((size_t)n * T + t_lo) * Q;
+  for (int i = tid; i < npos * Q; i += nt) {
+    const int pos = i / Q, j = i - pos * Q;
+    out[obase + i] = X[tile_row_offset(a, pos, CS) + j];
   }
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
-static int g_L = 64, g_GA = 8, g_GC = 8;
+static int g_L = 0;          // 0: choose per call
+static int g_k2_threads = 0; // 0: choose per call
+static int g_num_sms = 0;
+static long long* g_dbg = nullptr;  // device buffer for phase timestamps (debug)
 
 // optional per-kernel timing (bench.py's roofline leg): events around each launch of the last profiled call
 static bool g_prof = false;
-static cudaEvent_t g_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+static cudaEvent_t g_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 static int g_ev_n = 0;
 
 int profile_enable(int on) {
   if (on && !g_ev[0])
-    for (int i = 0; i < 4; ++i) HMM_CUDA_OK(cudaEventCreate(&g_ev[i]));
+    for (int i = 0; i < 5; ++i) HMM_CUDA_OK(cudaEventCreate(&g_ev[i]));
   g_prof = on != 0;
   g_ev_n = 0;
   return 0;
@@ -554,115 +1238,186 @@ int profile_read(float* ms, int n) {
   return k;
 }
 
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+      (void)cudaGetLastError();
+      sms = 148;
+    }
+    g_num_sms = sms;
+  }
+  return g_num_sms;
+}
+
+static int max_L(bool full) {
+  int L = MAX_L;
+  while (L > 1 && (k2_smem_bytes(L, full) > 227 * 1024 || k1_smem_bytes(L) > 227 * 1024)) --L;
+  return L;
+}
+
+// chunk length: the fewest tile rounds over the SMs (K2 runs one tile per SM at a time), then the shortest chunks
+static int choose_L(int NB, int T, bool full) {
+  const int Lmax = max_L(full);
+  if (g_L > 0) return g_L < Lmax ? g_L : Lmax;
+  const int sms = num_sms();
+  double best = 1e300;
+  int bestL = Lmax;
+  for (int L = 4; L <= Lmax; ++L) {
+    const int P = cdiv(cdiv(T, L), G);
+    const long long tiles = (long long)NB * P;
+    const long long rounds = (tiles + sms - 1) / sms;
+    // per-round cost model (cycles): throughput part ~ positions, latency part ~ scans + recursion steps
+    const double cost = (double)rounds * (30.0 * G * L + 500.0 * L + 300.0 * (12 + (P < MAX_INLINE_TILES ? P : 8)) + 6000.0);
+    if (cost < best) { best = cost; bestL = L; }
+  }
+  return bestL;
+}
+
 struct Layout {
-  size_t Mn, gsc, fvec, rvec, fcum, rcum, llws, total;
+  size_t Mh, Mt, bvf, bvr, llws, total;
 };
-static Layout layout(int NB, int C) {
+static Layout layout(int NB, int P) {
   Layout l;
   size_t off = 0;
-  const size_t NC = (size_t)NB * C;
-  l.Mn = off;   off = align_up(off + NC * MAT * sizeof(float), 256);
-  l.gsc = off;  off = align_up(off + NC * sizeof(float), 256);
-  l.fvec = off; off = align_up(off + NC * QP * sizeof(float), 256);
-  l.rvec = off; off = align_up(off + NC * QP * sizeof(float), 256);
-  l.fcum = off; off = align_up(off + NC * sizeof(float), 256);
-  l.rcum = off; off = align_up(off + NC * sizeof(float), 256);
+  const size_t NP = (size_t)NB * P;
+  l.Mh = off;   off = align_up(off + NP * HEAP * MAT * sizeof(float), 256);
+  l.Mt = off;   off = align_up(off + NP * MAT * sizeof(float), 256);
+  l.bvf = off;  off = align_up(off + NP * QP * sizeof(float), 256);
+  l.bvr = off;  off = align_up(off + NP * QP * sizeof(float), 256);
   l.llws = off; off = align_up(off + (size_t)NB * sizeof(float), 256);
   l.total = off;
   return l;
 }
 
-static size_t smem_products(int G, int L) { return sizeof(EmisParams) + (size_t)G * (L + 4) * 16 + (size_t)G * (L * QP + 4) * 4; }
-static size_t smem_finalize(int G, int L) { return sizeof(EmisParams) + (size_t)G * (L + 4) * 16 + 3 * (size_t)G * (L * QP + 4) * 4; }
-
 size_t workspace_size(int num_models, int batch, int T) {
   if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
-  return layout(num_models * batch, cdiv(T, g_L)).total;
+  // run() picks the chunk length from (NB, T, which outputs): cover both choices
+  const int NB = num_models * batch;
+  const size_t a = layout(NB, cdiv(cdiv(T, choose_L(NB, T, false)), G)).total;
+  const size_t b = layout(NB, cdiv(cdiv(T, choose_L(NB, T, true)), G)).total;
+  return a > b ? a : b;
 }
 
-int set_tuning(int L, int GA, int GC) {
-  if (L < 0 || GA < 0 || GC < 0 || GA > 16 || (GA & 1) || GC > 32 || L > 1024) return HMM_B200_EINVAL;
-  if (L) g_L = L;
-  if (GA) g_GA = GA;
-  if (GC) g_GC = GC;
-  if (smem_finalize(g_GC, g_L) > 227 * 1024 || smem_products(g_GA, g_L) > 227 * 1024) {
-    g_L = 64; g_GA = 8; g_GC = 8;
-    set_error("tuning rejected: shared memory footprint exceeds 227 KB");
+int set_debug_buffer(void* p) { g_dbg = static_cast<long long*>(p); return 0; }
+
+int set_tuning(int L, int k2_threads, int reserved) {
+  (void)reserved;
+  if (L < 0 || L > MAX_L || k2_threads < 0 || k2_threads > 512 || (k2_threads & 31) || (k2_threads > 0 && k2_threads < 128)) {
+    set_error("tuning rejected: chunk_len in [0,%d], finalize threads a multiple of 32 in [128,512] or 0", MAX_L);
     return HMM_B200_EINVAL;
   }
+  g_L = L;
+  g_k2_threads = k2_threads;
   return 0;
 }
 
 static int fill_args(Args& a, const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
-                     const float* Bfull, const float* codon, const float* hints, unsigned flags) {
-  HMM_REQUIRE(inputs && Bfull && codon, "genepred: null input pointer");
+                     const float* Bfull, const float* codon5, const float* hints, unsigned flags) {
+  HMM_REQUIRE(inputs && Bfull && codon5, "genepred: null input pointer");
   HMM_REQUIRE(num_models > 0 && batch > 0 && T > 0, "genepred: num_models, batch and T must be positive (got %d,%d,%d)",
               num_models, batch, T);
   HMM_REQUIRE((reinterpret_cast<uintptr_t>(inputs) & 15) == 0, "genepred: inputs must be 16-byte aligned");
+  HMM_REQUIRE((reinterpret_cast<uintptr_t>(codon5) & 15) == 0, "genepred: codon5 must be 16-byte aligned");
   HMM_REQUIRE((long long)num_models * batch <= 65535, "genepred: num_models*batch must be <= 65535");
-  a.inputs = inputs; a.A = A; a.pi = pi; a.Bfull = Bfull; a.codon = codon; a.hints = hints;
+  a.inputs = inputs; a.A = A; a.pi = pi; a.Bfull = Bfull; a.codon5 = codon5; a.hints = hints;
   a.num_models = num_models; a.batch = batch; a.T = T; a.flags = flags;
-  a.L = g_L; a.C = cdiv(T, g_L); a.GA = g_GA; a.GC = g_GC;
+  a.seq_off = 0; a.seq_total = T; a.halo = nullptr; a.dbg = g_dbg;
+  a.in_f = nullptr; a.in_r = nullptr;
+  return 0;
+}
+
+static void set_L(Args& a, int L) {
+  a.L = L;
+  a.mL = (1u << DIV_SHIFT) / (unsigned)L + 1u;
+  a.C = cdiv(a.T, L);
+  a.P = cdiv(a.C, G);
+}
+
+template <typename K>
+static int set_smem(K kernel, size_t bytes) {
+  HMM_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+static int k2_threads_for(int L) {
+  if (g_k2_threads > 0) return g_k2_threads;
+  int nt = ((G * L + 1) / 2 + 31) / 32 * 32;   // two positions per thread in the emission stage
+  if (nt < 128) nt = 128;
+  if (nt > 512) nt = 512;
+  return nt;
+}
+
+int prepare_codon(const float* codon64, float* codon5, cudaStream_t st) {
+  HMM_REQUIRE(codon64 && codon5, "prepare_codon: null pointer");
+  prepare_codon_kernel<<<1, 256, 0, st>>>(codon64, codon5);
+  HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
 int run(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
-        const float* codon, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
+        const float* codon5, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
         float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   Args a{};
-  int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon, hints, flags);
+  int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
   if (rc) return rc;
   HMM_REQUIRE(A && pi, "genepred: null A / pi");
   HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred: no output requested");
   const int NB = num_models * batch;
-  const Layout l = layout(NB, a.C);
+  const bool full = out_alpha || out_beta;
+  set_L(a, choose_L(NB, T, full));
+  const bool need_k2 = out_post || out_alpha || out_beta;
+  // log-likelihood only: the boundary kernel alone yields it; otherwise K2 scans short tile lists itself
+  a.top_inline = (need_k2 && a.P <= MAX_INLINE_TILES) ? 1 : 0;
+  const Layout l = layout(NB, a.P);
   if (!workspace || workspace_bytes < l.total) {
     set_error("genepred: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
     return HMM_B200_EWORKSPACE;
   }
   HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred: workspace must be 256-byte aligned");
   unsigned char* ws = static_cast<unsigned char*>(workspace);
-  a.Mn = reinterpret_cast<float*>(ws + l.Mn);     a.gsc = reinterpret_cast<float*>(ws + l.gsc);
-  a.fvec = reinterpret_cast<float*>(ws + l.fvec); a.rvec = reinterpret_cast<float*>(ws + l.rvec);
-  a.fcum = reinterpret_cast<float*>(ws + l.fcum); a.rcum = reinterpret_cast<float*>(ws + l.rcum);
+  a.Mh = reinterpret_cast<float*>(ws + l.Mh);
+  a.Mt = reinterpret_cast<float*>(ws + l.Mt);
+  a.bvf = reinterpret_cast<float*>(ws + l.bvf); a.bvr = reinterpret_cast<float*>(ws + l.bvr);
   a.llws = reinterpret_cast<float*>(ws + l.llws);
   a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = loglik;
 
-  const size_t smA = smem_products(a.GA, a.L), smC = smem_finalize(a.GC, a.L);
-  static bool attr_done = false;
-  static size_t attrA = 0, attrC = 0;
-  if (!attr_done || smA > attrA || smC > attrC) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(products_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smA));
-    HMM_CUDA_OK(cudaFuncSetAttribute(finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smC));
-    attr_done = true; attrA = smA; attrC = smC;
-  }
+  const size_t sm1 = k1_smem_bytes(a.L), sm2 = k2_smem_bytes(a.L, full);
+  static size_t att1 = 0, att2p = 0, att2f = 0, attb = 0;
+  if (sm1 > att1) { rc = set_smem(products_kernel, sm1); if (rc) return rc; att1 = sm1; }
+  if (need_k2 && !full && sm2 > att2p) { rc = set_smem(finalize_kernel<false>, sm2); if (rc) return rc; att2p = sm2; }
+  if (need_k2 && full && sm2 > att2f) { rc = set_smem(finalize_kernel<true>, sm2); if (rc) return rc; att2f = sm2; }
+  if (!a.top_inline && attb == 0) { rc = set_smem(boundary_kernel, sizeof(KBSmem)); if (rc) return rc; attb = sizeof(KBSmem); }
+
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
-  products_kernel<<<dim3(cdiv(a.C, a.GA), NB), a.GA * 16, smA, st>>>(a);
+  products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
   if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
-  scan_kernel<<<NB, SCAN_WARPS * 32, 0, st>>>(a);
-  if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
-  if (out_post || out_alpha || out_beta) {
-    finalize_kernel<<<dim3(cdiv(a.C, a.GC), NB), 256, smC, st>>>(a);
+  if (!a.top_inline) {
+    boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 0, nullptr);
+    if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
+  }
+  if (need_k2) {
+    // with the inline top-level scan the log-likelihood is produced by the last tile's CTA of K2
+    const int nt = k2_threads_for(a.L);
+    if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
+    else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);
     if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
-int emission(const float* inputs, int num_models, int batch, int T, const float* Bfull, const float* codon,
+int emission(const float* inputs, int num_models, int batch, int T, const float* Bfull, const float* codon5,
              const float* hints, unsigned flags, float* out_E, cudaStream_t st) {
   Args a{};
-  int rc = fill_args(a, inputs, num_models, batch, T, nullptr, nullptr, Bfull, codon, hints, flags);
+  int rc = fill_args(a, inputs, num_models, batch, T, nullptr, nullptr, Bfull, codon5, hints, flags);
   if (rc) return rc;
   HMM_REQUIRE(out_E, "genepred_emission: null output");
-  a.L = 64; a.GC = 8; a.C = cdiv(T, a.L);
-  const size_t sm = smem_products(a.GC, a.L);
+  set_L(a, 32);
+  const size_t sm = ((sizeof(EmisSmem) + 15) / 16) * 16 + (size_t)G * (a.L * QP + 4) * sizeof(float) + (((size_t)G * a.L + 4 + 15) / 16) * 16;
   static bool done = false;
-  if (!done) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(emission_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    done = true;
-  }
-  emission_kernel<<<dim3(cdiv(a.C, a.GC), num_models * batch), 256, sm, st>>>(a, out_E);
+  if (!done) { rc = set_smem(emission_kernel, sm); if (rc) return rc; done = true; }
+  emission_kernel<<<dim3(a.P, num_models * batch), 512, sm, st>>>(a, out_E);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -676,24 +1431,29 @@ size_t hmm_b200_genepred_workspace_size(int num_models, int batch, int T) {
   return hmm::gene15::workspace_size(num_models, batch, T);
 }
 
+int hmm_b200_debug_phases(void* device_buffer) { return hmm::gene15::set_debug_buffer(device_buffer); }
 int hmm_b200_profile_enable(int on) { return hmm::gene15::profile_enable(on); }
 int hmm_b200_profile_read(float* ms_host, int n) { return hmm::gene15::profile_read(ms_host, n); }
 
-int hmm_b200_set_tuning(int chunk_len, int chunks_per_products_cta, int chunks_per_finalize_cta) {
-  return hmm::gene15::set_tuning(chunk_len, chunks_per_products_cta, chunks_per_finalize_cta);
+int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int reserved) {
+  return hmm::gene15::set_tuning(chunk_len, finalize_threads, reserved);
+}
+
+int hmm_b200_genepred_prepare_codon(const float* codon64, float* codon5, void* stream) {
+  return hmm::gene15::prepare_codon(codon64, codon5, static_cast<cudaStream_t>(stream));
 }
 
 int hmm_b200_genepred_run(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
-                          const float* Bfull, const float* codon, const float* end_hints, unsigned flags,
+                          const float* Bfull, const float* codon5, const float* end_hints, unsigned flags,
                           float* out_post, float* out_alpha, float* out_beta, float* loglik, void* workspace,
                           size_t workspace_bytes, void* stream) {
-  return hmm::gene15::run(inputs, num_models, batch, T, A, pi, Bfull, codon, end_hints, flags, out_post, out_alpha,
+  return hmm::gene15::run(inputs, num_models, batch, T, A, pi, Bfull, codon5, end_hints, flags, out_post, out_alpha,
                           out_beta, loglik, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T, const float* Bfull,
-                               const float* codon, const float* end_hints, unsigned flags, float* out_E, void* stream) {
-  return hmm::gene15::emission(inputs, num_models, batch, T, Bfull, codon, end_hints, flags, out_E,
+                               const float* codon5, const float* end_hints, unsigned flags, float* out_E, void* stream) {
+  return hmm::gene15::emission(inputs, num_models, batch, T, Bfull, codon5, end_hints, flags, out_E,
                                static_cast<cudaStream_t>(stream));
 }
 

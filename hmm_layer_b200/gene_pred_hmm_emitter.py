@@ -119,12 +119,21 @@ class GenePredHMMEmitter(SimpleGenePredHMMEmitter):
         right = torch.cat([not_stop, anyc, anyc, not_stop, anyc, iend, iend, iend, stop], dim=1)
         self.register_buffer("codon_probs", torch.cat([left, right], dim=0).contiguous())   # (2, 9, 64)
 
+    def codon5(self, device):
+        """(2,125,12) 5-symbol codon tables the kernels read, built once per device from the constant codon_probs."""
+        from . import ops
+        c = getattr(self, "_codon5", None)
+        if c is None or c.device != torch.device(device):
+            c = ops.prepare_codon(self.codon_probs.to(device))
+            object.__setattr__(self, "_codon5", c)
+        return c
+
     def forward(self, inputs, end_hints=None, training=False):
         """(num_models, batch, T, 15+5) -> (num_models, batch, T, num_states) emission probabilities on the GPU."""
         from . import ops
         if self.num_copies != 1 or inputs.shape[-1] != 20:
             raise NotImplementedError("stand-alone CUDA emission supports num_copies=1 with 15 classes + 5 nucleotide flags")
-        return ops.genepred_emission(inputs, self.make_B_full().detach(), self.codon_probs.to(inputs.device),
+        return ops.genepred_emission(inputs, self.make_B_full().detach(), self.codon5(inputs.device),
                                      end_hints=end_hints, training=training)
 
     def get_config(self):

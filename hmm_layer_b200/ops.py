@@ -40,8 +40,10 @@ def _workspace(nbytes, device):
     return ws
 
 
-def set_tuning(chunk_len=0, chunks_per_products_cta=0, chunks_per_finalize_cta=0):
-    _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, chunks_per_products_cta, chunks_per_finalize_cta))
+def set_tuning(chunk_len=0, finalize_threads=0):
+    """chunk_len: positions per chunk (0 = chosen per call from the problem size and the SM count);
+    finalize_threads: threads per CTA of the finalize kernel (0 = derived from chunk_len)."""
+    _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, finalize_threads, 0))
 
 
 def profile_enable(on=True):
@@ -58,9 +60,25 @@ def profile_read():
     return [buf[i] for i in range(n)]
 
 
+def prepare_codon(codon):
+    """(2,9,64) codon_probs -> (2,125,12) 5-symbol tables the kernels read (once per parameter set)."""
+    codon = _req(codon, "codon", (2, 9, 64))
+    with torch.cuda.device(codon.device):
+        out = torch.empty((2, 125, 12), dtype=torch.float32, device=codon.device)
+        _lib.check(_lib.load().hmm_b200_genepred_prepare_codon(_ptr(codon), _ptr(out), _stream()))
+    return out
+
+
+def _codon5(codon):
+    if tuple(codon.shape) == (2, 125, 12):
+        return _req(codon, "codon5", (2, 125, 12))
+    return prepare_codon(codon)
+
+
 def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,
                  want_post=True, want_alpha=False, want_beta=False, out=None):
-    """Fused 15-state gene-HMM evaluation.  inputs (k,B,T,20).  Returns dict with the requested tensors
+    """Fused 15-state gene-HMM evaluation.  inputs (k,B,T,20); codon = the emitter's (2,9,64) codon_probs or the
+    prepared (2,125,12) tables (prepare_codon).  Returns dict with the requested tensors
     ('post','alpha','beta' each (k,B,T,15)) and 'loglik' (k,B)."""
     lib = _lib.load()
     if inputs.dim() != 4 or inputs.shape[-1] != 20:
@@ -69,7 +87,7 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
     inputs = _req(inputs, "inputs")
     dev = inputs.device
     A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
-    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _req(codon, "codon", (2, 9, 64))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
     if end_hints is not None:
         end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
     with torch.cuda.device(dev):
@@ -95,7 +113,7 @@ def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
         raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
     k, B, T, _ = inputs.shape
     inputs = _req(inputs, "inputs")
-    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _req(codon, "codon", (2, 9, 64))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
     if end_hints is not None:
         end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
     with torch.cuda.device(inputs.device):

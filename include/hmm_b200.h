@@ -32,14 +32,18 @@ extern "C" {
 int hmm_b200_abi_version(void);
 const char* hmm_b200_last_error(void);
 
-/* Optional tuning of the chunked scan (0 keeps the default): chunk length, chunks per products-CTA,
- * chunks per finalize-CTA.  Process-wide; meant for benchmarking. */
-int hmm_b200_set_tuning(int chunk_len, int chunks_per_products_cta, int chunks_per_finalize_cta);
+/* Optional tuning of the chunked scan: chunk length in positions (0 = chosen per call from the problem size and
+ * the SM count; at most 48), threads per CTA of the finalize kernel (0 = derived; a multiple of 32 in [128,512]).
+ * The third argument is reserved (pass 0).  Process-wide; meant for benchmarking and tests. */
+int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int reserved);
 
 /* Per-kernel timing for benchmarks: when enabled, hmm_b200_genepred_run records CUDA events around each of its
- * launches (products, scan, finalize); hmm_b200_profile_read waits for the last profiled call and writes up to n
+ * launches (products, [boundary], finalize); hmm_b200_profile_read waits for the last profiled call and writes up to n
  * durations in milliseconds to the HOST array ms_host, returning how many it wrote. */
 int hmm_b200_profile_enable(int on);
+/* Debug: when device_buffer is non-NULL, thread 0 of every CTA of the gene-HMM kernels writes clock64() phase
+ * timestamps into it (int64 [2][CTAs][16]); NULL switches it off (tools/phase_times.py). */
+int hmm_b200_debug_phases(void* device_buffer);
 int hmm_b200_profile_read(float* ms_host, int n);
 
 /* ---------------------------------------------------------------------------------------------------------
@@ -57,22 +61,29 @@ int hmm_b200_profile_read(float* ms_host, int n);
  *                                         (gene_pred_hmm_transitioner.py:200-221)
  *   pi        (num_models, 15)            initial distribution
  *   Bfull     (num_models, 15, 15)        [state][class] = softmax(emission kernel), intron rows already repeated
- *   codon     (2, 9, 64)                  left/right 3-mer tables for states E2,START,EI0-2,IE0-2,STOP
+ *   codon5    (2, 125, 12)                5-symbol (A,C,G,T,N) left/right 3-mer tables for states E2,START,EI0-2,
+ *                                         IE0-2,STOP (+3 pad), built from the emitter's (2,9,64) codon_probs by
+ *                                         hmm_b200_genepred_prepare_codon (once per parameter set)
  *   end_hints (num_models, batch, 2, 15)  or NULL
  *   out_post / out_alpha / out_beta (num_models, batch, T, 15), each may be NULL
  *   loglik    (num_models, batch)         may be NULL
  * --------------------------------------------------------------------------------------------------------- */
 size_t hmm_b200_genepred_workspace_size(int num_models, int batch, int T);
 
+/* codon64 (2,9,64) = GenePredHMMEmitter.codon_probs (gene_pred_hmm_emitter.py:198-217)  ->  codon5 (2,125,12):
+ * index (near*5 + far)*5 + pivot over A,C,G,T,N where N (and positions outside the sequence) average the four
+ * bases, which is what the reference's soft k-mers do for N (kmer.py:21-33). */
+int hmm_b200_genepred_prepare_codon(const float* codon64, float* codon5, void* stream);
+
 int hmm_b200_genepred_run(const float* inputs, int num_models, int batch, int T,
-                          const float* A, const float* pi, const float* Bfull, const float* codon,
+                          const float* A, const float* pi, const float* Bfull, const float* codon5,
                           const float* end_hints, unsigned flags,
                           float* out_post, float* out_alpha, float* out_beta, float* loglik,
                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* Stand-alone emission (cell.emission_probs API parity): out_E (num_models, batch, T, 15). */
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
-                               const float* Bfull, const float* codon, const float* end_hints,
+                               const float* Bfull, const float* codon5, const float* end_hints,
                                unsigned flags, float* out_E, void* stream);
 
 #ifdef __cplusplus

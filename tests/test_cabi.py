@@ -28,5 +28,7 @@ def test_abi_version_and_workspace_query_need_no_gpu():
     assert lib.hmm_b200_abi_version() == 1
     assert lib.hmm_b200_genepred_workspace_size(1, 32, 9999) > 0
     assert lib.hmm_b200_genepred_workspace_size(0, 32, 9999) == 0
-    assert lib.hmm_b200_set_tuning(64, 7, 8) != 0      # odd chunks-per-CTA rejected
-    assert lib.hmm_b200_set_tuning(64, 8, 8) == 0
+    assert lib.hmm_b200_set_tuning(64, 0, 0) != 0      # chunk length above the shared-memory bound rejected
+    assert lib.hmm_b200_set_tuning(32, 100, 0) != 0    # finalize threads must be a multiple of 32
+    assert lib.hmm_b200_set_tuning(32, 256, 0) == 0
+    assert lib.hmm_b200_set_tuning(0, 0, 0) == 0

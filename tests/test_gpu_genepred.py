@@ -97,8 +97,14 @@ def test_flags_hints_models():
         if kw.get("no_loglik"):
             # log_post + loglik is ~ -5500 here: float32 resolves that to 4.9e-4, so the un-normalised output
             # carries that quantisation (the reference's own output format has the same property)
-            np.testing.assert_allclose(got["post"] - got["loglik"][..., None, None], ref["log_post"] - ref["loglik"][..., None, None],
-                                       rtol=0, atol=5e-3)
+            # (the posterior-only kernel multiplies alpha-hat and R before the log and floors the product at
+            # 1e-37 before dividing by z = sum_q alpha-hat*R (z can be ~1e-3): log posteriors below about -75 are
+            # reported as -78 .. -87, so compare above -70)
+            gp = got["post"] - got["loglik"][..., None, None]
+            rp = ref["log_post"] - ref["loglik"][..., None, None]
+            vis = rp > -70
+            np.testing.assert_allclose(gp[vis], rp[vis], rtol=0, atol=5e-3)
+            assert (gp[~vis] < -65).all()
             got = dict(got, post=got["post"] - got["loglik"][..., None, None])
             ref = dict(ref, log_post=ref["log_post"] - ref["loglik"][..., None, None])
             tol_dp = 5e-4
@@ -117,16 +123,19 @@ def test_loglik_only_and_determinism():
     assert np.array_equal(b["post"], c["post"]) and np.array_equal(a["loglik"], b["loglik"])
 
 
-@pytest.mark.parametrize("L,GA,GC", [(16, 2, 4), (32, 8, 16), (128, 4, 4), (100, 6, 3)])
-def test_tuning_does_not_change_results(L, GA, GC):
+@pytest.mark.parametrize("L,NT", [(1, 128), (2, 0), (5, 256), (16, 0), (32, 512), (33, 160), (48, 0)])
+def test_tuning_does_not_change_results(L, NT):
+    """Chunk length / CTA width only change the decomposition; L=1,2 give > 24 tiles (boundary kernel path)."""
     x = syn.gene_inputs(1, 2, 1500, seed=9)
     A, pi, Bfull, tab = gene_params()
     ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
     try:
-        ops.set_tuning(L, GA, GC)
+        ops.set_tuning(L, NT)
         got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+        got2 = run_gpu(x, A, pi, Bfull, tab, want_post=True)
     finally:
-        ops.set_tuning(64, 8, 8)
+        ops.set_tuning(0, 0)
+    check_post(got2, ref)
     check_post(got, ref)
     check_ab(got, ref)
 
@@ -157,16 +166,22 @@ def test_config2_full_size_properties():
     sl = slice(0, 3)
     ref = oracle_gene(x.numpy()[:, sl], A, pi, Bfull, tab)
     check_post({k: v[:, sl] for k, v in got.items()}, ref)
-    # batch independence: a sequence evaluated alone gives the same bits
-    alone = run_gpu(x[:, 5:6].contiguous(), A, pi, Bfull, tab, want_post=True)
-    assert np.array_equal(alone["post"][0, 0], got["post"][0, 5])
-    # reversal symmetry of the recursion is not available for this model; instead: concatenation consistency
-    # loglik(seq) computed with chunk length 64 equals chunk length 37
+    # batch independence: with the same chunk length, a sequence evaluated alone gives the same bits
     try:
-        ops.set_tuning(37, 8, 8)
+        ops.set_tuning(35, 0)
+        both = run_gpu(x[:, 4:7].contiguous(), A, pi, Bfull, tab, want_post=True)
+        alone = run_gpu(x[:, 5:6].contiguous(), A, pi, Bfull, tab, want_post=True)
+    finally:
+        ops.set_tuning(0, 0)
+    assert np.array_equal(alone["post"][0, 0], both["post"][0, 1])
+    np.testing.assert_allclose(alone["post"][0, 0], got["post"][0, 5], rtol=0, atol=2e-4)
+    # reversal symmetry of the recursion is not available for this model; instead: concatenation consistency
+    # loglik(seq) computed with the automatic chunk length equals chunk length 37
+    try:
+        ops.set_tuning(37, 0)
         g2 = run_gpu(x[:, :4].contiguous(), A, pi, Bfull, tab, want_post=False)
     finally:
-        ops.set_tuning(64, 8, 8)
+        ops.set_tuning(0, 0)
     np.testing.assert_allclose(g2["loglik"], got["loglik"][:, :4], rtol=1e-6)
 
 

@@ -1,0 +1,37 @@
+"""Per-phase cycle counts of the gene-HMM kernels on config 2 (debug instrumentation, clock64 of thread 0)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+from hmm_layer_b200 import ops, synthetic as syn, _lib
+from tests.helpers import gene_params
+
+L = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+x = syn.gene_inputs(1, B, 9999, seed=1234).cuda()
+A, pi, Bfull, tab = [torch.as_tensor(np.asarray(v, np.float32)).cuda() for v in gene_params()]
+out = torch.empty((1, B, 9999, 15), device="cuda")
+ops.set_tuning(L, 0)
+for _ in range(3):
+    ops.genepred_run(x, A, pi, Bfull, tab, out={"post": out})
+nct = 4096
+dbg = torch.zeros((2, nct, 16), dtype=torch.int64, device="cuda")
+_lib.load().hmm_b200_debug_phases(dbg.data_ptr())
+ops.genepred_run(x, A, pi, Bfull, tab, out={"post": out})
+torch.cuda.synchronize()
+_lib.load().hmm_b200_debug_phases(None)
+d = dbg.cpu().numpy().reshape(-1, 16)
+nc = int((d[:, 0] > 0).sum()) // 2
+d = d[:2 * nc].reshape(2, nc, 16)
+names = [["params", "emission+coef", "rows", "blocks", "tree", "store"],
+         ["params", "emission+cpwait", "scan-top", "down-sweep", "recursion", "z", "out"]]
+for k in range(2):
+    t = d[k]
+    print(f"kernel {k}: {nc} CTAs; wall span = {(t[:, len(names[k])].max() - t[:, 0].min())} cycles")
+    dt = np.diff(t[:, :len(names[k]) + 1], axis=1)
+    for j, nm in enumerate(names[k]):
+        print(f"   {nm:18s} median {np.median(dt[:, j]):9.0f}  max {dt[:, j].max():9.0f}")
+    if k == 0:
+        print(f"   [params detail] codes {np.median(t[:, 7] - t[:, 0]):.0f}  +emis-params {np.median(t[:, 8] - t[:, 7]):.0f}  +barrier {np.median(t[:, 1] - t[:, 8]):.0f}"
+              f"   first-round CTAs params {np.median((t[:, 1] - t[:, 0])[:148]):.0f}, later {np.median((t[:, 1] - t[:, 0])[148:]):.0f}")
+    print(f"   per-CTA total      median {np.median(t[:, len(names[k])] - t[:, 0]):9.0f}")
