@@ -1,0 +1,368 @@
+// Generic dense-transition HMM path for sm_100a: scaled forward / backward / posterior for any number of states q
+// (profile HMMs q = 2L+3, multi-copy gene models q = 1+14k), from a materialised emission tensor.
+//
+// Reference semantics (MsaHmmCell.py:73-106 driven by BaseRNN.py:216-227, drivers MsaHMMLayer.py:227-521):
+//   forward   R_0 = max(pi, eps);  R_t = max(a-hat_{t-1} . A, eps);  a_t = max(E_t, eps) * R_t;  S_t = sum_q a_t;
+//             a-hat_t = a_t / S_t;  log alpha_t = log a-hat_t + sum_{tau<=t} log S_tau
+//   backward  R_{T-1} = 1;  R_t = max(b-hat_{t+1} . A^T, eps);  b_t = max(E_t, eps) * R_t;  b-hat_t = b_t / S;
+//             log beta_t = log R_t + sum_{tau>t} log S_tau
+//   posterior log alpha + log beta - loglik
+//
+// One launch per time step and direction, stream-ordered: a shared-memory tiled fp32 GEMM
+// state(B x q) . A(q x q) with the floor / emission / row-sum epilogue fused.  Normalisation is deferred to the consumer:
+// the step writes a_t (un-normalised) and per-column-tile partial row sums; the next step divides by their sum
+// (deterministic order), so no atomics and bit-reproducible results.  A tcgen05 version of the step GEMM for the
+// learnMSA sizes (q ~ 1000) is the next item of DESIGN.md; this CUDA-core step is the correct baseline it must match.
+#include "common.cuh"
+
+namespace hmm {
+namespace dense {
+
+constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;   // 256 threads, 4x4 outputs each
+constexpr int MAXP = 32;                                    // at most 32 column tiles (q <= 2048)
+
+struct StepArgs {
+  const float* state;    // (k, B, q) un-normalised previous vector (or the initial state when init)
+  const float* part_in;  // (k, B, ntile) partial sums of `state` (ignored when init)
+  const float* A;        // (k, q, q): forward A, backward A^T (row-major, so that U = state . A)
+  const float* E;        // emission rows of this step: E + ((m*B + b)*T + t)*q
+  float* state_out;      // (k, B, q)
+  float* part_out;       // (k, B, ntile)
+  float* store;          // optional (k, B, T, q) buffer; row t receives a_t (forward) / R_t (backward), un-normalised
+  float* scale_hist;     // (k, B, T): S of the *input* state used at this step (1 when init) -> slot t
+  int k, B, T, q, t, ntile;
+  int init, reverse;
+};
+
+__global__ void __launch_bounds__(256) step_kernel(const StepArgs a) {
+  __shared__ float As[BK][BM + 4];   // state tile, transposed: As[kk][row]
+  __shared__ float Bs[BK][BN + 4];
+  __shared__ float Sin[BM];          // 1 / S of the input rows
+  __shared__ float red[BM][BN / TN + 1];
+  const int m = blockIdx.z, row0 = blockIdx.y * BM, col0 = blockIdx.x * BN;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;   // thread tile: rows ty*4.., cols tx*4..
+  const int q = a.q, B = a.B;
+  const float* st = a.state + (size_t)m * B * q;
+  const float* Am = a.A + (size_t)m * q * q;
+
+  if (tid < BM) {
+    float s = 1.f;
+    const int r = row0 + tid;
+    if (!a.init && r < B) {
+      s = 0.f;
+      const float* p = a.part_in + ((size_t)m * B + r) * a.ntile;
+      for (int i = 0; i < a.ntile; ++i) s += p[i];
+    }
+    Sin[tid] = s;
+    if (blockIdx.x == 0 && r < B && a.scale_hist) a.scale_hist[((size_t)m * B + r) * a.T + a.t] = s;
+  }
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  if (!a.init) {
+    for (int k0 = 0; k0 < q; k0 += BK) {
+      // state tile: BM x BK (256 threads x 4 elements)
+#pragma unroll
+      for (int l = 0; l < (BM * BK) / 256; ++l) {
+        const int idx = tid + l * 256, r = idx / BK, kk = idx - r * BK;
+        const int gr = row0 + r, gk = k0 + kk;
+        As[kk][r] = (gr < B && gk < q) ? st[(size_t)gr * q + gk] : 0.f;
+      }
+#pragma unroll
+      for (int l = 0; l < (BK * BN) / 256; ++l) {
+        const int idx = tid + l * 256, kk = idx / BN, c = idx - kk * BN;
+        const int gk = k0 + kk, gc = col0 + c;
+        Bs[kk][c] = (gk < q && gc < q) ? Am[(size_t)gk * q + gc] : 0.f;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < BK; ++kk) {
+        float av[TM], bv[TN];
+#pragma unroll
+        for (int i = 0; i < TM; ++i) av[i] = As[kk][ty * TM + i];
+#pragma unroll
+        for (int j = 0; j < TN; ++j) bv[j] = Bs[kk][tx * TN + j];
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  } else {
+    __syncthreads();
+  }
+
+  // epilogue: R = max(U / S_in, eps)  (init: U = the given state);  x = max(E, eps) * R
+  float rsum[TM];
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    rsum[i] = 0.f;
+    const int r = row0 + ty * TM + i;
+    if (r >= B) continue;
+    const float inv = 1.0f / Sin[ty * TM + i];
+    const float* Er = a.E + (((size_t)m * B + r) * a.T + a.t) * q;
+    float* so = a.state_out + ((size_t)m * B + r) * q;
+    float* sr = a.store ? a.store + (((size_t)m * B + r) * a.T + a.t) * q : nullptr;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int c = col0 + tx * TN + j;
+      if (c >= q) continue;
+      const float U = a.init ? st[(size_t)r * q + c] : acc[i][j] * inv;
+      const float R = fmaxf(U, kEps);
+      const float x = fmaxf(Er[c], kEps) * R;
+      so[c] = x;
+      if (sr) sr[c] = a.reverse ? R : x;
+      rsum[i] += x;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) red[ty * TM + i][tx] = rsum[i];
+  __syncthreads();
+  if (tid < BM) {
+    const int r = row0 + tid;
+    if (r < B) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < BN / TN; ++j) s += red[tid][j];
+      a.part_out[((size_t)m * B + r) * a.ntile + blockIdx.x] = s;
+    }
+  }
+}
+
+// per sequence: cumulative log scales (double) and the log-likelihood.
+//   forward:  hist[t] = S_{t-1} (1 at t = 0), final = partial sums of the last state  ->  cum_f[t] = sum_{tau<=t} log S_tau
+//   backward: hist[t] = S_{t+1} (1 at t = T-1)                                        ->  cum_b[t] = sum_{tau>t} log S_tau
+__global__ void cum_kernel(const float* __restrict__ hist_f, const float* __restrict__ part_f, const float* __restrict__ hist_b,
+                           float* __restrict__ cum_f, float* __restrict__ cum_b, float* __restrict__ loglik, int N, int T, int ntile) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  if (hist_f) {
+    const float* h = hist_f + (size_t)n * T;
+    double c = 0.0;
+    for (int t = 0; t < T; ++t) {
+      float s;
+      if (t + 1 < T) s = h[t + 1];
+      else { s = 0.f; for (int i = 0; i < ntile; ++i) s += part_f[(size_t)n * ntile + i]; }
+      c += log((double)s);
+      if (cum_f) cum_f[(size_t)n * T + t] = (float)c;
+    }
+    if (loglik) loglik[n] = (float)c;
+  }
+  if (hist_b && cum_b) {
+    const float* h = hist_b + (size_t)n * T;
+    double c = 0.0;
+    for (int t = T - 1; t >= 0; --t) {
+      if (t + 1 < T) c += log((double)h[t]);   // h[t] = S of b_{t+1}
+      cum_b[(size_t)n * T + t] = (float)c;
+    }
+  }
+}
+
+// in place: stored a_t -> log alpha_t,  stored R_t -> log beta_t,  and the posterior
+__global__ void finish_kernel(float* __restrict__ alpha, float* __restrict__ beta, float* __restrict__ post,
+                              const float* __restrict__ hist_f, const float* __restrict__ part_f, const float* __restrict__ cum_f,
+                              const float* __restrict__ cum_b, const float* __restrict__ loglik, int N, int T, int q, int ntile,
+                              int no_loglik) {
+  const size_t row = blockIdx.x;           // (n, t)
+  const int n = (int)(row / T), t = (int)(row - (size_t)n * T);
+  float S = 1.f, cf = 0.f, cb = 0.f;
+  if (alpha) {
+    if (t + 1 < T) S = hist_f[(size_t)n * T + t + 1];
+    else { S = 0.f; for (int i = 0; i < ntile; ++i) S += part_f[(size_t)n * ntile + i]; }
+    cf = cum_f[(size_t)n * T + t];
+  }
+  if (beta) cb = cum_b[(size_t)n * T + t];
+  const float ll = (post && !no_loglik) ? loglik[n] : 0.f;
+  const float invS = 1.0f / S;
+  for (int j = threadIdx.x; j < q; j += blockDim.x) {
+    const size_t i = row * q + j;
+    float la = 0.f, lb = 0.f;
+    if (alpha) { la = logf(alpha[i] * invS) + cf; }
+    if (beta) { lb = logf(beta[i]) + cb; }
+    if (post) post[i] = la + lb - ll;
+    if (alpha) alpha[i] = la;
+    if (beta) beta[i] = lb;
+  }
+}
+
+// One HmmCell.forward call (MsaHmmCell.py:73-106) for API parity: row = (model, sequence, conditional row).
+//   E_t (k*n, q); scaled (k*n, qc*q); loglik (k*n, qc);  A (k, q, q) already oriented (A or A^T)
+//   out (k*n, qc*q + qc): [log a-hat | loglik] (forward) or [log R | old loglik] (reverse)
+__global__ void cell_step_kernel(const float* __restrict__ E, const float* __restrict__ scaled, const float* __restrict__ loglik,
+                                 const float* __restrict__ A, float* __restrict__ out, float* __restrict__ new_scaled,
+                                 float* __restrict__ new_loglik, int k, int n, int qc, int q, int reverse, int init) {
+  extern __shared__ float sh[];   // q state values + 32 reduction slots
+  float* sv = sh;
+  float* red = sh + q;
+  const size_t r = blockIdx.x;                 // over k*n*qc
+  const size_t seq = r / qc;                   // (model, sequence)
+  const int c = (int)(r - seq * qc);
+  const int m = (int)(seq / n);
+  const float* s = scaled + seq * (size_t)qc * q + (size_t)c * q;
+  for (int i = threadIdx.x; i < q; i += blockDim.x) sv[i] = s[i];
+  __syncthreads();
+  const float* Am = A + (size_t)m * q * q;
+  const float* Er = E + seq * (size_t)q;
+  float local = 0.f;
+  for (int j = threadIdx.x; j < q; j += blockDim.x) {
+    float U;
+    if (init) U = sv[j];
+    else {
+      U = 0.f;
+      for (int i = 0; i < q; ++i) U = fmaf(sv[i], Am[(size_t)i * q + j], U);
+    }
+    const float R = fmaxf(U, kEps);
+    const float x = fmaxf(Er[j], kEps) * R;
+    new_scaled[seq * (size_t)qc * q + (size_t)c * q + j] = x;          // normalised below
+    if (reverse) out[seq * ((size_t)qc * q + qc) + (size_t)c * q + j] = logf(R);
+    local += x;
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = local;
+  __syncthreads();
+  float S = 0.f;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) S += red[w];
+  const float old_ll = loglik[seq * qc + c];
+  const float ll = old_ll + logf(S);
+  const float inv = 1.0f / S;
+  for (int j = threadIdx.x; j < q; j += blockDim.x) {
+    const size_t si = seq * (size_t)qc * q + (size_t)c * q + j;
+    const float ah = new_scaled[si] * inv;
+    new_scaled[si] = ah;
+    if (!reverse) out[seq * ((size_t)qc * q + qc) + (size_t)c * q + j] = logf(ah);
+  }
+  if (threadIdx.x == 0) {
+    new_loglik[seq * qc + c] = ll;
+    out[seq * ((size_t)qc * q + qc) + (size_t)qc * q + c] = reverse ? old_ll : ll;
+  }
+}
+
+// fill (k, B, q) with pi broadcast (forward) or ones (backward)
+__global__ void init_state_kernel(float* __restrict__ st, const float* __restrict__ pi, int k, int B, int q) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)k * B * q) return;
+  const int j = (int)(i % q);
+  const int m = (int)(i / ((size_t)B * q));
+  st[i] = pi ? pi[(size_t)m * q + j] : 1.f;
+}
+
+struct Layout {
+  size_t st[2][2], part[2][2], hist[2], cum[2], ll, total;
+};
+static Layout layout(int k, int B, int T, int q) {
+  Layout l;
+  const int ntile = cdiv(q, BN);
+  const size_t N = (size_t)k * B;
+  size_t off = 0;
+  for (int d = 0; d < 2; ++d)
+    for (int p = 0; p < 2; ++p) { l.st[d][p] = off; off = align_up(off + N * q * sizeof(float), 256); }
+  for (int d = 0; d < 2; ++d)
+    for (int p = 0; p < 2; ++p) { l.part[d][p] = off; off = align_up(off + N * ntile * sizeof(float), 256); }
+  for (int d = 0; d < 2; ++d) { l.hist[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
+  for (int d = 0; d < 2; ++d) { l.cum[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
+  l.ll = off; off = align_up(off + N * sizeof(float), 256);
+  l.total = off;
+  return l;
+}
+
+size_t workspace_size(int k, int B, int T, int q) {
+  if (k <= 0 || B <= 0 || T <= 0 || q <= 0) return 0;
+  return layout(k, B, T, q).total;
+}
+
+// out_alpha / out_beta double as the per-step stores; out_post needs both (the caller passes scratch for the one it
+// does not want back: see hmm_b200.h)
+int run(const float* E, const float* A, const float* At, const float* pi, int k, int B, int T, int q, unsigned flags,
+        float* out_post, float* out_alpha, float* out_beta, float* loglik, void* workspace, size_t workspace_bytes,
+        cudaStream_t st) {
+  HMM_REQUIRE(E && A && pi, "dense: null input pointer");
+  HMM_REQUIRE(k > 0 && B > 0 && T > 0 && q > 0, "dense: k, B, T, q must be positive (got %d,%d,%d,%d)", k, B, T, q);
+  HMM_REQUIRE(cdiv(q, BN) <= MAXP, "dense: q = %d exceeds the supported %d states", q, MAXP * BN);
+  HMM_REQUIRE(cdiv(B, BM) <= 65535 && k <= 65535, "dense: batch / model count too large");
+  HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "dense: no output requested");
+  const bool need_f = out_post || out_alpha || loglik, need_b = out_post || out_beta;
+  HMM_REQUIRE(!out_post || (out_alpha && out_beta), "dense: the posterior needs alpha and beta buffers (scratch is fine)");
+  HMM_REQUIRE(!need_b || At, "dense: the backward pass needs A^T");
+  const Layout l = layout(k, B, T, q);
+  if (!workspace || workspace_bytes < l.total) {
+    set_error("dense: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
+    return HMM_B200_EWORKSPACE;
+  }
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  auto F = [&](size_t o) { return reinterpret_cast<float*>(ws + o); };
+  const int ntile = cdiv(q, BN);
+  const size_t N = (size_t)k * B;
+  const dim3 grid(ntile, cdiv(B, BM), k);
+  const int ib = 256, ig = (int)((N * q + ib - 1) / ib);
+  float* llbuf = loglik ? loglik : F(l.ll);
+
+  for (int d = 0; d < 2; ++d) {
+    if ((d == 0 && !need_f) || (d == 1 && !need_b)) continue;
+    init_state_kernel<<<ig, ib, 0, st>>>(F(l.st[d][0]), d == 0 ? pi : nullptr, k, B, q);
+    for (int s = 0; s < T; ++s) {
+      StepArgs a;
+      const int t = d == 0 ? s : T - 1 - s;
+      a.state = F(l.st[d][s & 1]); a.part_in = F(l.part[d][s & 1]);
+      a.state_out = F(l.st[d][(s + 1) & 1]); a.part_out = F(l.part[d][(s + 1) & 1]);
+      a.A = d == 0 ? A : At; a.E = E;
+      a.store = d == 0 ? out_alpha : out_beta;
+      a.scale_hist = F(l.hist[d]);
+      a.k = k; a.B = B; a.T = T; a.q = q; a.t = t; a.ntile = ntile; a.init = s == 0; a.reverse = d;
+      step_kernel<<<grid, 256, 0, st>>>(a);
+    }
+  }
+  HMM_CUDA_OK(cudaGetLastError());
+  const float* part_f = F(l.part[0][T & 1]);
+  cum_kernel<<<cdiv((int)N, 128), 128, 0, st>>>(need_f ? F(l.hist[0]) : nullptr, part_f, need_b ? F(l.hist[1]) : nullptr,
+                                                 (out_alpha || out_post) ? F(l.cum[0]) : nullptr,
+                                                 need_b ? F(l.cum[1]) : nullptr, need_f ? llbuf : nullptr, (int)N, T, ntile);
+  if (out_post || out_alpha || out_beta) {
+    HMM_REQUIRE(N * (size_t)T < 2147483647ull, "dense: k*B*T too large for one launch");
+    finish_kernel<<<(unsigned)(N * T), 128, 0, st>>>(need_f ? out_alpha : nullptr, need_b ? out_beta : nullptr, out_post,
+                                                     F(l.hist[0]), part_f, F(l.cum[0]), F(l.cum[1]), llbuf, (int)N, T, q, ntile,
+                                                     (flags & HMM_B200_NO_LOGLIK) ? 1 : 0);
+  }
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int cell_step(const float* E, const float* scaled, const float* loglik, const float* A, int k, int n, int qc, int q, int reverse,
+              int init, float* out, float* new_scaled, float* new_loglik, cudaStream_t st) {
+  HMM_REQUIRE(E && scaled && loglik && A && out && new_scaled && new_loglik, "cell_step: null pointer");
+  HMM_REQUIRE(k > 0 && n > 0 && q > 0 && (qc == 1 || qc == q), "cell_step: bad shape (k=%d n=%d qc=%d q=%d)", k, n, qc, q);
+  const size_t rows = (size_t)k * n * qc;
+  HMM_REQUIRE(rows < 2147483647ull, "cell_step: too many rows");
+  const int threads = q >= 128 ? 128 : (q >= 64 ? 64 : 32);
+  cell_step_kernel<<<(unsigned)rows, threads, (q + 32) * sizeof(float), st>>>(E, scaled, loglik, A, out, new_scaled, new_loglik, k, n,
+                                                                            qc, q, reverse, init);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace dense
+}  // namespace hmm
+
+extern "C" {
+
+size_t hmm_b200_dense_workspace_size(int num_models, int batch, int T, int q) {
+  return hmm::dense::workspace_size(num_models, batch, T, q);
+}
+
+int hmm_b200_dense_run(const float* E, const float* A, const float* A_transposed, const float* pi, int num_models, int batch, int T,
+                       int q, unsigned flags, float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                       void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::dense::run(E, A, A_transposed, pi, num_models, batch, T, q, flags, out_post, out_alpha, out_beta, loglik, workspace,
+                         workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_cell_step(const float* E_t, const float* scaled, const float* loglik, const float* A, int num_models, int n,
+                       int qc, int q, int reverse, int init, float* out, float* new_scaled, float* new_loglik, void* stream) {
+  return hmm::dense::cell_step(E_t, scaled, loglik, A, num_models, n, qc, q, reverse, init, out, new_scaled, new_loglik,
+                               static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -121,3 +121,55 @@ def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
         _lib.check(lib.hmm_b200_genepred_emission(_ptr(inputs), k, B, T, _ptr(Bfull), _ptr(codon), _ptr(end_hints),
                                                   TRAINING if training else 0, _ptr(E), _stream()))
     return E
+
+
+def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_loglik=False):
+    """Generic dense HMM evaluation from materialised emissions E (k,B,T,q), A (k,q,q), pi (k,q).
+    Returns dict with the requested tensors ('post','alpha','beta' each (k,B,T,q)) and 'loglik' (k,B)."""
+    lib = _lib.load()
+    if not isinstance(E, torch.Tensor) or E.dim() != 4:
+        raise ValueError("E must be a (num_models, batch, T, q) tensor")
+    k, B, T, q = E.shape
+    E = _req(E, "E")
+    dev = E.device
+    A = _req(A, "A", (k, q, q)); pi = _req(pi.reshape(k, q), "pi", (k, q))
+    need_b = want_post or want_beta
+    At = A.transpose(1, 2).contiguous() if need_b else None
+    with torch.cuda.device(dev):
+        res = {"loglik": torch.empty((k, B), dtype=torch.float32, device=dev)}
+        alpha = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if (want_alpha or want_post) else None
+        beta = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if need_b else None
+        post = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if want_post else None
+        ws = _workspace(lib.hmm_b200_dense_workspace_size(k, B, T, q), dev)
+        _lib.check(lib.hmm_b200_dense_run(_ptr(E), _ptr(A), _ptr(At), _ptr(pi), k, B, T, q, NO_LOGLIK if no_loglik else 0,
+                                          _ptr(post), _ptr(alpha), _ptr(beta), _ptr(res["loglik"]), _ptr(ws), ws.numel(), _stream()))
+    if want_post:
+        res["post"] = post
+    if want_alpha:
+        res["alpha"] = alpha
+    if want_beta:
+        res["beta"] = beta
+    return res
+
+
+def cell_step(emission_probs, scaled, loglik, A, num_models, reverse=False, init=False):
+    """One HmmCell.forward call (reference MsaHmmCell.py:73-106).  emission_probs (k*n, q); scaled (k*n, qc*q);
+    loglik (k*n, qc); A (k,q,q) already oriented.  Returns (output (k*n, qc*q+qc), new_scaled, new_loglik)."""
+    lib = _lib.load()
+    A = _req(A, "A")
+    q = A.shape[-1]
+    E = _req(emission_probs, "emission_probs").reshape(-1, q)
+    rows = E.shape[0]
+    scaled = _req(scaled, "scaled").reshape(rows, -1)
+    qc = scaled.shape[1] // q
+    loglik = _req(loglik, "loglik").reshape(rows, qc)
+    if rows % num_models or scaled.shape[1] != qc * q or qc not in (1, q):
+        raise ValueError(f"inconsistent cell state shapes: E {tuple(E.shape)}, scaled {tuple(scaled.shape)}, q={q}")
+    dev = E.device
+    with torch.cuda.device(dev):
+        out = torch.empty((rows, qc * q + qc), dtype=torch.float32, device=dev)
+        ns = torch.empty((rows, qc * q), dtype=torch.float32, device=dev)
+        nl = torch.empty((rows, qc), dtype=torch.float32, device=dev)
+        _lib.check(lib.hmm_b200_cell_step(_ptr(E), _ptr(scaled), _ptr(loglik), _ptr(A.contiguous()), num_models, rows // num_models,
+                                          qc, q, 1 if reverse else 0, 1 if init else 0, _ptr(out), _ptr(ns), _ptr(nl), _stream()))
+    return out, ns, nl

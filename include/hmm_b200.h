@@ -86,6 +86,38 @@ int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, i
                                const float* Bfull, const float* codon5, const float* end_hints,
                                unsigned flags, float* out_E, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Generic dense-transition HMM (any q: profile HMMs q = 2L+3, multi-copy gene models q = 1+14k) from a
+ * materialised emission tensor.  Replaces, for cells whose plugins are not the fused 15-state gene model:
+ *   HmmCell.forward + BaseRNN loop     MsaHmmCell.py:73-106, BaseRNN.py:216-227
+ *   Transitioner.__call__ (x.A, x.A^T) Transitioner.py:320-331, gene_pred_hmm_transitioner.py:114-125
+ *   _forward_recursion_impl / _backward_recursion_impl / _state_posterior_log_probs_impl (parallel_factor = 1
+ *   semantics)                         MsaHMMLayer.py:227-282, 322-381, 422-521
+ *
+ *   E            (num_models, batch, T, q)   emission probabilities (cell.emission_probs)
+ *   A            (num_models, q, q)          transition matrix;  A_transposed: its transpose (backward pass), may be
+ *                                            NULL when neither out_beta nor out_post is requested
+ *   pi           (num_models, q)
+ *   out_alpha / out_beta (num_models, batch, T, q): log alpha / log beta; out_post needs BOTH buffers (they hold
+ *                the per-step vectors; pass scratch for the one you do not want back)
+ *   loglik       (num_models, batch), may be NULL
+ *   flags        HMM_B200_NO_LOGLIK
+ * --------------------------------------------------------------------------------------------------------- */
+size_t hmm_b200_dense_workspace_size(int num_models, int batch, int T, int q);
+
+int hmm_b200_dense_run(const float* E, const float* A, const float* A_transposed, const float* pi,
+                       int num_models, int batch, int T, int q, unsigned flags,
+                       float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* One HmmCell.forward call (MsaHmmCell.py:73-106), for API parity with code that drives the cell step by step.
+ *   E_t (num_models*n, q); scaled (num_models*n, qc*q); loglik (num_models*n, qc), qc = 1 or q (chunked form);
+ *   A (num_models, q, q) already oriented (A forward, A^T reverse); init = 1 skips the transition (:77-78)
+ *   out (num_models*n, qc*q + qc) = [log a-hat | loglik] forward, [log R | old loglik] reverse (:96-103) */
+int hmm_b200_cell_step(const float* E_t, const float* scaled, const float* loglik, const float* A,
+                       int num_models, int n, int qc, int q, int reverse, int init,
+                       float* out, float* new_scaled, float* new_loglik, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
