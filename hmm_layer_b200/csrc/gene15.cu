@@ -1171,7 +1171,10 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
       const int ci = divL(a, pos);
       const int off = ci * CS + (pos - ci * L) * QP;
       const float f = Yf[off + j], r = Yr[off + j];
-      if (a.out_post) a.out_post[obase + i] = __logf(fmaxf((f * X[off + 1]) * (r * X[off + 2]), 1e-37f)) + X[off];
+      // two logs: the product of a floor-level alpha-hat (>= 1e-32) and a floor-level R (>= 1e-16) leaves the
+      // float range, its logarithm does not
+      if (a.out_post)
+        a.out_post[obase + i] = (__logf(fmaxf(f * X[off + 1], 1e-37f)) + __logf(fmaxf(r * X[off + 2], 1e-37f))) + X[off];
       if (a.out_alpha)
         a.out_alpha[obase + i] = (float)((double)__logf(fmaxf(f, 1e-37f)) + (double)(__float_as_int(Yf[off + 15]) + S.hef[G + ci]) * LN2D);
       if (a.out_beta)

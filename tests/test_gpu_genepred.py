@@ -97,14 +97,15 @@ def test_flags_hints_models():
         if kw.get("no_loglik"):
             # log_post + loglik is ~ -5500 here: float32 resolves that to 4.9e-4, so the un-normalised output
             # carries that quantisation (the reference's own output format has the same property)
-            # (the posterior-only kernel multiplies alpha-hat and R before the log and floors the product at
-            # 1e-37 before dividing by z = sum_q alpha-hat*R (z can be ~1e-3): log posteriors below about -75 are
-            # reported as -78 .. -87, so compare above -70)
+            # States whose posterior lies below the eps = 1e-16 floor of the recursion (MsaHmmCell.py:87-88) are made of
+            # floor injections; the chunk boundary vectors come from floor-free transfer-matrix products (as in the
+            # reference's own parallel_factor > 1 route), so log-space parity is asserted above the floor
+            # (log p > -30) and floor-level states only have to stay floor-level.
             gp = got["post"] - got["loglik"][..., None, None]
             rp = ref["log_post"] - ref["loglik"][..., None, None]
-            vis = rp > -70
+            vis = rp > -30
             np.testing.assert_allclose(gp[vis], rp[vis], rtol=0, atol=5e-3)
-            assert (gp[~vis] < -65).all()
+            assert (gp[~vis] < -28).all()
             got = dict(got, post=got["post"] - got["loglik"][..., None, None])
             ref = dict(ref, log_post=ref["log_post"] - ref["loglik"][..., None, None])
             tol_dp = 5e-4
