@@ -11,7 +11,8 @@ LIB_PATH = os.environ.get("HMM_B200_LIB", os.path.join(_HERE, "libhmm_b200.so"))
 EXPORTS = [
     "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read", "hmm_b200_debug_phases",
     "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_prepare_codon", "hmm_b200_genepred_run",
-    "hmm_b200_genepred_emission", "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_cell_step",
+    "hmm_b200_genepred_emission", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
+    "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_cell_step",
 ]
 
 _lib = None
@@ -44,6 +45,11 @@ def load():
                                           ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
     lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,
                                                ctypes.c_uint, c_fp, c_fp]
+    ci = ctypes.c_int
+    lib.hmm_b200_genepred_shard_reduce.argtypes = [c_fp, ci, ci, ci, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_uint,
+                                                   c_fp, c_fp, ctypes.c_size_t, c_fp]
+    lib.hmm_b200_genepred_shard_finalize.argtypes = [c_fp, ci, ci, ci, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_uint,
+                                                     c_fp, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
     lib.hmm_b200_dense_workspace_size.restype = ctypes.c_size_t
     lib.hmm_b200_dense_workspace_size.argtypes = [ctypes.c_int] * 4
     lib.hmm_b200_dense_run.argtypes = [c_fp, c_fp, c_fp, c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,

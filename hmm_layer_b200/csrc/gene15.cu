@@ -88,6 +88,7 @@ struct Args {
   const float* in_f;  // [NB][16] boundary entering this shard, slot 15 = exponent bits (NULL: pi)     multi-GPU
   const float* in_r;  // [NB][16] boundary leaving this shard (NULL: ones)
   float* llws;        // [NB] log-likelihood
+  int ll_external;    // the log-likelihood in llws comes from the cross-shard scan: boundary_kernel leaves it alone
   long long* dbg;     // optional phase timestamps (tools/phase_times.py), normally NULL
   float* out_post;
   float* out_alpha;
@@ -813,7 +814,7 @@ __global__ void __launch_bounds__(KB_WARPS * 32) boundary_kernel(const Args a, i
       __syncwarp();
     }
     const float tot = half_sum(h.v);
-    if (lane == 0) {
+    if (lane == 0 && !a.ll_external) {
       const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
       a.llws[n] = ll;
       if (a.loglik) a.loglik[n] = ll;
@@ -836,6 +837,43 @@ __global__ void __launch_bounds__(KB_WARPS * 32) boundary_kernel(const Args a, i
       matvec(stg, S.ones, hl, hi, true, h);
       __syncwarp();
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K_S: sequence sharding over GPUs.  blocks[w][n] = ordered product of all tile matrices of shard w of sequence n
+// (boundary_kernel mode 1 on every rank, then one all-gather).  One warp per sequence folds them into the boundary
+// vector entering this shard (pi . M_0 ... M_{rank-1}), the one leaving it (M_{rank+1} ... M_{W-1} . 1) and the
+// log-likelihood of the whole sequence: the TotalProbabilityCell scan (TotalProbabilityCell.py:30-49) across ranks.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) shard_boundary_kernel(const float* __restrict__ blocks, int rank, int world, int NB, int batch,
+                                                            const float* __restrict__ pi, float* __restrict__ in_f,
+                                                            float* __restrict__ in_r, float* __restrict__ llws,
+                                                            float* __restrict__ loglik) {
+  __shared__ __align__(16) float stg[2][BSZ];
+  __shared__ float ones[QP];
+  const int n = blockIdx.x, m = n / batch, lane = threadIdx.x, hl = lane & 15, hi = lane >> 4;
+  if (lane < QP) ones[lane] = 1.f;
+  HV h;
+  h.v = (hl < Q) ? (hi == 0 ? __ldg(pi + m * Q + hl) : 1.f) : 0.f;
+  h.e = 0;
+  __syncwarp();
+  for (int it = 0; it < world; ++it) {
+    // forward half: shards 0, 1, ... (snapshot when reaching this rank); backward half: shards W-1 ... rank+1
+    if (hi == 0 && it == rank) in_f[(size_t)n * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+    const int s = hi == 0 ? it : world - 1 - it;
+    const bool act = hi == 0 ? true : (s > rank);
+    hw_stage_block(stg[hi], blocks + ((size_t)(act ? s : rank) * NB + n) * MAT, hl);
+    __syncwarp();
+    matvec(stg[hi], ones, hl, hi, act, h);
+    __syncwarp();
+  }
+  if (hi == 1) in_r[(size_t)n * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+  const float tot = half_sum(h.v);
+  if (lane == 0) {
+    const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+    llws[n] = ll;
+    if (loglik) loglik[n] = ll;
   }
 }
 
@@ -1278,7 +1316,7 @@ static int choose_L(int NB, int T, bool full) {
 }
 
 struct Layout {
-  size_t Mh, Mt, bvf, bvr, llws, total;
+  size_t Mh, Mt, bvf, bvr, llws, inf, inr, total;
 };
 static Layout layout(int NB, int P) {
   Layout l;
@@ -1289,6 +1327,8 @@ static Layout layout(int NB, int P) {
   l.bvf = off;  off = align_up(off + NP * QP * sizeof(float), 256);
   l.bvr = off;  off = align_up(off + NP * QP * sizeof(float), 256);
   l.llws = off; off = align_up(off + (size_t)NB * sizeof(float), 256);
+  l.inf = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
+  l.inr = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
   l.total = off;
   return l;
 }
@@ -1337,11 +1377,16 @@ static void set_L(Args& a, int L) {
   a.P = cdiv(a.C, G);
 }
 
+// raises a kernel's dynamic shared memory limit when this call needs more than any earlier one (slot = kernel id)
+static size_t g_smem_set[5] = {0, 0, 0, 0, 0};
 template <typename K>
-static int set_smem(K kernel, size_t bytes) {
+static int set_smem(K kernel, int slot, size_t bytes) {
+  if (bytes <= g_smem_set[slot]) return 0;
   HMM_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  g_smem_set[slot] = bytes;
   return 0;
 }
+enum { SLOT_K1 = 0, SLOT_K2P = 1, SLOT_K2F = 2, SLOT_KB = 3, SLOT_EM = 4 };
 
 static int k2_threads_for(int L) {
   if (g_k2_threads > 0) return g_k2_threads;
@@ -1386,11 +1431,10 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = loglik;
 
   const size_t sm1 = k1_smem_bytes(a.L), sm2 = k2_smem_bytes(a.L, full);
-  static size_t att1 = 0, att2p = 0, att2f = 0, attb = 0;
-  if (sm1 > att1) { rc = set_smem(products_kernel, sm1); if (rc) return rc; att1 = sm1; }
-  if (need_k2 && !full && sm2 > att2p) { rc = set_smem(finalize_kernel<false>, sm2); if (rc) return rc; att2p = sm2; }
-  if (need_k2 && full && sm2 > att2f) { rc = set_smem(finalize_kernel<true>, sm2); if (rc) return rc; att2f = sm2; }
-  if (!a.top_inline && attb == 0) { rc = set_smem(boundary_kernel, sizeof(KBSmem)); if (rc) return rc; attb = sizeof(KBSmem); }
+  rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
+  if (need_k2 && !full) { rc = set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc; }
+  if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
+  if (!a.top_inline) { rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc; }
 
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
   products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
@@ -1410,6 +1454,85 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   return 0;
 }
 
+// ---- sequence sharding (multi-GPU): this rank holds positions [seq_off, seq_off + T) of every sequence -----------
+static int shard_args(Args& a, Layout& l, const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total,
+                      const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                      const float* hints, unsigned flags, void* workspace, size_t workspace_bytes) {
+  int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
+  if (rc) return rc;
+  HMM_REQUIRE(A && pi, "genepred shard: null A / pi");
+  HMM_REQUIRE(seq_off >= 0 && seq_total >= seq_off + T, "genepred shard: positions [%d, %d) outside a sequence of length %d",
+              seq_off, seq_off + T, seq_total);
+  HMM_REQUIRE(halo || (seq_off == 0 && seq_total == T), "genepred shard: a proper shard needs the 2+2 halo nucleotides");
+  a.seq_off = seq_off; a.seq_total = seq_total; a.halo = halo;
+  const int NB = num_models * batch;
+  set_L(a, choose_L(NB, T, true));   // one chunk length for both calls, whatever outputs are requested later
+  a.top_inline = 0;
+  l = layout(NB, a.P);
+  if (!workspace || workspace_bytes < l.total) {
+    set_error("genepred shard: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
+    return HMM_B200_EWORKSPACE;
+  }
+  HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred shard: workspace must be 256-byte aligned");
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  a.Mh = reinterpret_cast<float*>(ws + l.Mh);
+  a.Mt = reinterpret_cast<float*>(ws + l.Mt);
+  a.bvf = reinterpret_cast<float*>(ws + l.bvf); a.bvr = reinterpret_cast<float*>(ws + l.bvr);
+  a.llws = reinterpret_cast<float*>(ws + l.llws);
+  return 0;
+}
+
+int shard_reduce(const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total, const float* halo,
+                 const float* A, const float* pi, const float* Bfull, const float* codon5, const float* hints, unsigned flags,
+                 float* block_out, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  Layout l;
+  int rc = shard_args(a, l, inputs, num_models, batch, T, seq_off, seq_total, halo, A, pi, Bfull, codon5, hints, flags, workspace,
+                      workspace_bytes);
+  if (rc) return rc;
+  HMM_REQUIRE(block_out, "genepred shard_reduce: null output");
+  const int NB = num_models * batch;
+  const size_t sm1 = k1_smem_bytes(a.L);
+  rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
+  rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
+  products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
+  boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 1, block_out);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int shard_finalize(const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total, const float* halo,
+                   const float* A, const float* pi, const float* Bfull, const float* codon5, const float* hints, unsigned flags,
+                   const float* all_blocks, int rank, int world, float* out_post, float* out_alpha, float* out_beta,
+                   float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  Layout l;
+  int rc = shard_args(a, l, inputs, num_models, batch, T, seq_off, seq_total, halo, A, pi, Bfull, codon5, hints, flags, workspace,
+                      workspace_bytes);
+  if (rc) return rc;
+  HMM_REQUIRE(all_blocks && world > 0 && rank >= 0 && rank < world, "genepred shard_finalize: bad rank %d of %d", rank, world);
+  HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred shard_finalize: no output requested");
+  const int NB = num_models * batch;
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  float* in_f = reinterpret_cast<float*>(ws + l.inf);
+  float* in_r = reinterpret_cast<float*>(ws + l.inr);
+  shard_boundary_kernel<<<NB, 32, 0, st>>>(all_blocks, rank, world, NB, batch, pi, in_f, in_r, a.llws, loglik);
+  a.in_f = in_f; a.in_r = in_r; a.ll_external = 1;
+  a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = nullptr;
+  if (out_post || out_alpha || out_beta) {
+    const bool full = out_alpha || out_beta;
+    const size_t sm2 = k2_smem_bytes(a.L, full);
+    rc = full ? set_smem(finalize_kernel<true>, SLOT_K2F, sm2) : set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc;
+    rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
+    boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 0, nullptr);
+    const int nt = k2_threads_for(a.L);
+    if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
+    else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);
+  }
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int emission(const float* inputs, int num_models, int batch, int T, const float* Bfull, const float* codon5,
              const float* hints, unsigned flags, float* out_E, cudaStream_t st) {
   Args a{};
@@ -1418,8 +1541,7 @@ int emission(const float* inputs, int num_models, int batch, int T, const float*
   HMM_REQUIRE(out_E, "genepred_emission: null output");
   set_L(a, 32);
   const size_t sm = ((sizeof(EmisSmem) + 15) / 16) * 16 + (size_t)G * (a.L * QP + 4) * sizeof(float) + (((size_t)G * a.L + 4 + 15) / 16) * 16;
-  static bool done = false;
-  if (!done) { rc = set_smem(emission_kernel, sm); if (rc) return rc; done = true; }
+  rc = set_smem(emission_kernel, SLOT_EM, sm); if (rc) return rc;
   emission_kernel<<<dim3(a.P, num_models * batch), 512, sm, st>>>(a, out_E);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
@@ -1458,6 +1580,24 @@ int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, i
                                const float* codon5, const float* end_hints, unsigned flags, float* out_E, void* stream) {
   return hmm::gene15::emission(inputs, num_models, batch, T, Bfull, codon5, end_hints, flags, out_E,
                                static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_shard_reduce(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                   const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                   const float* end_hints, unsigned flags, float* block_out, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+  return hmm::gene15::shard_reduce(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
+                                   flags, block_out, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_shard_finalize(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                     const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                     const float* end_hints, unsigned flags, const float* all_blocks, int rank, int world,
+                                     float* out_post, float* out_alpha, float* out_beta, float* loglik, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  return hmm::gene15::shard_finalize(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
+                                     flags, all_blocks, rank, world, out_post, out_alpha, out_beta, loglik, workspace,
+                                     workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

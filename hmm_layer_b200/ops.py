@@ -107,6 +107,66 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
     return res
 
 
+def _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints):
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T_local, 20), got {tuple(inputs.shape)}")
+    k, B, T, _ = inputs.shape
+    if seq_off < 0 or seq_off + T > seq_total:
+        raise ValueError(f"shard [{seq_off}, {seq_off + T}) lies outside a sequence of length {seq_total}")
+    inputs = _req(inputs, "inputs")
+    if halo is None:
+        if seq_off != 0 or T != seq_total:
+            raise ValueError("a proper shard needs the halo nucleotides of its neighbours (sharded.slice_with_halo)")
+    else:
+        halo = _req(halo, "halo", (k * B, 4, 5))
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
+    return k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints
+
+
+def genepred_shard_reduce(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints=None, training=False):
+    """Step 1 of the sequence-sharded evaluation (include/hmm_b200.h): this rank's shard (k,B,T_local,20) reduced to
+    one stored transfer block per sequence.  Returns (block (k*B,256), workspace) — the workspace holds the shard's
+    product trees and must be handed unchanged to genepred_shard_finalize."""
+    lib = _lib.load()
+    k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints = _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints)
+    dev = inputs.device
+    with torch.cuda.device(dev):
+        block = torch.empty((k * B, 256), dtype=torch.float32, device=dev)
+        ws = torch.empty(max(lib.hmm_b200_genepred_workspace_size(k, B, T), 256), dtype=torch.uint8, device=dev)
+        _lib.check(lib.hmm_b200_genepred_shard_reduce(
+            _ptr(inputs), k, B, T, seq_off, seq_total, _ptr(halo), _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+            TRAINING if training else 0, _ptr(block), _ptr(ws), ws.numel(), _stream()))
+    return block, ws
+
+
+def genepred_shard_finalize(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, all_blocks, rank, world, workspace,
+                            end_hints=None, training=False, no_loglik=False, want_post=True, want_alpha=False,
+                            want_beta=False):
+    """Step 3: all_blocks (world, k*B, 256) = the all-gathered blocks of step 1.  Returns the requested tensors for
+    the local positions and 'loglik' (k,B) of the whole sequence."""
+    lib = _lib.load()
+    k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints = _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints)
+    dev = inputs.device
+    all_blocks = _req(all_blocks, "all_blocks", (world, k * B, 256))
+    if not 0 <= rank < world:
+        raise ValueError(f"rank {rank} outside world of {world}")
+    with torch.cuda.device(dev):
+        res = {}
+        for name, want in (("post", want_post), ("alpha", want_alpha), ("beta", want_beta)):
+            if want:
+                res[name] = torch.empty((k, B, T, 15), dtype=torch.float32, device=dev)
+        res["loglik"] = torch.empty((k, B), dtype=torch.float32, device=dev)
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        _lib.check(lib.hmm_b200_genepred_shard_finalize(
+            _ptr(inputs), k, B, T, seq_off, seq_total, _ptr(halo), _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+            flags, _ptr(all_blocks), rank, world, _ptr(res.get("post")), _ptr(res.get("alpha")), _ptr(res.get("beta")),
+            _ptr(res["loglik"]), _ptr(workspace), workspace.numel(), _stream()))
+    return res
+
+
 def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
     lib = _lib.load()
     if inputs.dim() != 4 or inputs.shape[-1] != 20:

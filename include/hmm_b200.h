@@ -87,6 +87,35 @@ int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, i
                                unsigned flags, float* out_E, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * Sequence sharding over GPUs (one genome-length sequence cut into contiguous shards, one per rank).  Replaces
+ * the reference's chunk combine with the chunks living on different devices:
+ *   _get_total_forward_from_chunks / _get_total_backward_from_chunks   MsaHMMLayer.py:285-319, 384-419
+ *   TotalProbabilityCell.forward                                       TotalProbabilityCell.py:30-49
+ *
+ * This rank holds positions [seq_off, seq_off + T_local) of every sequence of total length seq_total.
+ *   inputs     (num_models, batch, T_local, 20)
+ *   halo       (num_models*batch, 4, 5)  nucleotide one-hot rows of positions seq_off-2, seq_off-1, seq_off+T_local,
+ *                                        seq_off+T_local+1 (rows outside the sequence are ignored); the 3-mer windows
+ *                                        reach two positions across a shard edge (gene_pred_hmm_emitter.py:245-249)
+ *   end_hints  apply to positions 0 and seq_total-1 of the whole sequence
+ * Step 1, every rank:  shard_reduce  -> block_out (num_models*batch, 256): the shard's transfer matrix as one
+ *                      stored block (scaled rows, row scales, power-of-two exponent).
+ * Step 2, caller:      ONE all-gather of block_out over the ranks -> all_blocks (world, num_models*batch, 256).
+ * Step 3, every rank:  shard_finalize with the SAME workspace (it holds the shard's product trees from step 1)
+ *                      -> outputs for the local positions; loglik (num_models, batch) of the whole sequence.
+ * --------------------------------------------------------------------------------------------------------- */
+int hmm_b200_genepred_shard_reduce(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                   const float* halo, const float* A, const float* pi, const float* Bfull,
+                                   const float* codon5, const float* end_hints, unsigned flags, float* block_out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
+int hmm_b200_genepred_shard_finalize(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                     const float* halo, const float* A, const float* pi, const float* Bfull,
+                                     const float* codon5, const float* end_hints, unsigned flags, const float* all_blocks,
+                                     int rank, int world, float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Generic dense-transition HMM (any q: profile HMMs q = 2L+3, multi-copy gene models q = 1+14k) from a
  * materialised emission tensor.  Replaces, for cells whose plugins are not the fused 15-state gene model:
  *   HmmCell.forward + BaseRNN loop     MsaHmmCell.py:73-106, BaseRNN.py:216-227

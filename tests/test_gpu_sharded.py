@@ -1,0 +1,87 @@
+"""GPU parity of the sequence-sharded path (BASELINE config 5 shape class): one sequence cut into contiguous shards,
+one stored block per shard exchanged, every shard finalised on its own.  Virtual ranks on one device run the same
+kernels in the same order as the multi-rank path (hmm_layer_b200/sharded.py); the all-gather is a stack."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import hmm_oracle as O
+from hmm_layer_b200 import ops, sharded, synthetic as syn
+from tests.helpers import gene_params, oracle_gene
+from tests.test_gpu_genepred import check_ab, check_post, dev, run_gpu
+
+pytestmark = pytest.mark.gpu
+
+
+def run_sharded(x, world, A, pi, Bfull, tab, **kw):
+    xd = x.cuda()
+    shards = [sharded.slice_with_halo(xd, r, world) for r in range(world)]
+    hints = kw.pop("end_hints", None)
+    if hints is not None:
+        kw["end_hints"] = dev(hints)
+    res = sharded.sequence_sharded_run_local(shards, dev(A), dev(pi), dev(Bfull), ops.prepare_codon(dev(tab)), **kw)
+    torch.cuda.synchronize()
+    out = {k: np.concatenate([r[k].cpu().numpy() for r in res], axis=2) for k in res[0] if k != "loglik"}
+    lls = [r["loglik"].cpu().numpy() for r in res]
+    for ll in lls[1:]:
+        assert np.array_equal(ll, lls[0])          # the log-likelihood of the whole sequence, identical on every rank
+    out["loglik"] = lls[0]
+    return out
+
+
+@pytest.mark.parametrize("B,T,world", [(2, 4000, 2), (1, 4001, 3), (3, 2500, 8), (2, 64, 4), (1, 17, 8), (2, 1000, 1)])
+def test_sharded_matches_oracle_and_unsharded(B, T, world):
+    x = syn.gene_inputs(1, B, T, seed=500 + T, p_n=0.01)
+    A, pi, Bfull, tab = gene_params(pi_random=True)
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    got = run_sharded(x, world, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+    check_post(got, ref)
+    check_ab(got, ref)
+    one = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    np.testing.assert_allclose(got["loglik"], one["loglik"], rtol=1e-6)
+    np.testing.assert_allclose(np.exp(got["post"]), np.exp(one["post"]), atol=2e-5)
+
+
+def test_sharded_hints_flags_and_n_at_shard_edges():
+    """end_hints belong to the first / last position of the WHOLE sequence; N and soft nucleotides sit exactly on the
+    shard edges so that the 3-mer windows of both neighbours read them through the halo."""
+    B, T, world = 2, 1203, 4
+    x = syn.gene_inputs(1, B, T, seed=8, p_n=0.0)
+    for off, n in sharded.shard_bounds(T, world):
+        x[0, 0, max(off - 1, 0), 15:] = torch.tensor([0., 0, 0, 0, 1])
+        x[0, 1, min(off + n, T - 1), 15:] = torch.tensor([.1, .2, .3, .4, 0.])
+    A, pi, Bfull, tab = gene_params()
+    hints = np.random.RandomState(1).rand(1, B, 2, 15) + 0.01
+    for kw in (dict(end_hints=hints), dict(training=True), dict(end_hints=hints, training=True)):
+        ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, **kw)
+        got = run_sharded(x, world, A, pi, Bfull, tab, want_post=True, **kw)
+        check_post(got, ref)
+
+
+def test_config5_shape_properties():
+    """One ~1 Mbp sequence over 8 shards: normalisation everywhere, loglik equal to the unsharded evaluation, and the
+    oracle on the first shard's prefix (the forward direction of a prefix does not depend on what follows; the
+    posterior does, so only log alpha is compared there)."""
+    T, world = 999_900, 8
+    x = syn.gene_inputs(1, 1, T, seed=1234)
+    A, pi, Bfull, tab = gene_params()
+    got = run_sharded(x, world, A, pi, Bfull, tab, want_post=True, want_alpha=True)
+    assert np.isfinite(got["post"]).all()
+    np.testing.assert_allclose(np.exp(got["post"].astype(np.float64)).sum(-1), 1.0, atol=1e-4)
+    one = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    np.testing.assert_allclose(got["loglik"], one["loglik"], rtol=1e-6)
+    assert (np.argmax(got["post"], -1) != np.argmax(one["post"], -1)).mean() < 1e-5
+    n = 3000
+    ref = oracle_gene(x.numpy()[:, :, :n + 2], A, pi, Bfull, tab)   # +2: the 3-mer windows of the last two positions
+    r, g = ref["log_alpha"][:, :, :n], got["alpha"][:, :, :n]
+    big = r - r.max(-1, keepdims=True) > -14
+    assert (np.abs(g - r) / np.maximum(1.0, np.abs(r)))[big].max() < 1e-4
+
+
+def test_shard_argument_validation():
+    A, pi, Bfull, tab = gene_params()
+    x = syn.gene_inputs(1, 1, 100).cuda()
+    with pytest.raises(ValueError):
+        ops.genepred_shard_reduce(x[:, :, :50].contiguous(), None, 0, 100, dev(A), dev(pi), dev(Bfull), dev(tab))   # no halo
+    with pytest.raises(ValueError):
+        ops.genepred_shard_reduce(x, None, 10, 100, dev(A), dev(pi), dev(Bfull), dev(tab))                          # outside
