@@ -12,11 +12,27 @@
 // state(B x q) . A(q x q) with the floor / emission / row-sum epilogue fused.  Normalisation is deferred to the consumer:
 // the step writes a_t (un-normalised) and per-column-tile partial row sums; the next step divides by their sum
 // (deterministic order), so no atomics and bit-reproducible results.  A tcgen05 version of the step GEMM for the
-// learnMSA sizes (q ~ 1000) is the next item of DESIGN.md; this CUDA-core step is the correct baseline it must match.
+// learnMSA sizes (q >= 192) lives in dense_tc.cu and shares this file's scale bookkeeping and finish kernels.
 #include "common.cuh"
 
 namespace hmm {
+namespace dense_tc {   // dense_tc.cu: tcgen05 step for profile-HMM sizes
+bool supported(int k, int B, int q);
+int ntile(int q);
+size_t extra_workspace(int k, int B, int q);
+int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
+              float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st);
+}  // namespace dense_tc
 namespace dense {
+
+// 0 = by size (tensor cores from kTcMinStates states), 1 = CUDA-core step always, 2 = tensor-core step always
+static int g_path = 0;
+constexpr int kTcMinStates = 192;
+void set_path(int p) { g_path = (p == 1 || p == 2) ? p : 0; }
+static bool use_tc(int k, int B, int q) {
+  if (g_path == 1) return false;
+  return dense_tc::supported(k, B, q) && (g_path == 2 || q >= kTcMinStates);
+}
 
 constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;   // 256 threads, 4x4 outputs each
 constexpr int MAXP = 32;                                    // at most 32 column tiles (q <= 2048)
@@ -251,7 +267,7 @@ __global__ void init_state_kernel(float* __restrict__ st, const float* __restric
 }
 
 struct Layout {
-  size_t st[2][2], part[2][2], hist[2], cum[2], ll, total;
+  size_t st[2][2], part[2][2], hist[2], cum[2], ll, extra, total;
 };
 static Layout layout(int k, int B, int T, int q) {
   Layout l;
@@ -265,6 +281,8 @@ static Layout layout(int k, int B, int T, int q) {
   for (int d = 0; d < 2; ++d) { l.hist[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
   for (int d = 0; d < 2; ++d) { l.cum[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
   l.ll = off; off = align_up(off + N * sizeof(float), 256);
+  l.extra = off;
+  if (g_path != 1 && dense_tc::supported(k, B, q)) off += dense_tc::extra_workspace(k, B, q);
   l.total = off;
   return l;
 }
@@ -286,7 +304,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "dense: no output requested");
   const bool need_f = out_post || out_alpha || loglik, need_b = out_post || out_beta;
   HMM_REQUIRE(!out_post || (out_alpha && out_beta), "dense: the posterior needs alpha and beta buffers (scratch is fine)");
-  HMM_REQUIRE(!need_b || At, "dense: the backward pass needs A^T");
+  HMM_REQUIRE(!need_b || At || use_tc(k, B, q), "dense: the backward pass needs A^T");
   const Layout l = layout(k, B, T, q);
   if (!workspace || workspace_bytes < l.total) {
     set_error("dense: workspace too small (%zu < %zu bytes)", workspace_bytes, l.total);
@@ -294,13 +312,20 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   }
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   auto F = [&](size_t o) { return reinterpret_cast<float*>(ws + o); };
-  const int ntile = cdiv(q, BN);
+  const bool tc = use_tc(k, B, q);
+  const int ntile = tc ? dense_tc::ntile(q) : cdiv(q, BN);
   const size_t N = (size_t)k * B;
   const dim3 grid(ntile, cdiv(B, BM), k);
   const int ib = 256, ig = (int)((N * q + ib - 1) / ib);
   float* llbuf = loglik ? loglik : F(l.ll);
 
-  for (int d = 0; d < 2; ++d) {
+  if (tc) {
+    float* part[2][2] = {{F(l.part[0][0]), F(l.part[0][1])}, {F(l.part[1][0]), F(l.part[1][1])}};
+    float* hist[2] = {F(l.hist[0]), F(l.hist[1])};
+    const int rc = dense_tc::run_steps(E, A, pi, k, B, T, q, need_f, need_b, out_alpha, out_beta, part, hist, ws + l.extra, st);
+    if (rc) return rc;
+  }
+  for (int d = 0; d < 2 && !tc; ++d) {
     if ((d == 0 && !need_f) || (d == 1 && !need_b)) continue;
     init_state_kernel<<<ig, ib, 0, st>>>(F(l.st[d][0]), d == 0 ? pi : nullptr, k, B, q);
     for (int s = 0; s < T; ++s) {
@@ -316,7 +341,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     }
   }
   HMM_CUDA_OK(cudaGetLastError());
-  const float* part_f = F(l.part[0][T & 1]);
+  const float* part_f = F(l.part[0][tc ? ((T - 1) & 1) : (T & 1)]);   // slot written by the last forward step
   cum_kernel<<<cdiv((int)N, 128), 128, 0, st>>>(need_f ? F(l.hist[0]) : nullptr, part_f, need_b ? F(l.hist[1]) : nullptr,
                                                  (out_alpha || out_post) ? F(l.cum[0]) : nullptr,
                                                  need_b ? F(l.cum[1]) : nullptr, need_f ? llbuf : nullptr, (int)N, T, ntile);

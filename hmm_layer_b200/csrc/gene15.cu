@@ -35,6 +35,7 @@
 #include "common.cuh"
 
 namespace hmm {
+namespace dense { void set_path(int p); }
 namespace gene15 {
 
 constexpr int Q = 15;      // states
@@ -1630,8 +1631,8 @@ size_t workspace_size(int num_models, int batch, int T) {
 
 int set_debug_buffer(void* p) { g_dbg = static_cast<long long*>(p); return 0; }
 
-int set_tuning(int L, int k2_threads, int reserved) {
-  (void)reserved;
+int set_tuning(int L, int k2_threads, int dense_path) {
+  hmm::dense::set_path(dense_path);
   if (L < 0 || L > MAX_L || k2_threads < 0 || k2_threads > 512 || (k2_threads & 63) || (k2_threads > 0 && k2_threads < 128)) {
     set_error("tuning rejected: chunk_len in [0,%d], finalize threads a multiple of 64 in [128,512] or 0", MAX_L);
     return HMM_B200_EINVAL;

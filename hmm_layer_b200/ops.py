@@ -40,10 +40,11 @@ def _workspace(nbytes, device):
     return ws
 
 
-def set_tuning(chunk_len=0, finalize_threads=0):
+def set_tuning(chunk_len=0, finalize_threads=0, dense_path=0):
     """chunk_len: positions per chunk (0 = chosen per call from the problem size and the SM count);
-    finalize_threads: threads per CTA of the finalize kernel (0 = derived from chunk_len)."""
-    _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, finalize_threads, 0))
+    finalize_threads: threads per CTA of the finalize kernel (0 = derived from chunk_len);
+    dense_path: step kernel of the generic dense path, 0 = by size, 1 = CUDA cores, 2 = tcgen05 tensor cores."""
+    _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, finalize_threads, dense_path))
 
 
 def profile_enable(on=True):

@@ -34,8 +34,9 @@ const char* hmm_b200_last_error(void);
 
 /* Optional tuning of the chunked scan: chunk length in positions (0 = chosen per call from the problem size and
  * the SM count; at most 48), threads per CTA of the finalize kernel (0 = derived; a multiple of 32 in [128,512]).
- * The third argument is reserved (pass 0).  Process-wide; meant for benchmarking and tests. */
-int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int reserved);
+ * dense_path selects the step kernel of the generic dense path: 0 = by size (tcgen05 tensor-core step from 192 states),
+ * 1 = CUDA-core step always, 2 = tensor-core step always.  Process-wide; meant for benchmarking and tests. */
+int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int dense_path);
 
 /* Per-kernel timing for benchmarks: when enabled, hmm_b200_genepred_run records CUDA events around each of its
  * launches (products, [boundary], finalize); hmm_b200_profile_read waits for the last profiled call and writes up to n

@@ -117,3 +117,37 @@ def test_step_by_step_cell_with_base_rnn_matches_fused_path():
     np.testing.assert_allclose(stT[1].reshape(2, 3).cpu().numpy(), ll.cpu().numpy(), rtol=2e-6)
     big = (la - la.max(-1, keepdim=True).values > -14).cpu().numpy()
     assert np.abs((log_alpha - la).cpu().numpy())[big].max() < 1e-4
+
+
+@pytest.fixture
+def tensor_core_path():
+    ops.set_tuning(0, 0, dense_path=2)
+    yield
+    ops.set_tuning(0, 0, dense_path=0)
+
+
+@pytest.mark.parametrize("k,L,B,T", [(1, 32, 16, 20), (2, 100, 130, 9), (1, 500, 3, 6), (2, 500, 140, 12), (1, 160, 1, 1),
+                                     (1, 700, 5, 3)])
+def test_tensor_core_step_matches_oracle(tensor_core_path, k, L, B, T):
+    """tcgen05 step kernel (dense_tc.cu) forced on: padded rows (B not a multiple of 128), padded columns (q not a
+    multiple of 64 / 256), one and several column tiles, several heads; (2,500,140,12) is config 4's state count."""
+    A, pi, Bm = syn.profile_model(k, L)
+    x = syn.profile_inputs(k, B, T)
+    E = torch.einsum("kbts,kqs->kbtq", x, Bm)
+    ref = O.posterior(E.numpy().astype(np.float64), A.numpy().astype(np.float64), pi.numpy().astype(np.float64))
+    r = ops.dense_run(E.cuda(), A.cuda(), pi.cuda(), want_post=True, want_alpha=True, want_beta=True)
+    torch.cuda.synchronize()
+    got = {n: v.cpu().numpy() for n, v in r.items()}
+    rep = O.parity_report(got["post"], got["loglik"], ref["log_post"], ref["loglik"])
+    assert rep["loglik_rel"] < 2e-6 and rep["max_abs_dp"] < 1e-4 and rep["argmax_mismatch"] == 0, rep
+    check_ab(got, ref)
+    only = ops.dense_run(E.cuda(), A.cuda(), pi.cuda())["loglik"].cpu().numpy()       # forward direction alone
+    assert np.array_equal(only, got["loglik"])
+    bonly = ops.dense_run(E.cuda(), A.cuda(), pi.cuda(), want_beta=True)              # loglik + backward
+    assert np.array_equal(bonly["beta"].cpu().numpy(), got["beta"])
+    # the CUDA-core step on the same inputs: same recurrence, fp32 FMA instead of the bf16-pair tensor-core product
+    ops.set_tuning(0, 0, dense_path=1)
+    cc = ops.dense_run(E.cuda(), A.cuda(), pi.cuda(), want_post=True)
+    np.testing.assert_allclose(cc["loglik"].cpu().numpy(), got["loglik"], rtol=2e-6)
+    dp = np.abs(np.exp(cc["post"].cpu().numpy()) - np.exp(got["post"])).max()
+    assert dp < 1e-4, dp
