@@ -18,7 +18,7 @@
 namespace hmm {
 namespace dense_tc {   // dense_tc.cu: tcgen05 step for profile-HMM sizes
 bool supported(int k, int B, int q);
-int ntile(int q);
+int slots(int q);
 size_t extra_workspace(int k, int B, int q);
 int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
               float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st);
@@ -271,7 +271,7 @@ struct Layout {
 };
 static Layout layout(int k, int B, int T, int q) {
   Layout l;
-  const int ntile = cdiv(q, BN);
+  const int ntile = cdiv(q, BN) > dense_tc::slots(q) ? cdiv(q, BN) : dense_tc::slots(q);
   const size_t N = (size_t)k * B;
   size_t off = 0;
   for (int d = 0; d < 2; ++d)
@@ -313,7 +313,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   auto F = [&](size_t o) { return reinterpret_cast<float*>(ws + o); };
   const bool tc = use_tc(k, B, q);
-  const int ntile = tc ? dense_tc::ntile(q) : cdiv(q, BN);
+  const int ntile = tc ? dense_tc::slots(q) : cdiv(q, BN);
   const size_t N = (size_t)k * B;
   const dim3 grid(ntile, cdiv(B, BM), k);
   const int ib = 256, ig = (int)((N * q + ib - 1) / ib);

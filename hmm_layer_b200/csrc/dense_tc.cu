@@ -9,9 +9,9 @@
 // k-block issues three MMAs (hi.hi + hi.lo + lo.hi) into the same accumulator; the dropped lo.lo term is 2^-16 relative.
 // The state pair of step t+1 is written by the epilogue of step t, the transition pair once per call.
 //
-// One launch per time step covers both directions (forward t = s, backward t = T-1-s), all heads and all row blocks.
-// Warp roles: warp 0 = TMA producer (one lane), warp 1 = TMEM allocation + MMA issue (one lane), warps 2..5 = epilogue
-// (TMEM lane quarter = warp % 4).  Operand tiles are [rows][64] bf16 = 128-byte rows in the 128-byte-swizzled K-major
+// One persistent launch runs every time step of both directions (forward t = s, backward t = T-1-s), see chain_kernel.
+// Warp roles: warp 0 = TMA producer (one lane), warp 1 = TMEM allocation + MMA issue (one lane), warps 2..9 = epilogue
+// (TMEM lane quarter = warp % 4, two warps per quarter).  Operand tiles are [rows][64] bf16 = 128-byte rows in the 128-byte-swizzled K-major
 // layout, written by TMA and described to the MMA by shared-memory descriptors (SBO = 1024 B, +32 B per UMMA_K = 16).
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -26,11 +26,13 @@ constexpr int B_TILE = TBN * TBK * 2;                    // 32 KB  (one bf16 til
 constexpr int STAGE_BYTES = 2 * A_TILE + 2 * B_TILE;     // hi + lo of both operands = 96 KB
 constexpr int STG_PITCH = 33;
 constexpr int STG_WARP = 32 * STG_PITCH;                 // floats per epilogue warp
-constexpr int STG_BYTES = 4 * STG_WARP * 4;
+constexpr int EPI_WARPS = 8;                             // two per TMEM lane quarter, each owns half of the tile's columns
+constexpr int STG_BYTES = EPI_WARPS * STG_WARP * 4;
 constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + STG_BYTES + 128;
-constexpr int THREADS = 192;
-constexpr uint32_t TMEM_COLS = 256;
+constexpr int THREADS = 64 + EPI_WARPS * 32;
+constexpr uint32_t TMEM_COLS = 512;                      // two 256-column accumulators
 constexpr int MAXP = 32;
+static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 struct Args {
   const float* E;        // (k, B, T, q)
@@ -38,8 +40,9 @@ struct Args {
   float* store[2];       // per direction (k, B, T, q) or null: a_t (forward) / R_t (backward), un-normalised
   float* part[2][2];     // per direction, ping-pong: (k, B, ntile) partial row sums
   float* hist[2];        // per direction (k, B, T)
-  int k, B, T, q, s, ntile, Bpad, Npad, nkb;
-  int dir0, ndir;
+  unsigned* cnt;         // [chain][dir] CTAs of the chain that finished a step (zeroed per call)
+  int k, B, T, q, ntile, ntile_n, Bpad, Npad, nkb;   // ntile = partial-sum slots per row = 2 per column tile
+  int dir0, ndir, chain0, nrb;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -113,25 +116,47 @@ __device__ __forceinline__ size_t state_off(const Args& a, int dir, int pp, int 
   return (size_t)((dir * 2 + pp) * 2 + hl) * a.k * a.Bpad * (size_t)a.Npad;
 }
 
+// ---- cross-CTA step counters (one per chain and direction, counts CTAs that finished a step) -------------------------
+__device__ __forceinline__ unsigned ld_acquire(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void wait_count(const unsigned* p, unsigned want) {
+  for (uint32_t it = 0; it < (1u << 24); ++it) {
+    if (ld_acquire(p) >= want) return;
+    __nanosleep(64);
+  }
+  __trap();
+}
+__device__ __forceinline__ void proxy_fence_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+
+// Persistent kernel: CTA (j, c) owns column tile j of chain c = (head, block of 128 sequences) for ALL time steps and both
+// directions.  Its work items alternate forward step s / backward step s / forward step s+1 ...; item i accumulates into
+// TMEM buffer i & 1, so the epilogue of one direction runs under the MMAs of the other.  The only cross-CTA dependency
+// is inside a chain: step s+1 of a direction needs the state columns the chain's other column tiles wrote at step s;
+// each CTA bumps cnt[chain][dir] when its epilogue is done and the TMA producer waits for ntile * s before it loads the
+// state operand (the transition operand does not wait).  All CTAs of a launch are co-resident (cooperative launch).
 __global__ void __launch_bounds__(THREADS, 1)
-step_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmA, const Args a) {
+chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmA, const Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   float* stg_all = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + STG_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + STAGES), tfull = smem_u32(bars + 2 * STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + STAGES);
+  const uint32_t tfull0 = smem_u32(bars + 2 * STAGES), tempty0 = smem_u32(bars + 2 * STAGES + 2);
   const uint32_t stage0 = smem_u32(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int dir = a.dir0 + (int)blockIdx.z / a.k, m = (int)blockIdx.z % a.k;
-  const int row0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
-  const int pp = (a.s + 1) & 1;   // slot written by step s-1 (the first step, s = 0, is init_kernel -> slot 0)
-  const int t = dir == 0 ? a.s : a.T - 1 - a.s;
+  const int chain = a.chain0 + (int)blockIdx.y;
+  const int m = chain / a.nrb, row0 = (chain % a.nrb) * TBM, n0 = blockIdx.x * TBN;
+  const int nitems = (a.T - 1) * a.ndir;
+  const unsigned* cnt_r = a.cnt + (size_t)chain * 2;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
-    mbar_init(tfull, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(tfull0 + 8 * i, 1); mbar_init(tempty0 + 8 * i, EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -146,124 +171,168 @@ step_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUt
 
   if (warp == 0) {
     if (lane == 0) {
-      const int rS_hi = (int)(((size_t)((dir * 2 + pp) * 2 + 0) * a.k + m) * a.Bpad) + row0;
-      const int rS_lo = (int)(((size_t)((dir * 2 + pp) * 2 + 1) * a.k + m) * a.Bpad) + row0;
-      const int rA_hi = (int)(((size_t)(dir * 2 + 0) * a.k + m) * a.Npad) + n0;
-      const int rA_lo = (int)(((size_t)(dir * 2 + 1) * a.k + m) * a.Npad) + n0;
-      for (int kb = 0; kb < a.nkb; ++kb) {
-        const int st = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(empty0 + 8 * st, ph ^ 1u);
-        const uint32_t fb = full0 + 8 * st, sb = stage0 + st * STAGE_BYTES;
-        mbar_expect_tx(fb, STAGE_BYTES);
-        tma_load_2d(sb, &tmS, fb, kb * TBK, rS_hi);
-        tma_load_2d(sb + A_TILE, &tmS, fb, kb * TBK, rS_lo);
-        tma_load_2d(sb + 2 * A_TILE, &tmA, fb, kb * TBK, rA_hi);
-        tma_load_2d(sb + 2 * A_TILE + B_TILE, &tmA, fb, kb * TBK, rA_lo);
+      int kbg = 0;
+      for (int it = 0; it < nitems; ++it) {
+        const int s = 1 + it / a.ndir, dir = a.dir0 + it % a.ndir, pp = (s + 1) & 1;
+        const int rS_hi = (int)(((size_t)((dir * 2 + pp) * 2 + 0) * a.k + m) * a.Bpad) + row0;
+        const int rS_lo = (int)(((size_t)((dir * 2 + pp) * 2 + 1) * a.k + m) * a.Bpad) + row0;
+        const int rA_hi = (int)(((size_t)(dir * 2 + 0) * a.k + m) * a.Npad) + n0;
+        const int rA_lo = (int)(((size_t)(dir * 2 + 1) * a.k + m) * a.Npad) + n0;
+        for (int kb = 0; kb < a.nkb; ++kb, ++kbg) {
+          const int st = kbg % STAGES;
+          const uint32_t ph = (uint32_t)(kbg / STAGES) & 1u;
+          mbar_wait(empty0 + 8 * st, ph ^ 1u);
+          const uint32_t fb = full0 + 8 * st, sb = stage0 + st * STAGE_BYTES;
+          mbar_expect_tx(fb, STAGE_BYTES);
+          tma_load_2d(sb + 2 * A_TILE, &tmA, fb, kb * TBK, rA_hi);
+          tma_load_2d(sb + 2 * A_TILE + B_TILE, &tmA, fb, kb * TBK, rA_lo);
+          if (kb == 0 && s >= 2) {   // the chain's column tiles must all have written step s-1 of this direction
+            wait_count(cnt_r + dir, (unsigned)(a.ntile_n * (s - 1)));
+            proxy_fence_global();
+          }
+          tma_load_2d(sb, &tmS, fb, kb * TBK, rS_hi);
+          tma_load_2d(sb + A_TILE, &tmS, fb, kb * TBK, rS_lo);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      for (int kb = 0; kb < a.nkb; ++kb) {
-        const int st = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(full0 + 8 * st, ph);
+      int kbg = 0;
+      for (int it = 0; it < nitems; ++it) {
+        const int buf = it & 1;
+        mbar_wait(tempty0 + 8 * buf, (((uint32_t)it >> 1) & 1u) ^ 1u);   // the epilogue drained this accumulator
         tc_fence_after();
-        const uint32_t sb = stage0 + st * STAGE_BYTES;
+        const uint32_t acc = tmem + (uint32_t)(buf * TBN);
+        for (int kb = 0; kb < a.nkb; ++kb, ++kbg) {
+          const int st = kbg % STAGES;
+          const uint32_t ph = (uint32_t)(kbg / STAGES) & 1u;
+          mbar_wait(full0 + 8 * st, ph);
+          tc_fence_after();
+          const uint32_t sb = stage0 + st * STAGE_BYTES;
 #pragma unroll
-        for (int k4 = 0; k4 < TBK / UK; ++k4) {
-          const uint32_t ko = k4 * UK * 2;   // bytes along K inside the 128-byte swizzle atom
-          const uint64_t s_hi = smem_desc(sb + ko), s_lo = smem_desc(sb + A_TILE + ko);
-          const uint64_t a_hi = smem_desc(sb + 2 * A_TILE + ko), a_lo = smem_desc(sb + 2 * A_TILE + B_TILE + ko);
-          tc_mma(tmem, s_lo, a_hi, kIdesc, (kb | k4) ? 1u : 0u);
-          tc_mma(tmem, s_hi, a_lo, kIdesc, 1u);
-          tc_mma(tmem, s_hi, a_hi, kIdesc, 1u);
+          for (int k4 = 0; k4 < TBK / UK; ++k4) {
+            const uint32_t ko = k4 * UK * 2;   // bytes along K inside the 128-byte swizzle atom
+            const uint64_t s_hi = smem_desc(sb + ko), s_lo = smem_desc(sb + A_TILE + ko);
+            const uint64_t a_hi = smem_desc(sb + 2 * A_TILE + ko), a_lo = smem_desc(sb + 2 * A_TILE + B_TILE + ko);
+            tc_mma(acc, s_lo, a_hi, kIdesc, (kb | k4) ? 1u : 0u);
+            tc_mma(acc, s_hi, a_lo, kIdesc, 1u);
+            tc_mma(acc, s_hi, a_hi, kIdesc, 1u);
+          }
+          tc_commit(empty0 + 8 * st);
         }
-        tc_commit(empty0 + 8 * st);
+        tc_commit(tfull0 + 8 * buf);
       }
-      tc_commit(tfull);
     }
   } else {
-    // ---- epilogue: thread = row of the tile (TMEM lane), 8 chunks of 32 columns ----
-    const int qd = warp & 3;
-    float* stg = stg_all + qd * STG_WARP;
+    // ---- epilogue: thread = row of the tile (TMEM lane quarter = warp % 4), warp group ew / 4 = column half --------
+    const int ew = warp - 2, qd = warp & 3, half = ew >> 2;
+    constexpr int CH = TBN / 32 / (EPI_WARPS / 4);   // 32-column chunks per warp
+    float* stg = stg_all + ew * STG_WARP;
     const int rl = qd * 32 + lane, r = row0 + rl;
     const bool valid = r < a.B;
     const size_t seq = (size_t)m * a.B + (valid ? r : 0);
-    float Sin = 0.f;
-    if (valid) {
-      const float* p = a.part[dir][pp] + seq * a.ntile;
-      for (int i = 0; i < a.ntile; ++i) Sin += p[i];
-      if (blockIdx.x == 0) a.hist[dir][seq * a.T + t] = Sin;
-    }
-    const float inv = valid ? 1.0f / Sin : 0.f;
-    const float* Et = a.E + (size_t)t * a.q;          // + ((m*B + row)*T)*q per row
-    float* St = a.store[dir] ? a.store[dir] + (size_t)t * a.q : nullptr;
     const size_t rowpitch = (size_t)a.T * a.q;
     const size_t rbase = ((size_t)m * a.B + row0 + qd * 32) * rowpitch;   // first row of this warp
-    uint16_t* o_hi = a.state + state_off(a, dir, pp ^ 1, 0) + ((size_t)m * a.Bpad + r) * a.Npad + n0;
-    uint16_t* o_lo = a.state + state_off(a, dir, pp ^ 1, 1) + ((size_t)m * a.Bpad + r) * a.Npad + n0;
-    const int rows_here = min(32, a.B - (row0 + qd * 32));   // rows of this warp inside the batch (may be <= 0)
+    const int rows_here = min(32, a.B - (row0 + qd * 32));                // rows of this warp inside the batch (may be <= 0)
+    const int cbase = n0 + half * (CH * 32);
+    const int slot = blockIdx.x * (EPI_WARPS / 4) + half;                 // partial-sum slot of this warp group
 
-    // stage the first emission chunk while the MMAs run
-    {
-      const int col = n0 + lane;
-#pragma unroll 8
-      for (int i = 0; i < 32; ++i)
-        stg[i * STG_PITCH + lane] = (i < rows_here && col < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + col) : 0.f;
-    }
-    __syncwarp();
-    mbar_wait(tfull, 0);
-    tc_fence_after();
-
-    float rsum = 0.f;
-    for (int c = 0; c < TBN / 32; ++c) {
-      uint32_t acc[32];
-      tmem_ld32(tmem + ((uint32_t)(qd * 32) << 16) + (uint32_t)(c * 32), acc);
-      uint32_t hi[16], lo[16];
+    for (int it = 0; it < nitems; ++it) {
+      const int s = 1 + it / a.ndir, dir = a.dir0 + it % a.ndir, pp = (s + 1) & 1, buf = it & 1;
+      const int t = dir == 0 ? s : a.T - 1 - s;
+      const float* Et = a.E + (size_t)t * a.q;
+      float* St = a.store[dir] ? a.store[dir] + (size_t)t * a.q : nullptr;
+      float ereg[32];
+      {
+        const int col = cbase + lane;
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        float x2[2];
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int col = n0 + c * 32 + j + u;
-          const float e = stg[lane * STG_PITCH + j + u];
-          const float R = fmaxf(__uint_as_float(acc[j + u]) * inv, kEps);
-          float x = fmaxf(e, kEps) * R;
-          const bool live = valid && col < a.q;
-          x = live ? x : 0.f;
-          stg[lane * STG_PITCH + j + u] = dir ? R : x;
-          rsum += x;
-          x2[u] = x;
-        }
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(x2[0]), h1 = __float2bfloat16_rn(x2[1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(x2[0] - __bfloat162float(h0));
-        const __nv_bfloat16 l1 = __float2bfloat16_rn(x2[1] - __bfloat162float(h1));
-        hi[j >> 1] = pack_bf16(h0, h1);
-        lo[j >> 1] = pack_bf16(l0, l1);
-      }
-#pragma unroll
-      for (int v = 0; v < 4; ++v) {
-        reinterpret_cast<uint4*>(o_hi + c * 32)[v] = make_uint4(hi[4 * v], hi[4 * v + 1], hi[4 * v + 2], hi[4 * v + 3]);
-        reinterpret_cast<uint4*>(o_lo + c * 32)[v] = make_uint4(lo[4 * v], lo[4 * v + 1], lo[4 * v + 2], lo[4 * v + 3]);
-      }
-      __syncwarp();
-      const int col = n0 + c * 32 + lane;
-      if (St && col < a.q) {
-#pragma unroll 8
         for (int i = 0; i < 32; ++i)
-          if (i < rows_here) St[rbase + (size_t)i * rowpitch + col] = stg[i * STG_PITCH + lane];
+          ereg[i] = (i < rows_here && col < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + col) : 0.f;
       }
-      __syncwarp();
-      if (c + 1 < TBN / 32) {
-        const int ncol = col + 32;
-#pragma unroll 8
-        for (int i = 0; i < 32; ++i)
-          stg[i * STG_PITCH + lane] = (i < rows_here && ncol < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + ncol) : 0.f;
+      if (s >= 2) {
+        if (lane == 0) wait_count(cnt_r + dir, (unsigned)(a.ntile_n * (s - 1)));
         __syncwarp();
       }
+      float Sin = 0.f;
+      if (valid) {
+        const float* p = a.part[dir][pp] + seq * a.ntile;
+        for (int i = 0; i < a.ntile; ++i) Sin += __ldcg(p + i);
+        if (blockIdx.x == 0 && half == 0) a.hist[dir][seq * a.T + t] = Sin;
+      }
+      const float inv = valid ? 1.0f / Sin : 0.f;
+      uint16_t* o_hi = a.state + state_off(a, dir, pp ^ 1, 0) + ((size_t)m * a.Bpad + r) * a.Npad + cbase;
+      uint16_t* o_lo = a.state + state_off(a, dir, pp ^ 1, 1) + ((size_t)m * a.Bpad + r) * a.Npad + cbase;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) stg[i * STG_PITCH + lane] = ereg[i];
+      __syncwarp();
+      mbar_wait(tfull0 + 8 * buf, ((uint32_t)it >> 1) & 1u);
+      tc_fence_after();
+
+      float rsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < CH; ++c) {
+        const int col = cbase + c * 32 + lane;
+        if (c + 1 < CH) {   // next chunk's emissions: in flight while this chunk is processed
+          const int ncol = col + 32;
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            ereg[i] = (i < rows_here && ncol < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + ncol) : 0.f;
+        }
+        uint32_t acc[32];
+        tmem_ld32(tmem + ((uint32_t)(qd * 32) << 16) + (uint32_t)(buf * TBN + half * (CH * 32) + c * 32), acc);
+        if (c + 1 == CH) {   // accumulator fully read: hand the buffer back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tempty0 + 8 * buf) : "memory");
+        }
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          float x2[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int cc = cbase + c * 32 + j + u;
+            const float e = stg[lane * STG_PITCH + j + u];
+            const float R = fmaxf(__uint_as_float(acc[j + u]) * inv, kEps);
+            float x = fmaxf(e, kEps) * R;
+            x = (valid && cc < a.q) ? x : 0.f;
+            stg[lane * STG_PITCH + j + u] = dir ? R : x;
+            rsum += x;
+            x2[u] = x;
+          }
+          const __nv_bfloat16 h0 = __float2bfloat16_rn(x2[0]), h1 = __float2bfloat16_rn(x2[1]);
+          const __nv_bfloat16 l0 = __float2bfloat16_rn(x2[0] - __bfloat162float(h0));
+          const __nv_bfloat16 l1 = __float2bfloat16_rn(x2[1] - __bfloat162float(h1));
+          hi[j >> 1] = pack_bf16(h0, h1);
+          lo[j >> 1] = pack_bf16(l0, l1);
+        }
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          reinterpret_cast<uint4*>(o_hi + c * 32)[v] = make_uint4(hi[4 * v], hi[4 * v + 1], hi[4 * v + 2], hi[4 * v + 3]);
+          reinterpret_cast<uint4*>(o_lo + c * 32)[v] = make_uint4(lo[4 * v], lo[4 * v + 1], lo[4 * v + 2], lo[4 * v + 3]);
+        }
+        __syncwarp();
+        if (St && col < a.q) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < rows_here) St[rbase + (size_t)i * rowpitch + col] = stg[i * STG_PITCH + lane];
+        }
+        __syncwarp();
+        if (c + 1 < CH) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) stg[i * STG_PITCH + lane] = ereg[i];
+          __syncwarp();
+        }
+      }
+      if (valid) a.part[dir][pp ^ 1][seq * a.ntile + slot] = rsum;
+      // publish: every epilogue thread's global writes, then one counter bump per CTA
+      proxy_fence_global();
+      asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+      if (threadIdx.x == 64) {
+        __threadfence();
+        atomicAdd(a.cnt + (size_t)chain * 2 + dir, 1u);
+      }
     }
-    if (valid) a.part[dir][pp ^ 1][seq * a.ntile + blockIdx.x] = rsum;
   }
 
   tc_fence_before();
@@ -306,7 +375,7 @@ __global__ void __launch_bounds__(256) init_kernel(const Args a, const float* __
   if (threadIdx.x == 0 && valid) {
     float s = 0.f;
     for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
-    float* p = a.part[dir][0] + seq * a.ntile;   // read as "input sums" by step s = 0 ... which is this one: ping-pong slot 0
+    float* p = a.part[dir][0] + seq * a.ntile;   // ping-pong slot 0 = the sums step 1 divides by
     p[0] = s;
     for (int i = 1; i < a.ntile; ++i) p[i] = 0.f;
     a.hist[dir][seq * a.T + t] = 1.f;
@@ -335,6 +404,7 @@ __global__ void prep_kernel(const float* __restrict__ A, uint16_t* __restrict__ 
 }
 
 // ---- host ----------------------------------------------------------------------------------------------------------
+int slots(int q);
 typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -373,45 +443,61 @@ static int make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t cols, 
 }
 
 struct Dims {
-  int Bpad, Npad, Kpad, ntile;
-  size_t state_bytes, aop_bytes;
+  int Bpad, Npad, Kpad, ntile_n, nrb, nchain;
+  size_t state_bytes, aop_bytes, cnt_bytes;
 };
 static Dims dims(int k, int B, int q) {
   Dims d;
   d.Bpad = cdiv(B, TBM) * TBM;
   d.Npad = cdiv(q, TBN) * TBN;
   d.Kpad = cdiv(q, TBK) * TBK;
-  d.ntile = d.Npad / TBN;
+  d.ntile_n = d.Npad / TBN;
+  d.nrb = d.Bpad / TBM;
+  d.nchain = k * d.nrb;
   d.state_bytes = (size_t)8 * k * d.Bpad * d.Npad * 2;
   d.aop_bytes = (size_t)4 * k * d.Npad * d.Kpad * 2;
+  d.cnt_bytes = (size_t)d.nchain * 2 * sizeof(unsigned);
   return d;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 0;
+  }
+  return n;
 }
 
 bool supported(int k, int B, int q) {
   const Dims d = dims(k, B, q);
-  return d.ntile <= MAXP && (size_t)8 * k * d.Bpad < 2147483647ull && (size_t)4 * k * d.Npad < 2147483647ull &&
-         (size_t)2 * k <= 65535 && d.Bpad / TBM <= 65535;
+  return slots(q) <= MAXP && (size_t)8 * k * d.Bpad < 2147483647ull && (size_t)4 * k * d.Npad < 2147483647ull &&
+         d.ntile_n <= 128;
 }
-int ntile(int q) { return cdiv(q, TBN); }
+// partial-sum slots per row: one per epilogue warp group (column half) of every column tile
+int slots(int q) { return cdiv(q, TBN) * (EPI_WARPS / 4); }
 
-// extra workspace (beyond the part / hist / cum / ll slots shared with dense.cu): bf16 state pairs + transition pairs
+// extra workspace (beyond the part / hist / cum / ll slots shared with dense.cu): bf16 state pairs, transition pairs, counters
 size_t extra_workspace(int k, int B, int q) {
   const Dims d = dims(k, B, q);
-  return align_up(d.state_bytes, 1024) + align_up(d.aop_bytes, 1024) + 1024;
+  return align_up(d.state_bytes, 1024) + align_up(d.aop_bytes, 1024) + align_up(d.cnt_bytes, 1024) + 1024;
 }
 
-// Runs every step of the requested directions.  part[d][p], hist[d]: the slots of dense.cu's layout with ntile = ntile(q).
+// Runs every step of the requested directions.  part[d][p], hist[d]: the slots of dense.cu's layout with slots(q) per row.
 int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
               float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st) {
   const Dims d = dims(k, B, q);
   static bool attr_done = false;
   if (!attr_done) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    HMM_CUDA_OK(cudaFuncSetAttribute(chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr_done = true;
   }
+  const int sms = sm_count();
+  HMM_REQUIRE(sms >= d.ntile_n, "dense_tc: %d column tiles need as many SMs (device has %d)", d.ntile_n, sms);
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(extra) + 1023) & ~(uintptr_t)1023);
   uint16_t* state = reinterpret_cast<uint16_t*>(base);
   uint16_t* aop = reinterpret_cast<uint16_t*>(base + align_up(d.state_bytes, 1024));
+  unsigned* cnt = reinterpret_cast<unsigned*>(base + align_up(d.state_bytes, 1024) + align_up(d.aop_bytes, 1024));
   CUtensorMap tmS, tmA;
   int rc = make_map(&tmS, state, (uint64_t)8 * k * d.Bpad, (uint64_t)d.Npad, TBM);
   if (rc) return rc;
@@ -419,28 +505,42 @@ int run_steps(const float* E, const float* A, const float* pi, int k, int B, int
   if (rc) return rc;
 
   Args a;
-  a.E = E; a.state = state;
+  a.E = E; a.state = state; a.cnt = cnt;
   a.store[0] = store_f; a.store[1] = store_b;
   for (int dd = 0; dd < 2; ++dd) {
     a.part[dd][0] = part[dd][0]; a.part[dd][1] = part[dd][1];
     a.hist[dd] = hist[dd];
   }
-  a.k = k; a.B = B; a.T = T; a.q = q; a.s = 0; a.ntile = d.ntile; a.Bpad = d.Bpad; a.Npad = d.Npad; a.nkb = d.Kpad / TBK;
+  a.k = k; a.B = B; a.T = T; a.q = q; a.ntile = slots(q); a.ntile_n = d.ntile_n; a.Bpad = d.Bpad; a.Npad = d.Npad;
+  a.nkb = d.Kpad / TBK;
   a.dir0 = need_f ? 0 : 1;
   a.ndir = (need_f ? 1 : 0) + (need_b ? 1 : 0);
+  a.chain0 = 0; a.nrb = d.nrb;
 
   const size_t per = (size_t)k * d.Npad * d.Kpad;
+  HMM_CUDA_OK(cudaMemsetAsync(cnt, 0, d.cnt_bytes, st));
   prep_kernel<<<(unsigned)((per + 255) / 256), 256, 0, st>>>(A, aop, k, q, d.Npad, d.Kpad);
   init_kernel<<<dim3(d.Bpad, k, a.ndir), 256, 0, st>>>(a, pi);
   HMM_CUDA_OK(cudaGetLastError());
-  const dim3 grid(d.ntile, d.Bpad / TBM, k * a.ndir);
-  // step s reads ping-pong slot (s-1)&1 and writes slot s&1
-  for (int s = 1; s < T; ++s) {
+  if (T < 2) return 0;
+  // chains are independent: as many per launch as are co-resident (one CTA per SM), the rest in further launches
+  const int per_launch = sms / d.ntile_n;
+  for (int c0 = 0; c0 < d.nchain; c0 += per_launch) {
     Args b = a;
-    b.s = s;
-    step_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(tmS, tmA, b);
+    b.chain0 = c0;
+    const int nc = d.nchain - c0 < per_launch ? d.nchain - c0 : per_launch;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(d.ntile_n, nc, 1);
+    cfg.blockDim = dim3(THREADS, 1, 1);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, chain_kernel, tmS, tmA, b));
   }
-  HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
