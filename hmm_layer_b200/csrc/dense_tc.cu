@@ -40,6 +40,7 @@ struct Args {
   float* store[2];       // per direction (k, B, T, q) or null: a_t (forward) / R_t (backward), un-normalised
   float* part[2][2];     // per direction, ping-pong: (k, B, ntile) partial row sums
   float* hist[2];        // per direction (k, B, T)
+  long long* dbg;        // optional phase timestamps of CTA (0,0): [role 0..2][item - DBG_IT0 (8)][8] globaltimer ns
   unsigned* cnt;         // [chain][dir] CTAs of the chain that finished a step (zeroed per call)
   int k, B, T, q, ntile, ntile_n, Bpad, Npad, nkb;   // ntile = partial-sum slots per row = 2 per column tile
   int dir0, ndir, chain0, nrb;
@@ -129,6 +130,14 @@ __device__ __forceinline__ void wait_count(const unsigned* p, unsigned want) {
   }
   __trap();
 }
+constexpr int DBG_IT0 = 200;
+__device__ __forceinline__ void dbg_stamp(const Args& a, int role, int it, int slot) {
+  if (a.dbg && blockIdx.x == 0 && blockIdx.y == 0 && it >= DBG_IT0 && it < DBG_IT0 + 8) {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.dbg[(role * 8 + (it - DBG_IT0)) * 8 + slot] = t;
+  }
+}
 __device__ __forceinline__ void proxy_fence_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 
 // Persistent kernel: CTA (j, c) owns column tile j of chain c = (head, block of 128 sequences) for ALL time steps and both
@@ -187,9 +196,12 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
           tma_load_2d(sb + 2 * A_TILE, &tmA, fb, kb * TBK, rA_hi);
           tma_load_2d(sb + 2 * A_TILE + B_TILE, &tmA, fb, kb * TBK, rA_lo);
           if (kb == 0 && s >= 2) {   // the chain's column tiles must all have written step s-1 of this direction
+            dbg_stamp(a, 0, it, 0);
             wait_count(cnt_r + dir, (unsigned)(a.ntile_n * (s - 1)));
             proxy_fence_global();
+            dbg_stamp(a, 0, it, 1);
           }
+          if (kb == a.nkb - 1) dbg_stamp(a, 0, it, 2);
           tma_load_2d(sb, &tmS, fb, kb * TBK, rS_hi);
           tma_load_2d(sb + A_TILE, &tmS, fb, kb * TBK, rS_lo);
         }
@@ -200,14 +212,17 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
       int kbg = 0;
       for (int it = 0; it < nitems; ++it) {
         const int buf = it & 1;
+        dbg_stamp(a, 1, it, 0);
         mbar_wait(tempty0 + 8 * buf, (((uint32_t)it >> 1) & 1u) ^ 1u);   // the epilogue drained this accumulator
         tc_fence_after();
+        dbg_stamp(a, 1, it, 1);
         const uint32_t acc = tmem + (uint32_t)(buf * TBN);
         for (int kb = 0; kb < a.nkb; ++kb, ++kbg) {
           const int st = kbg % STAGES;
           const uint32_t ph = (uint32_t)(kbg / STAGES) & 1u;
           mbar_wait(full0 + 8 * st, ph);
           tc_fence_after();
+          if (kb == 0) dbg_stamp(a, 1, it, 2);
           const uint32_t sb = stage0 + st * STAGE_BYTES;
 #pragma unroll
           for (int k4 = 0; k4 < TBK / UK; ++k4) {
@@ -221,6 +236,7 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
           tc_commit(empty0 + 8 * st);
         }
         tc_commit(tfull0 + 8 * buf);
+        dbg_stamp(a, 1, it, 3);
       }
     }
   } else {
@@ -242,6 +258,8 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
       const int t = dir == 0 ? s : a.T - 1 - s;
       const float* Et = a.E + (size_t)t * a.q;
       float* St = a.store[dir] ? a.store[dir] + (size_t)t * a.q : nullptr;
+      const bool stamp = (ew == 0 && lane == 0);
+      if (stamp) dbg_stamp(a, 2, it, 0);
       float ereg[32];
       {
         const int col = cbase + lane;
@@ -265,8 +283,10 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
 #pragma unroll
       for (int i = 0; i < 32; ++i) stg[i * STG_PITCH + lane] = ereg[i];
       __syncwarp();
+      if (stamp) dbg_stamp(a, 2, it, 1);
       mbar_wait(tfull0 + 8 * buf, ((uint32_t)it >> 1) & 1u);
       tc_fence_after();
+      if (stamp) dbg_stamp(a, 2, it, 2);
 
       float rsum = 0.f;
 #pragma unroll 1
@@ -324,6 +344,7 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
           __syncwarp();
         }
       }
+      if (stamp) dbg_stamp(a, 2, it, 3);
       if (valid) a.part[dir][pp ^ 1][seq * a.ntile + slot] = rsum;
       // publish: every epilogue thread's global writes, then one counter bump per CTA
       proxy_fence_global();
@@ -332,6 +353,7 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
         __threadfence();
         atomicAdd(a.cnt + (size_t)chain * 2 + dir, 1u);
       }
+      if (stamp) dbg_stamp(a, 2, it, 4);
     }
   }
 
@@ -442,6 +464,9 @@ static int make_map(CUtensorMap* map, void* base, uint64_t rows, uint64_t cols, 
   return 0;
 }
 
+static long long* g_dbg = nullptr;
+void set_debug(void* p) { g_dbg = static_cast<long long*>(p); }   // tools/c4_phases.py
+
 struct Dims {
   int Bpad, Npad, Kpad, ntile_n, nrb, nchain;
   size_t state_bytes, aop_bytes, cnt_bytes;
@@ -505,7 +530,7 @@ int run_steps(const float* E, const float* A, const float* pi, int k, int B, int
   if (rc) return rc;
 
   Args a;
-  a.E = E; a.state = state; a.cnt = cnt;
+  a.E = E; a.state = state; a.cnt = cnt; a.dbg = g_dbg;
   a.store[0] = store_f; a.store[1] = store_b;
   for (int dd = 0; dd < 2; ++dd) {
     a.part[dd][0] = part[dd][0]; a.part[dd][1] = part[dd][1];

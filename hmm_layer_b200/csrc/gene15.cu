@@ -36,6 +36,7 @@
 
 namespace hmm {
 namespace dense { void set_path(int p); }
+namespace dense_tc { void set_debug(void* p); }
 namespace gene15 {
 
 constexpr int Q = 15;      // states
@@ -1629,7 +1630,7 @@ size_t workspace_size(int num_models, int batch, int T) {
   return a > b ? a : b;
 }
 
-int set_debug_buffer(void* p) { g_dbg = static_cast<long long*>(p); return 0; }
+int set_debug_buffer(void* p) { g_dbg = static_cast<long long*>(p); hmm::dense_tc::set_debug(p); return 0; }
 
 int set_tuning(int L, int k2_threads, int dense_path) {
   hmm::dense::set_path(dense_path);

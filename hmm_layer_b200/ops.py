@@ -6,6 +6,8 @@ from . import _lib
 
 TRAINING = 1
 NO_LOGLIK = 2
+ALPHA_SCRATCH = 4
+BETA_SCRATCH = 8
 
 
 def _ptr(t):
@@ -202,7 +204,8 @@ def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_l
         beta = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if need_b else None
         post = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if want_post else None
         ws = _workspace(lib.hmm_b200_dense_workspace_size(k, B, T, q), dev)
-        _lib.check(lib.hmm_b200_dense_run(_ptr(E), _ptr(A), _ptr(At), _ptr(pi), k, B, T, q, NO_LOGLIK if no_loglik else 0,
+        flags = (NO_LOGLIK if no_loglik else 0) | (0 if want_alpha else ALPHA_SCRATCH) | (0 if want_beta else BETA_SCRATCH)
+        _lib.check(lib.hmm_b200_dense_run(_ptr(E), _ptr(A), _ptr(At), _ptr(pi), k, B, T, q, flags,
                                           _ptr(post), _ptr(alpha), _ptr(beta), _ptr(res["loglik"]), _ptr(ws), ws.numel(), _stream()))
     if want_post:
         res["post"] = post

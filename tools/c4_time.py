@@ -16,16 +16,17 @@ idx = torch.randint(0, 24, (k, B, T), device="cuda", generator=g)
 E = Bm.transpose(1, 2)[torch.arange(k, device="cuda")[:, None, None], idx]      # (k,B,T,q) = B[:, :, symbol]
 E = E.contiguous()
 ops.set_tuning(0, 0, dense_path=path)
-for mode in ("loglik", "post"):
+modes = sys.argv[4].split(",") if len(sys.argv) > 4 else ("loglik", "post")
+for mode in modes:
     for r in range(reps):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        out = ops.dense_run(E, A, pi, want_post=(mode == "post"))
+        out = ops.dense_run(E, A, pi, want_post=(mode == "post"), want_alpha=(mode == "alpha"), want_beta=(mode == "beta"))
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         cells = float(k) * B * T * q * q
-        flops = 2 * cells * (2 if mode == "post" else 1)
+        flops = 2 * cells * (2 if mode in ("post", "beta") else 1)
         print(f"path={path} T={T} {mode}: {ms:.2f} ms  {cells / ms * 1e3:.3e} cells/s  {flops / ms * 1e-9:.1f} TFLOP/s algorithmic  loglik[0,0]={float(out['loglik'][0, 0]):.4f}")
         del out
