@@ -1106,6 +1106,54 @@ __global__ void __launch_bounds__(KB_WARPS * 32) boundary_kernel(const Args a, i
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K_G: two-level boundary scan for very long sequences (config 5: 1 Mbp = 1737 tiles).  boundary_kernel walks a
+// sequence's tile matrices with one CTA; beyond a few hundred tiles that walk is the whole run time.  Here the tile
+// matrices are grouped by G: group_reduce_kernel multiplies every group down to one block (the same tensor-core
+// product tree as K1), boundary_kernel then runs on the group matrices (a copy of Args with Mt / P / bvf / bvr pointing
+// at the group level), and group_down_kernel replays each group from its boundary vectors to the tile level.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(K1_THREADS) group_reduce_kernel(const Args a, float* __restrict__ Gt) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* H = reinterpret_cast<float*>(smem);   // heap order: leaves [G, 2G), root at 1
+  const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, tid = threadIdx.x;
+  const int nb = min(G, P - g * G);
+  const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+  float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+  for (int i = tid; i < nb * (MAT / 4); i += K1_THREADS) dst[i] = __ldg(src + i);
+  for (int b = nb + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+  __syncthreads();
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  float4* out = reinterpret_cast<float4*>(Gt + ((size_t)n * PG + g) * MAT);
+  for (int i = tid; i < MAT / 4; i += K1_THREADS) out[i] = reinterpret_cast<const float4*>(H + MAT)[i];
+}
+
+__global__ void __launch_bounds__(256) group_down_kernel(const Args a, const float* __restrict__ gvf, const float* __restrict__ gvr) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* stg = reinterpret_cast<float*>(smem);       // G staged blocks, row stride BST
+  float* ones = stg + G * BSZ;
+  const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, tid = threadIdx.x;
+  const int nb = min(G, P - g * G);
+  stage_blocks_async(stg, a.Mt + ((size_t)n * P + (size_t)g * G) * MAT, nb);
+  cp_async_commit();
+  if (tid < QP) ones[tid] = 1.f;
+  cp_async_wait_all();
+  __syncthreads();
+  if (tid >= 32) return;
+  const int hl = tid & 15, hi = tid >> 4;
+  const float* gv = (hi == 0 ? gvf : gvr) + ((size_t)n * PG + g) * QP;
+  HV h;
+  h.v = (hl < Q) ? __ldg(gv + hl) : 0.f;
+  h.e = __float_as_int(__ldg(gv + 15));
+  float* vout = (hi == 0 ? a.bvf : a.bvr) + ((size_t)n * P + (size_t)g * G) * QP;
+  for (int it = 0; it < nb; ++it) {
+    const int s = hi == 0 ? it : nb - 1 - it;
+    vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+    matvec(stg + s * BSZ, ones, hl, hi, true, h);
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K_S: sequence sharding over GPUs.  blocks[w][n] = ordered product of all tile matrices of shard w of sequence n
 // (boundary_kernel mode 1 on every rank, then one all-gather).  One warp per sequence folds them into the boundary
 // vector entering this shard (pi . M_0 ... M_{rank-1}), the one leaving it (M_{rank+1} ... M_{W-1} . 1) and the
@@ -1601,7 +1649,7 @@ static int choose_L(int NB, int T, bool full) {
 }
 
 struct Layout {
-  size_t Mh, Mt, bvf, bvr, llws, inf, inr, cnt, Ews, total;
+  size_t Mh, Mt, bvf, bvr, llws, inf, inr, cnt, Gt, gvf, gvr, Ews, total;
 };
 static Layout layout(int NB, int P, int L) {
   Layout l;
@@ -1615,6 +1663,10 @@ static Layout layout(int NB, int P, int L) {
   l.inf = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
   l.inr = off;  off = align_up(off + (size_t)NB * QP * sizeof(float), 256);
   l.cnt = off;  off = align_up(off + (size_t)NB * sizeof(unsigned), 256);
+  const size_t NG = (size_t)NB * cdiv(P, G);   // tile groups of the two-level boundary scan
+  l.Gt = off;   off = align_up(off + NG * MAT * sizeof(float), 256);
+  l.gvf = off;  off = align_up(off + NG * QP * sizeof(float), 256);
+  l.gvr = off;  off = align_up(off + NG * QP * sizeof(float), 256);
   l.Ews = off;  off = align_up(off + NP * G * ((size_t)L * QP + 4) * sizeof(float), 256);
   l.total = off;
   return l;
@@ -1666,7 +1718,7 @@ static void set_L(Args& a, int L) {
 }
 
 // raises a kernel's dynamic shared memory limit when this call needs more than any earlier one (slot = kernel id)
-static size_t g_smem_set[5] = {0, 0, 0, 0, 0};
+static size_t g_smem_set[7] = {0, 0, 0, 0, 0, 0, 0};
 template <typename K>
 static int set_smem(K kernel, int slot, size_t bytes) {
   if (bytes <= g_smem_set[slot]) return 0;
@@ -1707,6 +1759,33 @@ int prepare_codon(const float* codon64, float* codon5, cudaStream_t st) {
   return 0;
 }
 
+// Boundary vectors of every tile (mode 0) or the product of all tile matrices (mode 1) after products_kernel.
+// Long tile lists go through the two-level scan (K_G); `groups_ready`: Gt still holds this call pair's group matrices.
+constexpr int GROUP_MIN_TILES = 96;
+enum { SLOT_KG1 = 5, SLOT_KG2 = 6 };
+static int launch_boundary(const Args& a, const Layout& l, int NB, int mode, float* total_out, bool groups_ready, void* workspace,
+                           cudaStream_t st) {
+  int rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
+  if (a.P < GROUP_MIN_TILES) {
+    boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, mode, total_out);
+    return 0;
+  }
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  float* Gt = reinterpret_cast<float*>(ws + l.Gt);
+  float* gvf = reinterpret_cast<float*>(ws + l.gvf);
+  float* gvr = reinterpret_cast<float*>(ws + l.gvr);
+  const int PG = cdiv(a.P, G);
+  const size_t smg = (size_t)HEAP * MAT * sizeof(float), smd = ((size_t)G * BSZ + QP) * sizeof(float);
+  rc = set_smem(group_reduce_kernel, SLOT_KG1, smg); if (rc) return rc;
+  rc = set_smem(group_down_kernel, SLOT_KG2, smd); if (rc) return rc;
+  if (!groups_ready) group_reduce_kernel<<<dim3(PG, NB), K1_THREADS, smg, st>>>(a, Gt);
+  Args top = a;
+  top.Mt = Gt; top.P = PG; top.bvf = gvf; top.bvr = gvr;
+  boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(top, mode, total_out);
+  if (mode == 0) group_down_kernel<<<dim3(PG, NB), 256, smd, st>>>(a, gvf, gvr);
+  return 0;
+}
+
 int run(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
         const float* codon5, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
         float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
@@ -1731,14 +1810,13 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
   if (need_k2 && !full) { rc = set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc; }
   if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
-  if (!a.top_scan) { rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc; }
   if (a.top_scan) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
 
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
   products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
   if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   if (!a.top_scan) {
-    boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 0, nullptr);
+    rc = launch_boundary(a, l, NB, 0, nullptr, false, workspace, st); if (rc) return rc;
     if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   }
   if (need_k2) {
@@ -1782,9 +1860,8 @@ int shard_reduce(const float* inputs, int num_models, int batch, int T, int seq_
   const int NB = num_models * batch;
   const size_t sm1 = k1_smem_bytes(a.L, a.P);
   rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
-  rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
   products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
-  boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 1, block_out);
+  rc = launch_boundary(a, l, NB, 1, block_out, false, workspace, st); if (rc) return rc;
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -1811,8 +1888,7 @@ int shard_finalize(const float* inputs, int num_models, int batch, int T, int se
     const bool full = out_alpha || out_beta;
     const size_t sm2 = k2_smem_bytes(a.L, full);
     rc = full ? set_smem(finalize_kernel<true>, SLOT_K2F, sm2) : set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc;
-    rc = set_smem(boundary_kernel, SLOT_KB, sizeof(KBSmem)); if (rc) return rc;
-    boundary_kernel<<<NB, KB_WARPS * 32, sizeof(KBSmem), st>>>(a, 0, nullptr);
+    rc = launch_boundary(a, l, NB, 0, nullptr, true, workspace, st); if (rc) return rc;   // Gt: from shard_reduce
     const int nt = k2_threads_for(a.L);
     if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
     else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);

@@ -85,3 +85,28 @@ def test_shard_argument_validation():
         ops.genepred_shard_reduce(x[:, :, :50].contiguous(), None, 0, 100, dev(A), dev(pi), dev(Bfull), dev(tab))   # no halo
     with pytest.raises(ValueError):
         ops.genepred_shard_reduce(x, None, 10, 100, dev(A), dev(pi), dev(Bfull), dev(tab))                          # outside
+
+
+def test_two_level_boundary_scan_long_tile_lists():
+    """More than 96 tiles per sequence (here forced with chunk length 4: 128 positions per tile) take the two-level
+    boundary scan (group_reduce_kernel / boundary_kernel on the group matrices / group_down_kernel), unsharded and
+    sharded (config 5's route at 1 Mbp)."""
+    A, pi, Bfull, tab = gene_params(pi_random=True)
+    ops.set_tuning(4, 0)
+    try:
+        x = syn.gene_inputs(1, 2, 20011, seed=77, p_n=0.01)            # 157 tiles per sequence
+        ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+        got = run_gpu(x, A, pi, Bfull, tab, want_post=True, want_alpha=True, want_beta=True)
+        check_post(got, ref)
+        check_ab(got, ref)
+        only = run_gpu(x, A, pi, Bfull, tab, want_post=False)
+        np.testing.assert_allclose(only["loglik"], got["loglik"], rtol=1e-6)
+        xs = syn.gene_inputs(1, 1, 30000, seed=78, p_n=0.01)           # 2 shards x 118 tiles
+        refs = oracle_gene(xs.numpy(), A, pi, Bfull, tab)
+        gs = run_sharded(xs, 2, A, pi, Bfull, tab, want_post=True)
+        check_post(gs, refs)
+    finally:
+        ops.set_tuning(0, 0)
+    same = run_gpu(x, A, pi, Bfull, tab, want_post=True)                # default chunk length: single-level scan
+    np.testing.assert_allclose(same["loglik"], got["loglik"], rtol=1e-6)
+    np.testing.assert_allclose(np.exp(same["post"]), np.exp(got["post"]), atol=2e-5)
