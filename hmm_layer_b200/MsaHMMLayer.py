@@ -20,20 +20,30 @@ def _is_fused_gene_cell(cell):
 
 
 def _check_inputs(inputs, cell, parallel_factor):
+    """CPU inputs are accepted for the fused gene model only (host path: outputs come back as CPU tensors, like the
+    reference's); the parameters always live on the GPU."""
     if inputs.dim() != 4:
         raise ValueError(f"inputs must have shape (num_model, b, seq_len, s), got {tuple(inputs.shape)}")
     if inputs.shape[0] != cell.num_models:
         raise ValueError(f"inputs carry {inputs.shape[0]} models but the cell has {cell.num_models}")
     if parallel_factor < 1 or inputs.shape[2] % parallel_factor != 0:
         raise ValueError(f"parallel_factor={parallel_factor} must divide the sequence length {inputs.shape[2]}")
-    if not inputs.is_cuda:
-        raise ValueError("inputs must be CUDA tensors: this layer has no CPU path")
+    if not inputs.is_cuda and not (_is_fused_gene_cell(cell) and cell.init_dist.is_cuda):
+        raise ValueError("inputs must be CUDA tensors (CPU inputs only for the fused gene model with its cell on a GPU): "
+                         "this layer has no CPU compute path")
 
 
 def _gene_run(inputs, cell, end_hints, training, **want):
     em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
-    return ops.genepred_run(inputs, tr.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1),
-                            em.make_B_full().detach(), em.codon5(inputs.device), end_hints=end_hints, training=training, **want)
+    dev = cell.init_dist.device
+    gp = getattr(cell, "_gene_params", None)   # kernel-ready parameter tensors of this parameter version (recurrent_init resets)
+    if gp is None:
+        gp = (tr.A.detach().contiguous(), cell.init_dist.detach().reshape(cell.num_models, -1).contiguous(),
+              em.make_B_full().detach().contiguous(), em.codon5(dev))
+        object.__setattr__(cell, "_gene_params", gp)
+    if not inputs.is_cuda:   # host buffers: H2D / kernels / D2H pipelined inside the library, CPU tensors back
+        return ops.genepred_run_host(inputs, *gp, end_hints=None if end_hints is None else end_hints.cpu(), training=training, **want)
+    return ops.genepred_run(inputs, *gp, end_hints=end_hints, training=training, **want)
 
 
 def _priors(cell, result, return_prior):
@@ -164,6 +174,8 @@ class MsaHmmLayer(nn.Module):
         else:
             E = cell.emission_probs(inputs, training=training)
             loglik = ops.dense_run(E, cell.transitioner.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1))["loglik"]
+        if self.sequence_weights is not None:
+            loglik = loglik.to(self.sequence_weights.device)
         loglik_mean = torch.squeeze(self.apply_sequence_weights(loglik, indices, aggregate=True))
         if self.use_prior:
             return loglik, loglik_mean, self._scale_prior(cell.get_prior_log_density()), cell.get_aux_loss()

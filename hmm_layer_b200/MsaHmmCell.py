@@ -25,15 +25,27 @@ class HmmCell(nn.Module):
         self.recurrent_init()
 
     # ---- parameter -> matrices, once per call (reference :41-59) ----
+    def _param_key(self):
+        """Identity + version of every parameter / buffer: unchanged key = unchanged derived tensors (A, B, pi)."""
+        return tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
+
     def recurrent_init(self):
+        """Derived tensors of this call (reference MsaHmmCell.py:41-59).  They are functions of the parameters only, so
+        they are rebuilt only when a parameter changed (in-place updates bump the version, .to()/.data swaps change the
+        pointer): at inference the ~20 small parameter-construction launches drop out of every call."""
+        if not self.reverse and self.use_step_counter:
+            self.step_counter = torch.tensor(-1, dtype=torch.int32)
+        key = self._param_key()
+        if getattr(self, "_ri_key", None) == key:
+            return
         self.transitioner.recurrent_init()
         for em in self.emitter:
             em.recurrent_init()
         self.log_A_dense = self.transitioner.make_log_A()
         self.log_A_dense_t = self.log_A_dense.transpose(1, 2)
         self.init_dist = self.make_initial_distribution()
-        if not self.reverse and self.use_step_counter:
-            self.step_counter = torch.tensor(-1, dtype=torch.int32)
+        object.__setattr__(self, "_ri_key", key)
+        object.__setattr__(self, "_gene_params", None)
 
     def make_initial_distribution(self):
         return self.transitioner.make_initial_distribution()
@@ -105,6 +117,7 @@ class HmmCell(nn.Module):
         """Reference :160-162.  Only flips this cell; a transitioner shared with another cell is swapped for a
         reversed view instead of being mutated."""
         self.reverse = reverse
+        object.__setattr__(self, "_ri_key", None)   # derived tensors belong to the previous orientation
         if reverse and hasattr(self.transitioner, "reversed_view"):
             self.transitioner = self.transitioner.reversed_view()
         elif not reverse and hasattr(self.transitioner, "base"):

@@ -32,6 +32,7 @@
 // All scales are exact powers of two (integer bookkeeping), so no log/exp rounding enters the posteriors.
 //
 // The numpy model tests/chunk_algo_model.py mirrors the arithmetic and is checked against the oracle.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace hmm {
@@ -1829,6 +1830,130 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   return 0;
 }
 
+// ---- host buffers: batch-sliced H2D -> kernels -> D2H pipeline --------------------------------------------------------
+// Sequences are independent, so the batch is cut into slices; slice i's kernels run on the caller's stream while slice
+// i+1's inputs come up and slice i-1's outputs go down on two copy streams (PCIe is full duplex).  Device memory comes
+// from the caller (`scratch`, host_scratch_size); the copy streams and events are created once per thread and device.
+struct HostPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_k[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+  cudaEvent_t ev_start = nullptr;
+  bool ready = false;
+};
+static int host_pipe(HostPipe** out) {
+  static thread_local HostPipe pipes[64];
+  int dev = 0;
+  HMM_CUDA_OK(cudaGetDevice(&dev));
+  HMM_REQUIRE(dev >= 0 && dev < 64, "genepred run_host: device index %d out of range", dev);
+  HostPipe& p = pipes[dev];
+  if (!p.ready) {
+    HMM_CUDA_OK(cudaStreamCreateWithFlags(&p.s_in, cudaStreamNonBlocking));
+    HMM_CUDA_OK(cudaStreamCreateWithFlags(&p.s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      HMM_CUDA_OK(cudaEventCreateWithFlags(&p.ev_in[i], cudaEventDisableTiming));
+      HMM_CUDA_OK(cudaEventCreateWithFlags(&p.ev_k[i], cudaEventDisableTiming));
+      HMM_CUDA_OK(cudaEventCreateWithFlags(&p.ev_out[i], cudaEventDisableTiming));
+    }
+    HMM_CUDA_OK(cudaEventCreateWithFlags(&p.ev_start, cudaEventDisableTiming));
+    p.ready = true;
+  }
+  *out = &p;
+  return 0;
+}
+
+static int g_host_slices = 0;   // 0 = by batch size; HMM_HOST_SLICES overrides (experiments)
+static int host_slice_len(int batch) {
+  static const int env = getenv("HMM_HOST_SLICES") ? atoi(getenv("HMM_HOST_SLICES")) : 0;
+  int ns = env > 0 ? env : g_host_slices;
+  if (ns <= 0) ns = batch >= 16 ? 4 : (batch >= 4 ? 2 : 1);   // measured on config 2: 2, 4 and 8 slices within 1 %
+  if (ns > batch) ns = batch;
+  return cdiv(batch, ns);
+}
+
+struct HostLayout {
+  size_t in[2], post[2], alpha[2], beta[2], ws[2], ll, hints, total;
+  size_t ws_bytes;
+  int slice;
+};
+static HostLayout host_layout(int num_models, int batch, int T) {
+  HostLayout h;
+  h.slice = host_slice_len(batch);
+  const size_t rows = (size_t)h.slice * T;
+  h.ws_bytes = workspace_size(1, h.slice, T);
+  size_t off = 0;
+  for (int b = 0; b < 2; ++b) { h.in[b] = off; off = align_up(off + rows * SIN * sizeof(float), 256); }
+  for (int b = 0; b < 2; ++b) { h.post[b] = off; off = align_up(off + rows * Q * sizeof(float), 256); }
+  for (int b = 0; b < 2; ++b) { h.alpha[b] = off; off = align_up(off + rows * Q * sizeof(float), 256); }
+  for (int b = 0; b < 2; ++b) { h.beta[b] = off; off = align_up(off + rows * Q * sizeof(float), 256); }
+  for (int b = 0; b < 2; ++b) { h.ws[b] = off; off = align_up(off + h.ws_bytes, 256); }
+  h.ll = off; off = align_up(off + (size_t)num_models * batch * sizeof(float), 256);
+  h.hints = off; off = align_up(off + (size_t)num_models * batch * 2 * Q * sizeof(float), 256);
+  h.total = off;
+  return h;
+}
+size_t host_scratch_size(int num_models, int batch, int T) {
+  if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
+  return host_layout(num_models, batch, T).total;
+}
+
+int run_host(const float* h_inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
+             const float* codon5, const float* h_hints, unsigned flags, float* h_post, float* h_alpha, float* h_beta,
+             float* h_loglik, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  HMM_REQUIRE(h_inputs && A && pi && Bfull && codon5, "genepred run_host: null input pointer");
+  HMM_REQUIRE(num_models > 0 && batch > 0 && T > 0, "genepred run_host: num_models, batch and T must be positive");
+  HMM_REQUIRE(h_post || h_alpha || h_beta || h_loglik, "genepred run_host: no output requested");
+  const HostLayout h = host_layout(num_models, batch, T);
+  if (!scratch || scratch_bytes < h.total) {
+    set_error("genepred run_host: device scratch too small (%zu < %zu bytes)", scratch_bytes, h.total);
+    return HMM_B200_EWORKSPACE;
+  }
+  HMM_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 255) == 0, "genepred run_host: scratch must be 256-byte aligned");
+  HostPipe* pp = nullptr;
+  int rc = host_pipe(&pp); if (rc) return rc;
+  HostPipe& p = *pp;
+  unsigned char* ws = static_cast<unsigned char*>(scratch);
+  auto F = [&](size_t o) { return reinterpret_cast<float*>(ws + o); };
+  float* d_ll = F(h.ll);
+  float* d_hints = h_hints ? F(h.hints) : nullptr;
+  // everything queued on the copy streams starts after the work already on the caller's stream
+  HMM_CUDA_OK(cudaEventRecord(p.ev_start, st));
+  HMM_CUDA_OK(cudaStreamWaitEvent(p.s_in, p.ev_start, 0));
+  HMM_CUDA_OK(cudaStreamWaitEvent(p.s_out, p.ev_start, 0));
+  if (h_hints)
+    HMM_CUDA_OK(cudaMemcpyAsync(d_hints, h_hints, (size_t)num_models * batch * 2 * Q * sizeof(float), cudaMemcpyHostToDevice, p.s_in));
+  int it = 0;
+  for (int m = 0; m < num_models; ++m) {
+    for (int b0 = 0; b0 < batch; b0 += h.slice, ++it) {
+      const int nb = batch - b0 < h.slice ? batch - b0 : h.slice, buf = it & 1;
+      const size_t seq0 = (size_t)m * batch + b0, rows = (size_t)nb * T;
+      if (it >= 2) HMM_CUDA_OK(cudaStreamWaitEvent(p.s_in, p.ev_k[buf], 0));      // the kernels of slice it-2 read this buffer
+      HMM_CUDA_OK(cudaMemcpyAsync(F(h.in[buf]), h_inputs + seq0 * T * SIN, rows * SIN * sizeof(float), cudaMemcpyHostToDevice, p.s_in));
+      HMM_CUDA_OK(cudaEventRecord(p.ev_in[buf], p.s_in));
+      HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_in[buf], 0));
+      if (it >= 2) HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_out[buf], 0));        // slice it-2's outputs have left
+      rc = run(F(h.in[buf]), 1, nb, T, A + (size_t)m * Q * Q, pi + (size_t)m * Q, Bfull + (size_t)m * Q * Q, codon5,
+               d_hints ? d_hints + seq0 * 2 * Q : nullptr, flags, h_post ? F(h.post[buf]) : nullptr,
+               h_alpha ? F(h.alpha[buf]) : nullptr, h_beta ? F(h.beta[buf]) : nullptr, d_ll + seq0, ws + h.ws[buf], h.ws_bytes, st);
+      if (rc) return rc;
+      HMM_CUDA_OK(cudaEventRecord(p.ev_k[buf], st));
+      HMM_CUDA_OK(cudaStreamWaitEvent(p.s_out, p.ev_k[buf], 0));
+      if (h_post) HMM_CUDA_OK(cudaMemcpyAsync(h_post + seq0 * T * Q, F(h.post[buf]), rows * Q * sizeof(float), cudaMemcpyDeviceToHost, p.s_out));
+      if (h_alpha) HMM_CUDA_OK(cudaMemcpyAsync(h_alpha + seq0 * T * Q, F(h.alpha[buf]), rows * Q * sizeof(float), cudaMemcpyDeviceToHost, p.s_out));
+      if (h_beta) HMM_CUDA_OK(cudaMemcpyAsync(h_beta + seq0 * T * Q, F(h.beta[buf]), rows * Q * sizeof(float), cudaMemcpyDeviceToHost, p.s_out));
+      HMM_CUDA_OK(cudaEventRecord(p.ev_out[buf], p.s_out));
+    }
+  }
+  if (h_loglik) {
+    HMM_CUDA_OK(cudaStreamWaitEvent(p.s_out, p.ev_k[(it - 1) & 1], 0));
+    HMM_CUDA_OK(cudaMemcpyAsync(h_loglik, d_ll, (size_t)num_models * batch * sizeof(float), cudaMemcpyDeviceToHost, p.s_out));
+    HMM_CUDA_OK(cudaEventRecord(p.ev_out[(it - 1) & 1], p.s_out));
+  }
+  // completion is ordered on the caller's stream: it waits for the last copies of both buffers
+  HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_out[(it - 1) & 1], 0));
+  if (it >= 2) HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_out[it & 1], 0));
+  return 0;
+}
+
 // ---- sequence sharding (multi-GPU): this rank holds positions [seq_off, seq_off + T) of every sequence -----------
 static int shard_args(Args& a, Layout& l, const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total,
                       const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
@@ -1918,6 +2043,19 @@ extern "C" {
 
 size_t hmm_b200_genepred_workspace_size(int num_models, int batch, int T) {
   return hmm::gene15::workspace_size(num_models, batch, T);
+}
+
+size_t hmm_b200_genepred_host_scratch_size(int num_models, int batch, int T) {
+  return hmm::gene15::host_scratch_size(num_models, batch, T);
+}
+
+int hmm_b200_genepred_run_host(const float* host_inputs, int num_models, int batch, int T, const float* A, const float* pi,
+                               const float* Bfull, const float* codon5, const float* host_end_hints, unsigned flags,
+                               float* host_out_post, float* host_out_alpha, float* host_out_beta, float* host_loglik,
+                               void* device_scratch, size_t device_scratch_bytes, void* stream) {
+  return hmm::gene15::run_host(host_inputs, num_models, batch, T, A, pi, Bfull, codon5, host_end_hints, flags, host_out_post,
+                               host_out_alpha, host_out_beta, host_loglik, device_scratch, device_scratch_bytes,
+                               static_cast<cudaStream_t>(stream));
 }
 
 int hmm_b200_debug_phases(void* device_buffer) { return hmm::gene15::set_debug_buffer(device_buffer); }

@@ -110,6 +110,41 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
     return res
 
 
+def genepred_run_host(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,
+                      want_post=True, want_alpha=False, want_beta=False):
+    """The fused evaluation for HOST inputs (k,B,T,20) (CPU tensor, ideally pinned): batch-sliced H2D -> kernels -> D2H
+    pipeline inside the library (hmm_b200_genepred_run_host).  Parameters A, pi, Bfull, codon are CUDA tensors.
+    Returns pinned CPU tensors ('post','alpha','beta' (k,B,T,15) as requested, 'loglik' (k,B)), complete on return."""
+    lib = _lib.load()
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    if inputs.is_cuda or inputs.dtype != torch.float32:
+        raise ValueError("genepred_run_host takes a float32 CPU tensor (use genepred_run for CUDA tensors)")
+    inputs = inputs.contiguous()
+    k, B, T, _ = inputs.shape
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    dev = A.device
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
+    if end_hints is not None:
+        if end_hints.is_cuda or tuple(end_hints.shape) != (k, B, 2, 15):
+            raise ValueError("end_hints must be a CPU tensor of shape (num_models, batch, 2, 15) on the host path")
+        end_hints = end_hints.to(torch.float32).contiguous()
+    with torch.cuda.device(dev):
+        res = {}
+        for name, want in (("post", want_post), ("alpha", want_alpha), ("beta", want_beta)):
+            if want:
+                res[name] = torch.empty((k, B, T, 15), dtype=torch.float32, pin_memory=True)
+        res["loglik"] = torch.empty((k, B), dtype=torch.float32, pin_memory=True)
+        scratch = _workspace(lib.hmm_b200_genepred_host_scratch_size(k, B, T), dev)
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        _lib.check(lib.hmm_b200_genepred_run_host(
+            _ptr(inputs), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints), flags,
+            _ptr(res.get("post")), _ptr(res.get("alpha")), _ptr(res.get("beta")), _ptr(res["loglik"]),
+            _ptr(scratch), scratch.numel(), _stream()))
+        torch.cuda.current_stream(dev).synchronize()
+    return res
+
+
 def _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints):
     if inputs.dim() != 4 or inputs.shape[-1] != 20:
         raise ValueError(f"inputs must have shape (num_models, batch, T_local, 20), got {tuple(inputs.shape)}")

@@ -84,6 +84,22 @@ int hmm_b200_genepred_run(const float* inputs, int num_models, int batch, int T,
                           float* out_post, float* out_alpha, float* out_beta, float* loglik,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same evaluation with HOST buffers (what a caller holding CPU tensors binds: the reference takes CPU tensors and
+ * returns CPU tensors, MsaHMMLayer.py:134-153).  host_inputs / host_end_hints / host_out_* / host_loglik are HOST
+ * pointers (pinned memory for full copy/compute overlap; pageable memory works, serialised by the driver); A, pi, Bfull,
+ * codon5 stay DEVICE pointers (parameters live on the GPU).  The batch is cut into slices: slice i's kernels run on
+ * `stream` while slice i+1's inputs and slice i-1's outputs move over PCIe on two internal copy streams (created once per
+ * thread and device; no device memory is allocated inside: device_scratch is the caller's, sized by
+ * hmm_b200_genepred_host_scratch_size).  The call returns when everything is queued; the outputs are complete once the
+ * work queued on `stream` up to this call has finished (cudaStreamSynchronize(stream)). */
+size_t hmm_b200_genepred_host_scratch_size(int num_models, int batch, int T);
+
+int hmm_b200_genepred_run_host(const float* host_inputs, int num_models, int batch, int T,
+                               const float* A, const float* pi, const float* Bfull, const float* codon5,
+                               const float* host_end_hints, unsigned flags,
+                               float* host_out_post, float* host_out_alpha, float* host_out_beta, float* host_loglik,
+                               void* device_scratch, size_t device_scratch_bytes, void* stream);
+
 /* Stand-alone emission (cell.emission_probs API parity): out_E (num_models, batch, T, 15). */
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
                                const float* Bfull, const float* codon5, const float* end_hints,

@@ -198,3 +198,41 @@ def test_argument_validation():
         ops.genepred_run(x.cuda()[..., :19], dev(A), dev(pi), dev(Bfull), dev(tab))
     with pytest.raises(ValueError):
         ops.genepred_run(x.cuda().double(), dev(A), dev(pi), dev(Bfull), dev(tab))
+
+
+@pytest.mark.parametrize("B,T", [(1, 300), (5, 1001), (7, 640), (19, 333)])
+def test_host_buffer_path_matches_device_path(B, T):
+    """hmm_b200_genepred_run_host (CPU tensors in and out, batch-sliced copy/compute pipeline: 1, 2 and 4 slices, ragged
+    last slice) against the device-resident call and the oracle; end hints and the training flag travel too."""
+    x = syn.gene_inputs(1, B, T, seed=900 + B, p_n=0.01)
+    A, pi, Bfull, tab = gene_params(pi_random=True)
+    hints = np.random.RandomState(B).rand(1, B, 2, 15).astype(np.float32) + 0.01
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, end_hints=hints, training=True)
+    r = ops.genepred_run_host(x.pin_memory() if B % 2 else x, dev(A), dev(pi), dev(Bfull), dev(tab),
+                              end_hints=torch.as_tensor(hints), training=True, want_post=True, want_alpha=True, want_beta=True)
+    assert all(not v.is_cuda for v in r.values())
+    got = {k: v.numpy() for k, v in r.items()}
+    check_post(got, ref)
+    check_ab(got, ref)
+    one = run_gpu(x, A, pi, Bfull, tab, end_hints=hints, training=True, want_post=True)
+    np.testing.assert_allclose(got["loglik"], one["loglik"], rtol=1e-6)
+    np.testing.assert_allclose(np.exp(got["post"]), np.exp(one["post"]), atol=2e-5)
+    ll_only = ops.genepred_run_host(x, dev(A), dev(pi), dev(Bfull), dev(tab), end_hints=torch.as_tensor(hints), training=True,
+                                    want_post=False)["loglik"].numpy()
+    np.testing.assert_allclose(ll_only, got["loglik"], rtol=1e-6)
+
+
+def test_layer_accepts_cpu_inputs_and_returns_cpu_outputs():
+    import hmm_layer_b200 as H
+    em = H.GenePredHMMEmitter(**syn.GENE_CODONS)
+    em.build((1, 6, 500, 15))
+    tr = H.GenePredMultiHMMTransitioner(initial_exon_len=200, initial_intron_len=4500, initial_ir_len=10000)
+    layer = H.MsaHmmLayer(H.HmmCell([15], 15, em, tr).cuda(), use_prior=False)
+    x = syn.gene_inputs(1, 6, 500, seed=31)
+    p_host = layer.state_posterior_log_probs(x)
+    p_dev = layer.state_posterior_log_probs(x.cuda())
+    assert not p_host.is_cuda and p_dev.is_cuda
+    np.testing.assert_allclose(np.exp(p_host.numpy()), np.exp(p_dev.cpu().numpy()), atol=2e-5)
+    ll_h, _ = layer(x)
+    ll_d, _ = layer(x.cuda())
+    np.testing.assert_allclose(ll_h.numpy(), ll_d.cpu().numpy(), rtol=1e-6)
