@@ -22,6 +22,11 @@ import torch
 WORKLOAD = dict(num_models=1, batch=32, T=9999, q=15)
 BYTES_PER_POSITION = 140.0            # 80 B inputs read once + 60 B log-posterior written once
 NBUF = 8                              # rotating input/output sets: 8 x 44.8 MB = 358 MB > 126 MB L2
+# dram__bytes_read.sum + dram__bytes_write.sum of the two kernels of one pass, from the committed ncu --set full capture
+# (profiles/r1c_ncu_summary.txt: products 25.71 + 7.03 MB, finalize 58.79 + 1.68 MB).  ncu flushes the caches before
+# every kernel, so the L2-resident workspace K1 hands to K2 (emission rows 20.5 MB + product trees 37 MB) shows up as
+# DRAM traffic there; in the back-to-back bench those reads are L2 hits.
+NCU_TRAFFIC_BYTES = 93.22e6
 
 
 def peaks():
@@ -423,7 +428,9 @@ def main():
                     "api": "MsaHmmLayer.state_posterior_log_probs(pinned CPU tensor) -> pinned CPU log-posterior, through hmm_b200_genepred_run_host (batch-sliced H2D / kernels / D2H pipeline)"},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                         "frac": (achieved / peak) if achieved else None, "traffic": NCU_TRAFFIC_BYTES,
+                         "traffic_note": "ncu cold-cache capture r1c: includes 57 MB of K1->K2 workspace that is L2-resident outside the profiler",
+                         "peak_source": peak_src,
                          "scope": "the fused pass = 2 launches (products_kernel, finalize_kernel); algorithmic bytes = 140 B/position x 319968 positions = 44.8 MB per pass; duration = sum of the two kernels' CUDA-event times",
                          "kernel_ms": {"products_kernel": ker[0], "finalize_kernel": ker[1]}},
             "clocks": clocks,
