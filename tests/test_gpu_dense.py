@@ -151,3 +151,31 @@ def test_tensor_core_step_matches_oracle(tensor_core_path, k, L, B, T):
     np.testing.assert_allclose(cc["loglik"].cpu().numpy(), got["loglik"], rtol=2e-6)
     dp = np.abs(np.exp(cc["post"].cpu().numpy()) - np.exp(got["post"])).max()
     assert dp < 1e-4, dp
+
+
+def test_config4_full_size_properties():
+    """BASELINE config 4 at full size (8 heads x 1003 states, batch 512 x len 600) on the tensor-core path: finite,
+    posteriors sum to one, the fp64 oracle on two sequences of one head, and the CUDA-core step on a slice of the batch."""
+    k, L, B, T = 8, 500, 512, 600
+    q = 2 * L + 3
+    A, pi, Bm = syn.profile_model(k, L)
+    g = torch.Generator(device="cuda").manual_seed(2100)
+    idx = torch.randint(0, 24, (k, B, T), device="cuda", generator=g)
+    E = Bm.cuda().transpose(1, 2)[torch.arange(k, device="cuda")[:, None, None], idx].contiguous()     # (k,B,T,q)
+    r = ops.dense_run(E, A.cuda(), pi.cuda(), want_post=True)
+    torch.cuda.synchronize()
+    post, ll = r["post"], r["loglik"]
+    assert bool(torch.isfinite(post).all()) and bool(torch.isfinite(ll).all())
+    s = torch.exp(post[:, ::37].double()).sum(-1)
+    assert float((s - 1).abs().max()) < 2e-3, float((s - 1).abs().max())
+    h, sl = 3, slice(100, 102)
+    ref = O.posterior(E[h:h + 1, sl].cpu().numpy().astype(np.float64), A[h:h + 1].numpy().astype(np.float64),
+                      pi[h:h + 1].numpy().astype(np.float64))
+    rep = O.parity_report(post[h:h + 1, sl].cpu().numpy(), ll[h:h + 1, sl].cpu().numpy(), ref["log_post"], ref["loglik"])
+    assert rep["loglik_rel"] < 1e-5 and rep["max_abs_dp"] < 1e-4 and rep["argmax_mismatch"] == 0, rep
+    try:
+        ops.set_tuning(0, 0, dense_path=1)
+        cc = ops.dense_run(E[:, :16].contiguous(), A.cuda(), pi.cuda())["loglik"]
+    finally:
+        ops.set_tuning(0, 0, dense_path=0)
+    np.testing.assert_allclose(cc.cpu().numpy(), ll[:, :16].cpu().numpy(), rtol=1e-5)

@@ -236,3 +236,34 @@ def test_layer_accepts_cpu_inputs_and_returns_cpu_outputs():
     ll_h, _ = layer(x)
     ll_d, _ = layer(x.cuda())
     np.testing.assert_allclose(ll_h.numpy(), ll_d.cpu().numpy(), rtol=1e-6)
+
+
+def test_config3_full_size_through_the_layer():
+    """BASELINE config 3 shape: k-mer emitter (k = 3), bidirectional posterior, batch 64 x 9999 bp, through
+    MsaHmmLayer.state_posterior_log_probs; size-independent properties + the oracle on two sequences."""
+    import hmm_layer_b200 as H
+    B, T = 64, 9999
+    em = H.GenePredHMMEmitter(**syn.GENE_CODONS)
+    em.build((1, B, T, 15))
+    with torch.no_grad():
+        em.emission_kernel.copy_(syn.gene_emission_kernel())
+    np.random.seed(0)
+    tr = H.GenePredMultiHMMTransitioner(initial_exon_len=200, initial_intron_len=4500, initial_ir_len=10000)
+    cell = H.HmmCell([15], 15, em, tr).cuda()
+    layer = H.MsaHmmLayer(cell, use_prior=False)
+    x = syn.gene_inputs(1, B, T, seed=3333)
+    post = layer.state_posterior_log_probs(x.cuda())
+    loglik, _ = layer(x.cuda())
+    torch.cuda.synchronize()
+    assert post.shape == (1, B, T, 15) and bool(torch.isfinite(post).all())
+    s = torch.exp(post.double()).sum(-1)
+    assert float((s - 1).abs().max()) < 1e-4
+    A = tr.A.detach().cpu().numpy().astype(np.float64)
+    pi = cell.init_dist.detach().cpu().numpy().reshape(1, 15).astype(np.float64)
+    Bfull = em.make_B_full().detach().cpu().numpy().astype(np.float64)
+    sl = [7, 63]
+    E = O.genepred_emission(x.numpy()[:, sl], Bfull, em.codon_probs.cpu().numpy())
+    ref = O.posterior(E, A, pi)
+    check_post({"post": post.cpu().numpy()[:, sl], "loglik": loglik.cpu().numpy()[:, sl]}, ref)
+    no = layer.state_posterior_log_probs(x.cuda(), no_loglik=True)
+    np.testing.assert_allclose((no - loglik[..., None, None]).cpu().numpy()[:, sl], post.cpu().numpy()[:, sl], rtol=0, atol=0.05)
