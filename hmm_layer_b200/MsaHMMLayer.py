@@ -46,6 +46,15 @@ def _gene_run(inputs, cell, end_hints, training, **want):
     return ops.genepred_run(inputs, *gp, end_hints=end_hints, training=training, **want)
 
 
+def _gene_loglik_diff(inputs, cell, training):
+    """Differentiable log-likelihood of the fused gene model (training through the layer; the reference lets autograd
+    trace its Python loop, MsaHmmCell.py:73-106).  A, pi and B stay attached to the parameters' graph; the kernels'
+    closed-form gradient (ops.GenePredLoglik) supplies d loglik / d (inputs, A, pi, Bfull)."""
+    em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
+    pi = cell.init_dist.reshape(cell.num_models, -1)
+    return ops.GenePredLoglik.apply(inputs, tr.A, pi, em.make_B_full(), em.codon5(inputs.device), None, training)
+
+
 def _priors(cell, result, return_prior):
     if not return_prior:
         return result
@@ -167,9 +176,13 @@ class MsaHmmLayer(nn.Module):
         inputs = inputs.to(torch.float32)
         self.build(inputs.shape)
         cell = self.cell
-        cell.recurrent_init()
+        diff = torch.is_grad_enabled() and _is_fused_gene_cell(cell) and inputs.is_cuda and (
+            inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
+        cell.recurrent_init(fresh=diff)
         _check_inputs(inputs, cell, self.parallel_factor)
-        if _is_fused_gene_cell(cell):
+        if diff:
+            loglik = _gene_loglik_diff(inputs, cell, training)
+        elif _is_fused_gene_cell(cell):
             loglik = _gene_run(inputs, cell, None, training, want_post=False)["loglik"]
         else:
             E = cell.emission_probs(inputs, training=training)

@@ -29,14 +29,15 @@ class HmmCell(nn.Module):
         """Identity + version of every parameter / buffer: unchanged key = unchanged derived tensors (A, B, pi)."""
         return tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
 
-    def recurrent_init(self):
+    def recurrent_init(self, fresh=False):
         """Derived tensors of this call (reference MsaHmmCell.py:41-59).  They are functions of the parameters only, so
         they are rebuilt only when a parameter changed (in-place updates bump the version, .to()/.data swaps change the
-        pointer): at inference the ~20 small parameter-construction launches drop out of every call."""
+        pointer): at inference the ~20 small parameter-construction launches drop out of every call.
+        fresh=True rebuilds them regardless (a differentiable call needs its own autograd graph from the parameters)."""
         if not self.reverse and self.use_step_counter:
             self.step_counter = torch.tensor(-1, dtype=torch.int32)
         key = self._param_key()
-        if getattr(self, "_ri_key", None) == key:
+        if getattr(self, "_ri_key", None) == key and not fresh:
             return
         self.transitioner.recurrent_init()
         for em in self.emitter:

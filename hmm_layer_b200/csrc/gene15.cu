@@ -1510,13 +1510,16 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
     if (tid >= 64 && tid < 64 + tail) dstg[head + mid + tid - 64] = OUT[head + mid + tid - 64];
     if (tid == 0) bulk_wait_read();
   } else {
-    if (a.out_post) {
+    const bool norm_alpha = (a.flags & HMM_B200_ALPHA_NORMALIZED) != 0;
+    if (a.out_post || norm_alpha) {
       for (int i = tid; i < npos; i += nt) {
         float f[QP], r[QP];
         const int off = tile_row_offset(a, i, CS);
         load_row16(Yf + off, f);
         load_row16(Yr + off, r);
-        const float sf = pow2neg(pexp(sum15p(f))), sr = pow2neg(pexp(sum15p(r)));
+        const float fsum = sum15p(f);
+        const float sf = pow2neg(pexp(fsum)), sr = pow2neg(pexp(sum15p(r)));
+        X[off + 3] = __logf(fmaxf(fsum, 1e-37f));   // slot 3: log of the row sum of alpha-hat (normalised alpha output)
         float z = 0.f;
 #pragma unroll
         for (int j = 0; j < Q; ++j) z += fmaxf((f[j] * sf) * (r[j] * sr), 1e-37f);
@@ -1538,7 +1541,8 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
       if (a.out_post)
         a.out_post[obase + i] = (__logf(fmaxf(f * X[off + 1], 1e-37f)) + __logf(fmaxf(r * X[off + 2], 1e-37f))) + X[off];
       if (a.out_alpha)
-        a.out_alpha[obase + i] = (float)((double)__logf(fmaxf(f, 1e-37f)) + (double)(__float_as_int(Yf[off + 15]) + S.hef[G + ci]) * LN2D);
+        a.out_alpha[obase + i] = norm_alpha ? __logf(fmaxf(f, 1e-37f)) - X[off + 3]
+            : (float)((double)__logf(fmaxf(f, 1e-37f)) + (double)(__float_as_int(Yf[off + 15]) + S.hef[G + ci]) * LN2D);
       if (a.out_beta)
         a.out_beta[obase + i] = (float)((double)__logf(fmaxf(r, 1e-37f)) + (double)(__float_as_int(Yr[off + 15]) + S.her[G + ci]) * LN2D);
     }
@@ -1572,6 +1576,191 @@ __global__ void __launch_bounds__(512) emission_kernel(const Args a, float* __re
   for (int i = tid; i < npos * Q; i += nt) {
     const int pos = i / Q, j = i - pos * Q;
     out[obase + i] = X[tile_row_offset(a, pos, CS) + j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Gradient of the log-likelihood (training through the layer: the reference differentiates its Python loop with
+// autograd, MsaHmmCell.py:73-106 / gene_pred_hmm_emitter.py:93-121,231-263).  Inputs: the normalised log posterior
+// gamma and the normalised forward vector alpha-hat of the fused evaluation.  With R_t = alpha-hat_{t-1} A,
+//   d ll / d A[i][j]   = sum_t gamma_t(j) alpha-hat_{t-1}(i) / R_t(j)           (xi_t(i,j) / A[i][j]; the emission cancels)
+//   d ll / d pi[i]     = gamma_0(i) / pi(i)
+//   d ll / d dot_t(q)  = gamma_t(q) / dot_t(q),  dot_t(q) = sum_c x_t[c] B[q][c]  (codon factor and end hint cancel)
+//   d ll / d x_t[c]    = sum_q r_t(q) B[q][c],   d ll / d B[q][c] = sum_t r_t(q) x_t[c],   r_t(q) = gamma_t(q) / dot_t(q)
+// A floored factor (max(E, eps), max(R, eps), MsaHmmCell.py:87-88) passes no gradient, like torch.maximum.
+// One thread per position for the per-position part, then the CTA's 256 x (15 x 15) outer-product sum; per-CTA partial
+// sums go to the workspace and grad_reduce_kernel adds them in a fixed order (deterministic, no atomics).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int GR_POS = 256;        // positions (= threads) per CTA
+constexpr int GR_PART = 320;       // floats per partial record: [0,256) dB[q][c] (stride 16), [256,279) dA edges, [288,303) dpi
+
+struct GradArgs {
+  const float* log_post;   // [NB][T][15] normalised log posterior
+  const float* log_ahat;   // [NB][T][15] log of the normalised forward vector (HMM_B200_ALPHA_NORMALIZED)
+  const float* gll;        // [NB] upstream gradient of every log-likelihood
+  float* grad_inputs;      // [NB][T][20] or NULL
+  float* part;             // [NB * PT][GR_PART] partial sums
+  int PT;                  // CTAs per sequence
+};
+
+struct GradSmem {
+  EmisSmem sp;
+  float A[QP * QP];               // row stride Q; padded so that what follows stays 16-byte aligned
+  float pi[QP];
+  float WA[GR_POS / 32][24];
+  float GP[QP];
+  float X[GR_POS * SIN];          // input rows
+  float R[GR_POS][QP];            // r_t(q) * upstream gradient
+  float PS[GR_POS * Q];           // log posterior rows
+  float AS[(GR_POS + 1) * Q];     // log alpha-hat rows of positions t0 - 1 .. t0 + 255
+  signed char codes[GR_POS + 16];
+};
+
+__global__ void __launch_bounds__(GR_POS, 2) grad_kernel(const Args a, const GradArgs g) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  GradSmem& S = *reinterpret_cast<GradSmem*>(smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch, T = a.T;
+  const int t0 = p * GR_POS, npos = min(T, t0 + GR_POS) - t0;
+  codes_stage(a, S.codes, n, t0, npos);
+  load_emis_params(S.sp, a.Bfull + (size_t)m * Q * Q, a.codon5);
+  if (tid < Q * Q) S.A[tid] = __ldg(a.A + (size_t)m * Q * Q + tid);
+  if (tid < QP) { S.pi[tid] = (tid < Q) ? __ldg(a.pi + m * Q + tid) : 0.f; S.GP[tid] = 0.f; }
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.inputs + ((size_t)n * T + t0) * SIN);
+    float4* dst = reinterpret_cast<float4*>(S.X);
+    for (int i = tid; i < npos * (SIN / 4); i += GR_POS) dst[i] = __ldg(src + i);
+    const float* ps = g.log_post + ((size_t)n * T + t0) * Q;
+    for (int i = tid; i < npos * Q; i += GR_POS) S.PS[i] = __ldg(ps + i);
+    const int lead = (t0 > 0) ? Q : 0;    // row t0 - 1 exists
+    const float* as = g.log_ahat + ((size_t)n * T + t0) * Q - lead;
+    for (int i = tid; i < npos * Q + lead - Q; i += GR_POS) S.AS[Q - lead + i] = __ldg(as + i);   // rows t0-1 .. t0+npos-2
+  }
+  __syncthreads();
+
+  const float w = __ldg(g.gll + n);
+  float gA[NEDGE];
+#pragma unroll
+  for (int e = 0; e < NEDGE; ++e) gA[e] = 0.f;
+  if (tid < npos) {
+    const int i = tid, t = t0 + i;
+    const float4* row = reinterpret_cast<const float4*>(S.X + i * SIN);
+    const float4 x0 = row[0], x1 = row[1], x2 = row[2], x3 = row[3];
+    float cod[9];
+    codon_factors(a, S.sp, n, t, S.codes + 2 + i, cod);
+    const float train = (a.flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
+    const float free_cod = (1.0f / 4096.0f) + train;
+    const int gpos = a.seq_off + t;
+    const float* hint = nullptr;
+    if (a.hints != nullptr) {
+      if (gpos == 0) hint = a.hints + (size_t)n * 2 * Q;
+      else if (gpos == a.seq_total - 1) hint = a.hints + (size_t)n * 2 * Q + Q;
+    }
+    const bool both_hints = a.hints != nullptr && a.seq_total == 1;
+    float gam[Q], r[Q];
+#pragma unroll
+    for (int q = 0; q < Q; ++q) {
+      const float4* b = reinterpret_cast<const float4*>(S.sp.B[q]);
+      const float dot = dot4(x3, b[3], dot4(x2, b[2], dot4(x1, b[1], dot4(x0, b[0], 0.f))));
+      float e = dot * ((q < 6) ? free_cod : cod[q < 6 ? 0 : q - 6] + train);
+      if (hint) e *= __ldg(hint + q);
+      if (both_hints) e *= __ldg(a.hints + (size_t)n * 2 * Q + Q + q);
+      gam[q] = __expf(S.PS[i * Q + q]);
+      r[q] = (e > kEps) ? w * gam[q] / dot : 0.f;
+    }
+    store_row16(S.R[i], r, 0.f);
+    if (g.grad_inputs) {
+      float gx[QP];
+#pragma unroll
+      for (int c = 0; c < QP; ++c) gx[c] = 0.f;
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const float4* b = reinterpret_cast<const float4*>(S.sp.B[q]);
+        const float4 b0 = b[0], b1 = b[1], b2 = b[2], b3 = b[3];
+        gx[0] = fmaf(r[q], b0.x, gx[0]); gx[1] = fmaf(r[q], b0.y, gx[1]); gx[2] = fmaf(r[q], b0.z, gx[2]); gx[3] = fmaf(r[q], b0.w, gx[3]);
+        gx[4] = fmaf(r[q], b1.x, gx[4]); gx[5] = fmaf(r[q], b1.y, gx[5]); gx[6] = fmaf(r[q], b1.z, gx[6]); gx[7] = fmaf(r[q], b1.w, gx[7]);
+        gx[8] = fmaf(r[q], b2.x, gx[8]); gx[9] = fmaf(r[q], b2.y, gx[9]); gx[10] = fmaf(r[q], b2.z, gx[10]); gx[11] = fmaf(r[q], b2.w, gx[11]);
+        gx[12] = fmaf(r[q], b3.x, gx[12]); gx[13] = fmaf(r[q], b3.y, gx[13]); gx[14] = fmaf(r[q], b3.z, gx[14]);
+      }
+      float4* o = reinterpret_cast<float4*>(g.grad_inputs + ((size_t)n * T + t) * SIN);
+      o[0] = make_float4(gx[0], gx[1], gx[2], gx[3]);
+      o[1] = make_float4(gx[4], gx[5], gx[6], gx[7]);
+      o[2] = make_float4(gx[8], gx[9], gx[10], gx[11]);
+      o[3] = make_float4(gx[12], gx[13], gx[14], 0.f);   // the nucleotide flags are data: no gradient
+      o[4] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (gpos == 0) {
+#pragma unroll
+      for (int q = 0; q < Q; ++q) S.GP[q] = (S.pi[q] > kEps) ? w * gam[q] / S.pi[q] : 0.f;
+    } else {
+      float ah[Q], den[Q];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) { ah[q] = __expf(S.AS[i * Q + q]); den[q] = 0.f; }
+#pragma unroll
+      for (int e = 0; e < NEDGE; ++e) den[EDST[e]] = fmaf(ah[ESRC[e]], S.A[ESRC[e] * Q + EDST[e]], den[EDST[e]]);
+      float gd[Q];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) gd[q] = (den[q] > kEps) ? w * gam[q] / den[q] : 0.f;
+#pragma unroll
+      for (int e = 0; e < NEDGE; ++e) gA[e] = gd[EDST[e]] * ah[ESRC[e]];
+    }
+  }
+  // edge sums: warp shuffle tree, then the 8 warps in order
+#pragma unroll
+  for (int e = 0; e < NEDGE; ++e) {
+    float v = gA[e];
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) S.WA[warp][e] = v;
+  }
+  __syncthreads();
+  float* part = g.part + ((size_t)n * g.PT + p) * GR_PART;
+  {
+    // dB[q][c] = sum over the CTA's positions of r(q) x[c]
+    const int q = tid >> 4, c = tid & 15;
+    float acc0 = 0.f, acc1 = 0.f;
+    int i = 0;
+    for (; i + 1 < npos; i += 2) {
+      acc0 = fmaf(S.R[i][q], S.X[i * SIN + c], acc0);
+      acc1 = fmaf(S.R[i + 1][q], S.X[(i + 1) * SIN + c], acc1);
+    }
+    if (i < npos) acc0 = fmaf(S.R[i][q], S.X[i * SIN + c], acc0);
+    part[tid] = (c < Q) ? acc0 + acc1 : 0.f;
+  }
+  if (tid < 32) {
+    float v = 0.f;
+    if (tid < NEDGE) {
+#pragma unroll
+      for (int k = 0; k < GR_POS / 32; ++k) v += S.WA[k][tid];
+    }
+    part[256 + tid] = v;
+    part[288 + tid] = (tid < Q) ? S.GP[tid] : 0.f;
+  }
+}
+
+// partial records of model blockIdx.y -> grad_A (23 edges; the rest of the matrix is zeroed by the caller), grad_pi,
+// grad_Bfull.  Block x owns 32 consecutive record slots; warp w adds records w, w + 32, ... and warp 0 adds the 32 sums.
+__global__ void __launch_bounds__(1024) grad_reduce_kernel(const float* __restrict__ part, int nrec, float* __restrict__ gA,
+                                                           float* __restrict__ gpi, float* __restrict__ gB) {
+  __shared__ float red[32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, m = blockIdx.y, slot = blockIdx.x * 32 + lane;
+  const float* src = part + (size_t)m * nrec * GR_PART + slot;
+  float v = 0.f;
+  for (int j = warp; j < nrec; j += 32) v += __ldg(src + (size_t)j * GR_PART);
+  red[warp][lane] = v;
+  __syncthreads();
+  if (warp != 0) return;
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 32; ++k) s += red[k][lane];
+  if (slot < 256) {
+    const int q = slot >> 4, c = slot & 15;
+    if (gB && q < Q && c < Q) gB[(size_t)m * Q * Q + q * Q + c] = s;
+  } else if (slot < 256 + NEDGE) {
+    const int e = slot - 256;
+    if (gA) gA[(size_t)m * Q * Q + ESRC[e] * Q + EDST[e]] = s;
+  } else if (slot >= 288 && slot < 288 + Q) {
+    if (gpi) gpi[(size_t)m * Q + slot - 288] = s;
   }
 }
 
@@ -2036,10 +2225,63 @@ int emission(const float* inputs, int num_models, int batch, int T, const float*
   return 0;
 }
 
+size_t grad_workspace_size(int num_models, int batch, int T) {
+  if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
+  return (size_t)num_models * batch * cdiv(T, GR_POS) * GR_PART * sizeof(float);
+}
+
+int grad(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
+         const float* codon5, const float* hints, unsigned flags, const float* log_post, const float* log_ahat,
+         const float* grad_loglik, float* grad_inputs, float* grad_A, float* grad_pi, float* grad_Bfull, void* workspace,
+         size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
+  if (rc) return rc;
+  HMM_REQUIRE(A && pi, "genepred_grad: null A / pi");
+  HMM_REQUIRE(log_post && log_ahat && grad_loglik, "genepred_grad: null log_post / log_alpha_hat / grad_loglik");
+  HMM_REQUIRE(grad_inputs || grad_A || grad_pi || grad_Bfull, "genepred_grad: no gradient requested");
+  HMM_REQUIRE(!grad_inputs || (reinterpret_cast<uintptr_t>(grad_inputs) & 15) == 0, "genepred_grad: grad_inputs must be 16-byte aligned");
+  const int NB = num_models * batch;
+  GradArgs g{};
+  g.log_post = log_post; g.log_ahat = log_ahat; g.gll = grad_loglik; g.grad_inputs = grad_inputs;
+  g.PT = cdiv(T, GR_POS);
+  const size_t need = grad_workspace_size(num_models, batch, T);
+  if (!workspace || workspace_bytes < need) {
+    set_error("genepred_grad: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+    return HMM_B200_EWORKSPACE;
+  }
+  g.part = static_cast<float*>(workspace);
+  set_L(a, 32);   // codes_stage / emission helpers only need a valid chunk length
+  static bool smem_set = false;
+  if (!smem_set) {
+    HMM_CUDA_OK(cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GradSmem)));
+    smem_set = true;
+  }
+  if (grad_A) HMM_CUDA_OK(cudaMemsetAsync(grad_A, 0, (size_t)num_models * Q * Q * sizeof(float), st));
+  grad_kernel<<<dim3(g.PT, NB), GR_POS, sizeof(GradSmem), st>>>(a, g);
+  grad_reduce_kernel<<<dim3(GR_PART / 32, num_models), 1024, 0, st>>>(g.part, batch * g.PT, grad_A, grad_pi, grad_Bfull);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace gene15
 }  // namespace hmm
 
 extern "C" {
+
+size_t hmm_b200_genepred_grad_workspace_size(int num_models, int batch, int T) {
+  return hmm::gene15::grad_workspace_size(num_models, batch, T);
+}
+
+int hmm_b200_genepred_grad(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
+                           const float* Bfull, const float* codon5, const float* end_hints, unsigned flags,
+                           const float* log_post, const float* log_alpha_hat, const float* grad_loglik, float* grad_inputs,
+                           float* grad_A, float* grad_pi, float* grad_Bfull, void* workspace, size_t workspace_bytes,
+                           void* stream) {
+  return hmm::gene15::grad(inputs, num_models, batch, T, A, pi, Bfull, codon5, end_hints, flags, log_post, log_alpha_hat,
+                           grad_loglik, grad_inputs, grad_A, grad_pi, grad_Bfull, workspace, workspace_bytes,
+                           static_cast<cudaStream_t>(stream));
+}
 
 size_t hmm_b200_genepred_workspace_size(int num_models, int batch, int T) {
   return hmm::gene15::workspace_size(num_models, batch, T);

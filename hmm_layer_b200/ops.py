@@ -8,6 +8,7 @@ TRAINING = 1
 NO_LOGLIK = 2
 ALPHA_SCRATCH = 4
 BETA_SCRATCH = 8
+ALPHA_NORMALIZED = 16
 
 
 def _ptr(t):
@@ -79,7 +80,7 @@ def _codon5(codon):
 
 
 def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,
-                 want_post=True, want_alpha=False, want_beta=False, out=None):
+                 want_post=True, want_alpha=False, want_beta=False, out=None, alpha_normalized=False):
     """Fused 15-state gene-HMM evaluation.  inputs (k,B,T,20); codon = the emitter's (2,9,64) codon_probs or the
     prepared (2,125,12) tables (prepare_codon).  Returns dict with the requested tensors
     ('post','alpha','beta' each (k,B,T,15)) and 'loglik' (k,B)."""
@@ -102,12 +103,75 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
         res["loglik"] = torch.empty((k, B), dtype=torch.float32, device=dev)
         nbytes = lib.hmm_b200_genepred_workspace_size(k, B, T)
         ws = _workspace(nbytes, dev)
-        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0) | (ALPHA_NORMALIZED if alpha_normalized else 0)
         _lib.check(lib.hmm_b200_genepred_run(
             _ptr(inputs), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints), flags,
             _ptr(res.get("post")), _ptr(res.get("alpha")), _ptr(res.get("beta")), _ptr(res["loglik"]),
             _ptr(ws), ws.numel(), _stream()))
     return res
+
+
+def genepred_grad(inputs, A, pi, Bfull, codon, log_post, log_alpha_hat, grad_loglik, end_hints=None, training=False,
+                  want_inputs=True, want_A=True, want_pi=True, want_B=True):
+    """Gradient of sum(grad_loglik * loglik) of the fused gene-HMM evaluation (hmm_b200_genepred_grad).
+    log_post / log_alpha_hat: 'post' and 'alpha' of genepred_run(..., want_alpha=True, alpha_normalized=True).
+    Returns dict with 'inputs' (k,B,T,20), 'A' (k,15,15), 'pi' (k,15), 'Bfull' (k,15,15) as requested."""
+    lib = _lib.load()
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    k, B, T, _ = inputs.shape
+    inputs = _req(inputs, "inputs")
+    dev = inputs.device
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
+    log_post = _req(log_post, "log_post", (k, B, T, 15)); log_alpha_hat = _req(log_alpha_hat, "log_alpha_hat", (k, B, T, 15))
+    grad_loglik = _req(grad_loglik, "grad_loglik", (k, B))
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
+    if not (want_inputs or want_A or want_pi or want_B):
+        return {}
+    with torch.cuda.device(dev):
+        res = {}
+        if want_inputs:
+            res["inputs"] = torch.empty((k, B, T, 20), dtype=torch.float32, device=dev)
+        if want_A:
+            res["A"] = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+        if want_pi:
+            res["pi"] = torch.empty((k, 15), dtype=torch.float32, device=dev)
+        if want_B:
+            res["Bfull"] = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+        ws = _workspace(lib.hmm_b200_genepred_grad_workspace_size(k, B, T), dev)
+        _lib.check(lib.hmm_b200_genepred_grad(
+            _ptr(inputs), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints), TRAINING if training else 0,
+            _ptr(log_post), _ptr(log_alpha_hat), _ptr(grad_loglik), _ptr(res.get("inputs")), _ptr(res.get("A")),
+            _ptr(res.get("pi")), _ptr(res.get("Bfull")), _ptr(ws), ws.numel(), _stream()))
+    return res
+
+
+class GenePredLoglik(torch.autograd.Function):
+    """loglik (k,B) of the fused gene HMM, differentiable w.r.t. inputs (class probabilities), A, pi and Bfull.
+    Forward = one fused evaluation that also keeps log posterior and normalised forward vectors; backward = the
+    closed-form expected-count kernel.  codon / end_hints / training are constants of the graph."""
+
+    @staticmethod
+    def forward(ctx, inputs, A, pi, Bfull, codon, end_hints, training):
+        r = genepred_run(inputs, A, pi, Bfull, codon, end_hints=end_hints, training=training, want_post=True,
+                         want_alpha=True, alpha_normalized=True)
+        ctx.save_for_backward(inputs, A, pi, Bfull, codon, r["post"], r["alpha"])
+        ctx.end_hints, ctx.training = end_hints, training
+        return r["loglik"]
+
+    @staticmethod
+    def backward(ctx, grad_loglik):
+        inputs, A, pi, Bfull, codon, post, ahat = ctx.saved_tensors
+        need = ctx.needs_input_grad
+        g = genepred_grad(inputs, A, pi, Bfull, codon, post, ahat, grad_loglik.contiguous().to(torch.float32),
+                          end_hints=ctx.end_hints, training=ctx.training,
+                          want_inputs=need[0], want_A=need[1], want_pi=need[2], want_B=need[3])
+        gpi = g.get("pi")
+        if gpi is not None:
+            gpi = gpi.reshape(pi.shape)
+        return g.get("inputs"), g.get("A"), gpi, g.get("Bfull"), None, None, None
 
 
 def genepred_run_host(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,

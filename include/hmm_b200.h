@@ -30,6 +30,8 @@ extern "C" {
 #define HMM_B200_NO_LOGLIK 2u /* posterior without the "- loglik" (MsaHMMLayer.py:513-514) */
 #define HMM_B200_ALPHA_SCRATCH 4u /* dense_run: out_alpha is only lent as scratch, its final contents are not needed */
 #define HMM_B200_BETA_SCRATCH 8u  /* dense_run: same for out_beta */
+#define HMM_B200_ALPHA_NORMALIZED 16u /* genepred_run: out_alpha = log of the per-position normalised forward vector
+                                        (the scaled state of MsaHmmCell.py:92) instead of log alpha; input of genepred_grad */
 
 int hmm_b200_abi_version(void);
 const char* hmm_b200_last_error(void);
@@ -104,6 +106,29 @@ int hmm_b200_genepred_run_host(const float* host_inputs, int num_models, int bat
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
                                const float* Bfull, const float* codon5, const float* end_hints,
                                unsigned flags, float* out_E, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Gradient of the gene-HMM log-likelihood (training through the layer).  The reference has no backward code of its
+ * own: autograd differentiates its Python time loop (HmmCell.forward MsaHmmCell.py:73-106, the emitter
+ * gene_pred_hmm_emitter.py:93-121,231-263, parameters rebuilt per call :65,80 and gene_pred_hmm_transitioner.py:66-71).
+ * This entry point replaces that traced backward pass with the closed form (expected transition / emission counts):
+ *   log_post       (num_models, batch, T, 15)  out_post of hmm_b200_genepred_run (without HMM_B200_NO_LOGLIK)
+ *   log_alpha_hat  (num_models, batch, T, 15)  out_alpha of the same call made with HMM_B200_ALPHA_NORMALIZED
+ *   grad_loglik    (num_models, batch)         upstream gradient of every log-likelihood
+ *   grad_inputs    (num_models, batch, T, 20)  or NULL; the 5 nucleotide flags are data and get zeros
+ *   grad_A         (num_models, 15, 15)        or NULL; non-zero on the 23 gene-model edges only
+ *   grad_pi        (num_models, 15)            or NULL
+ *   grad_Bfull     (num_models, 15, 15)        or NULL; [state][class]
+ * flags: HMM_B200_TRAINING as in the forward call.  Deterministic (fixed-order partial sums, no atomics).
+ * --------------------------------------------------------------------------------------------------------- */
+size_t hmm_b200_genepred_grad_workspace_size(int num_models, int batch, int T);
+
+int hmm_b200_genepred_grad(const float* inputs, int num_models, int batch, int T,
+                           const float* A, const float* pi, const float* Bfull, const float* codon5,
+                           const float* end_hints, unsigned flags,
+                           const float* log_post, const float* log_alpha_hat, const float* grad_loglik,
+                           float* grad_inputs, float* grad_A, float* grad_pi, float* grad_Bfull,
+                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Sequence sharding over GPUs (one genome-length sequence cut into contiguous shards, one per rank).  Replaces
