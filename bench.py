@@ -301,6 +301,74 @@ def run_config5(args, rank, world, local):
         dist.destroy_process_group()
 
 
+def run_train(args, rank, world, local):
+    """`--train`: one TRAINING step of config 2 through the public layer API — MsaHmmLayer.forward (differentiable
+    log-likelihood) and loglik_mean.backward(): gradients for the emission / transition / start kernels and for the class
+    probabilities (the upstream network's output).  Same JSON line; batch-sharded over the ranks, no collective in the
+    timed region (a trainer would all-reduce the three small parameter gradients, 1.1 kB)."""
+    import torch.distributed as dist
+    from hmm_layer_b200 import synthetic as syn
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    k, B, T, q = WORKLOAD["num_models"], WORKLOAD["batch"], WORKLOAD["T"], WORKLOAD["q"]
+    layer, cell = build_layer(dev)
+    xs = [syn.gene_inputs(k, B, T, seed=1234 + 10 * rank).to(dev).requires_grad_(True) for _ in range(NBUF)]
+
+    def step(i):
+        x = xs[i % NBUF]
+        x.grad = None
+        layer.zero_grad(set_to_none=True)
+        loglik, mean = layer(x)
+        mean.backward()
+        return loglik
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    for i in range(max(args.warmup, 10)):
+        step(i)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / args.steps
+    grads_ok = all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in layer.parameters() if p.requires_grad)
+    if rank == 0:
+        peak, src = peaks()
+        alg = 140.0 * k * B * T     # 80 B inputs read + 60 B class-probability gradient written per position
+        achieved = world * alg / (ms_step * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": "hmm_cells_per_s", "value": world * syn.cells(k, B, T, q) / (ms_step * 1e-3), "unit": "cells/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 10), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "config2 TRAINING step: gene_pred 15-state HMM log-likelihood forward + gradient "
+                                   "(emission / transition / start kernels and class probabilities), batch 32 x 9999 bp per GPU",
+                       **WORKLOAD, "api": "MsaHmmLayer.forward(x) -> loglik_mean.backward()",
+                       "l2_policy": f"{NBUF} rotating input sets"},
+            "gpu_launches": 4 * args.steps, "grads_finite": grads_ok,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": world * peak, "unit": "GB/s",
+                         "frac": achieved / (world * peak), "traffic": None, "peak_source": src,
+                         "scope": "whole training step (products, finalize<alpha+posterior>, grad, grad_reduce + the host-side "
+                                  "parameter construction and its autograd); algorithmic bytes = 140 B/position"},
+            "clocks": clocks,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", type=int, default=2, choices=[2, 4, 5],
@@ -312,6 +380,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-spinup", action="store_true", help="skip the 0.3 s clock spin-up (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--train", action="store_true", help="config 2 training step (forward + gradient) instead of forward+posterior")
     ap.add_argument("--tune", default="", help="chunk_len,finalize_threads")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -323,6 +392,8 @@ def main():
         args.warmup = min(args.warmup, 1)
         return run_reference(args, rank)
 
+    if args.train:
+        return run_train(args, rank, world, local)
     if args.config == 4:
         return run_config4(args, rank, world, local)
     if args.config == 5:

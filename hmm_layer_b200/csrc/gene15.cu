@@ -1716,16 +1716,30 @@ __global__ void __launch_bounds__(GR_POS, 2) grad_kernel(const Args a, const Gra
   __syncthreads();
   float* part = g.part + ((size_t)n * g.PT + p) * GR_PART;
   {
-    // dB[q][c] = sum over the CTA's positions of r(q) x[c]
-    const int q = tid >> 4, c = tid & 15;
-    float acc0 = 0.f, acc1 = 0.f;
-    int i = 0;
-    for (; i + 1 < npos; i += 2) {
-      acc0 = fmaf(S.R[i][q], S.X[i * SIN + c], acc0);
-      acc1 = fmaf(S.R[i + 1][q], S.X[(i + 1) * SIN + c], acc1);
+    // dB[q][c] = sum over the CTA's positions of r(q) x[c]: lane = 2 x 4 block of (q, c), warp w takes positions w, w + 8, ...;
+    // the 8 warp sums are added in order through RED (the log posterior rows are dead by now)
+    float* RED = S.PS;
+    const int qt = lane >> 2, ct = lane & 3;
+    float acc[2][4];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k >> 2][k & 3] = 0.f;
+#pragma unroll 4
+    for (int i = warp; i < npos; i += GR_POS / 32) {
+      const float2 rv = *reinterpret_cast<const float2*>(&S.R[i][2 * qt]);
+      const float4 xv = *reinterpret_cast<const float4*>(&S.X[i * SIN + 4 * ct]);
+      acc[0][0] = fmaf(rv.x, xv.x, acc[0][0]); acc[0][1] = fmaf(rv.x, xv.y, acc[0][1]);
+      acc[0][2] = fmaf(rv.x, xv.z, acc[0][2]); acc[0][3] = fmaf(rv.x, xv.w, acc[0][3]);
+      acc[1][0] = fmaf(rv.y, xv.x, acc[1][0]); acc[1][1] = fmaf(rv.y, xv.y, acc[1][1]);
+      acc[1][2] = fmaf(rv.y, xv.z, acc[1][2]); acc[1][3] = fmaf(rv.y, xv.w, acc[1][3]);
     }
-    if (i < npos) acc0 = fmaf(S.R[i][q], S.X[i * SIN + c], acc0);
-    part[tid] = (c < Q) ? acc0 + acc1 : 0.f;
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      *reinterpret_cast<float4*>(&RED[warp * 256 + (2 * qt + h) * QP + 4 * ct]) = make_float4(acc[h][0], acc[h][1], acc[h][2], acc[h][3]);
+    __syncthreads();
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < GR_POS / 32; ++k) v += RED[k * 256 + tid];
+    part[tid] = ((tid & 15) < Q) ? v : 0.f;
   }
   if (tid < 32) {
     float v = 0.f;
