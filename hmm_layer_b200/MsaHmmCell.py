@@ -126,17 +126,41 @@ class HmmCell(nn.Module):
 
 
 class MsaHmmCell(HmmCell):
-    """Profile-HMM cell, q = 2*length+3 (reference :164-182).  The reference's default ProfileHMMEmitter /
-    ProfileHMMTransitioner cannot be constructed as shipped; this class therefore requires explicit
-    plugins that follow the emitter / transitioner interface."""
+    """Profile-HMM cell, q = 2*length+3 (reference :164-182).  Defaults to ProfileHMMEmitter / ProfileHMMTransitioner
+    like the reference.  The plugins learn the model lengths BEFORE the base constructor runs its first
+    `recurrent_init` (the shipped order, :179-182, initialises from plugins that do not know their size yet),
+    and the emitter is built for `dim` input symbols right away."""
 
     def __init__(self, length, dim=24, emitter=None, transitioner=None, **kwargs):
-        if emitter is None or transitioner is None:
-            raise ValueError("MsaHmmCell needs an emitter and a transitioner (see hmm_layer_b200.dense_plugins)")
+        from .Emitter import ProfileHMMEmitter
+        from .Transitioner import ProfileHMMTransitioner
         self.length = [length] if not isinstance(length, list) else length
-        super().__init__([2 * l + 3 for l in self.length], dim, emitter, transitioner, **kwargs)
-        for em in self.emitter:
+        k = len(self.length)
+        if emitter is None:
+            emitter = _default_emitter(k)
+        if transitioner is None:
+            transitioner = _default_transitioner(k)
+        for em in (emitter if isinstance(emitter, (list, tuple)) else [emitter]):
             if hasattr(em, "set_lengths"):
                 em.set_lengths(self.length)
-        if hasattr(self.transitioner, "set_lengths"):
-            self.transitioner.set_lengths(self.length)
+            if hasattr(em, "build") and not getattr(em, "built", True):
+                em.build((k, 1, 1, dim))
+        if hasattr(transitioner, "set_lengths"):
+            transitioner.set_lengths(self.length)
+        if hasattr(transitioner, "build"):
+            transitioner.build()
+        super().__init__([2 * l + 3 for l in self.length], dim, emitter, transitioner, **kwargs)
+
+
+def _default_emitter(k):
+    from . import Initializers as I
+    from .Emitter import ProfileHMMEmitter
+    return ProfileHMMEmitter(emission_init=[I.make_default_emission_init() for _ in range(k)],
+                             insertion_init=[I.make_default_insertion_init() for _ in range(k)])
+
+
+def _default_transitioner(k):
+    from . import Initializers as I
+    from .Transitioner import ProfileHMMTransitioner
+    return ProfileHMMTransitioner(transition_init=[I.make_default_transition_init() for _ in range(k)],
+                                  flank_init=[I.make_default_flank_init() for _ in range(k)])

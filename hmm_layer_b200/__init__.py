@@ -6,10 +6,12 @@ from .BaseRNN import BaseRNN
 from .Bidirectional import Bidirectional
 from .TotalProbabilityCell import TotalProbabilityCell
 from .dense_plugins import DenseEmitter, DenseTransitioner
+from .Emitter import ProfileHMMEmitter
+from .Transitioner import ProfileHMMTransitioner
 from .gene_pred_hmm_emitter import GenePredHMMEmitter, SimpleGenePredHMMEmitter
 from .gene_pred_hmm_transitioner import (GenePredHMMTransitioner, GenePredMultiHMMTransitioner,
                                          SimpleGenePredHMMTransitioner)
 
 __all__ = ["HmmCell", "MsaHmmCell", "MsaHmmLayer", "BaseRNN", "Bidirectional", "TotalProbabilityCell", "DenseEmitter",
-           "DenseTransitioner", "GenePredHMMEmitter", "SimpleGenePredHMMEmitter",
+           "DenseTransitioner", "ProfileHMMEmitter", "ProfileHMMTransitioner", "GenePredHMMEmitter", "SimpleGenePredHMMEmitter",
            "GenePredHMMTransitioner", "GenePredMultiHMMTransitioner", "SimpleGenePredHMMTransitioner"]

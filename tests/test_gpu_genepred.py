@@ -234,7 +234,7 @@ def test_layer_accepts_cpu_inputs_and_returns_cpu_outputs():
     assert not p_host.is_cuda and p_dev.is_cuda
     np.testing.assert_allclose(np.exp(p_host.numpy()), np.exp(p_dev.cpu().numpy()), atol=2e-5)
     ll_h, _ = layer(x)
-    ll_d, _ = layer(x.cuda())
+    ll_d = layer(x.cuda())[0].detach()   # differentiable call: the output carries a graph
     np.testing.assert_allclose(ll_h.numpy(), ll_d.cpu().numpy(), rtol=1e-6)
 
 
@@ -253,7 +253,7 @@ def test_config3_full_size_through_the_layer():
     layer = H.MsaHmmLayer(cell, use_prior=False)
     x = syn.gene_inputs(1, B, T, seed=3333)
     post = layer.state_posterior_log_probs(x.cuda())
-    loglik, _ = layer(x.cuda())
+    loglik = layer(x.cuda())[0].detach()
     torch.cuda.synchronize()
     assert post.shape == (1, B, T, 15) and bool(torch.isfinite(post).all())
     s = torch.exp(post.double()).sum(-1)
