@@ -148,6 +148,21 @@ class MsaHmmLayer(nn.Module):
                                                return_prior=return_prior, training=training, no_loglik=no_loglik,
                                                parallel_factor=self.parallel_factor)
 
+    def viterbi(self, inputs, end_hints=None, training=False, return_score=False):
+        """Most probable state path (num_model, b, seq_len) int64 — the decoding the reference names (MsaHmmCell.py:13,
+        `log_A_dense` :46-47) but does not ship.  Fused gene model only."""
+        self.build(inputs.shape)
+        cell = self.cell
+        cell.recurrent_init()
+        _check_inputs(inputs, cell, 1)
+        if not _is_fused_gene_cell(cell) or not inputs.is_cuda:
+            raise NotImplementedError("viterbi is implemented for the 15-state gene model with CUDA inputs")
+        em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
+        path, score = ops.genepred_viterbi(inputs, tr.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1),
+                                           em.make_B_full().detach(), em.codon5(inputs.device), end_hints=end_hints,
+                                           training=training)
+        return (path.long(), score) if return_score else path.long()
+
     def apply_sequence_weights(self, loglik, indices, aggregate=False):
         if self.sequence_weights is not None:
             weights = self.sequence_weights[indices]

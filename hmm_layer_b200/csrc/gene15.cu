@@ -1779,6 +1779,113 @@ __global__ void __launch_bounds__(1024) grad_reduce_kernel(const float* __restri
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Viterbi decoding (most probable state path).  The reference names it (MsaHmmCell.py:13, log_A_dense :46-47) but does
+// not implement it; the recursion is the max-product form of MsaHmmCell.py:73-106 over the same floored quantities:
+//   delta_0 = log max(pi, eps) + log max(E_0, eps),  delta_t(j) = max_i (delta_{t-1}(i) + log A[i][j]) + log max(E_t(j), eps),
+// ties to the lowest state index.  One warp per sequence (lane = state; a gene-model state has at most 3 in-edges):
+// the recursion is a chain of T dependent steps, so this kernel is latency-bound by construction; emissions come from
+// the emission kernel's buffer 16 steps ahead of their use, back-pointers go to a byte table that the same warp walks
+// backwards through shared memory, 2048 steps at a time.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int VT_PF = 16;       // emission prefetch depth (steps)
+constexpr int VT_BLK = 2048;    // back-pointer steps staged per backtracking round
+
+__global__ void __launch_bounds__(32) viterbi_kernel(const float* __restrict__ E, const float* __restrict__ A,
+                                                     const float* __restrict__ pi, int batch, int T,
+                                                     unsigned char* __restrict__ psi, unsigned char* __restrict__ path,
+                                                     float* __restrict__ score) {
+  __shared__ uint4 pbuf[VT_BLK];
+  __shared__ unsigned char obuf[VT_BLK];
+  const int n = blockIdx.x, m = n / batch, lane = threadIdx.x;
+  const bool live = lane < Q;
+  const int j = live ? lane : 0;
+  const float NEG = -INFINITY;
+  int src[3] = {0, 0, 0};
+  float la[3] = {NEG, NEG, NEG};
+  {
+    int ns = 0;
+    for (int i = 0; i < Q; ++i) {
+      const float a = __ldg(A + (size_t)m * Q * Q + i * Q + j);
+      if (a > 0.f && ns < 3 && live) {
+        if (ns == 0) { src[0] = i; la[0] = logf(a); }
+        else if (ns == 1) { src[1] = i; la[1] = logf(a); }
+        else { src[2] = i; la[2] = logf(a); }
+        ++ns;
+      }
+    }
+  }
+  const float* Erow = E + (size_t)n * T * Q + j;
+  unsigned char* prow = psi + (size_t)n * T * 16;
+  float delta = live ? logf(fmaxf(__ldg(pi + m * Q + j), kEps)) + logf(fmaxf(__ldg(Erow), kEps)) : NEG;
+  double offset = 0.0;
+  float ecur[VT_PF], enext[VT_PF];
+#pragma unroll
+  for (int u = 0; u < VT_PF; ++u) ecur[u] = (1 + u < T) ? __ldg(Erow + (size_t)(1 + u) * Q) : 1.f;
+  for (int tb = 1; tb < T; tb += VT_PF) {
+#pragma unroll
+    for (int u = 0; u < VT_PF; ++u) enext[u] = (tb + VT_PF + u < T) ? __ldg(Erow + (size_t)(tb + VT_PF + u) * Q) : 1.f;
+#pragma unroll
+    for (int u = 0; u < VT_PF; ++u) {
+      const int t = tb + u;
+      if (t < T) {   // warp-uniform
+        const float c0 = __shfl_sync(0xffffffffu, delta, src[0]) + la[0];
+        const float c1 = __shfl_sync(0xffffffffu, delta, src[1]) + la[1];
+        const float c2 = __shfl_sync(0xffffffffu, delta, src[2]) + la[2];
+        float best = c0;
+        int arg = src[0];
+        if (c1 > best) { best = c1; arg = src[1]; }
+        if (c2 > best) { best = c2; arg = src[2]; }
+        delta = live ? best + logf(fmaxf(ecur[u], kEps)) : NEG;
+        if (lane < 16) prow[(size_t)t * 16 + lane] = (unsigned char)arg;
+      }
+    }
+    {   // keep the magnitudes small: take the running maximum out (exact bookkeeping in double)
+      float mx = delta;
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      delta -= mx;
+      offset += (double)mx;
+    }
+#pragma unroll
+    for (int u = 0; u < VT_PF; ++u) ecur[u] = enext[u];
+  }
+  // best final state, lowest index on ties
+  float bv = delta;
+  int bs = live ? lane : Q;
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int os = __shfl_xor_sync(0xffffffffu, bs, o);
+    if (ov > bv || (ov == bv && os < bs)) { bv = ov; bs = os; }
+  }
+  if (lane == 0 && score) score[n] = (float)(offset + (double)bv);
+  // backtracking: s_{t-1} = psi_t(s_t)
+  __threadfence_block();
+  __syncwarp();
+  int s = bs;
+  unsigned char* out = path + (size_t)n * T;
+  const uint4* pg = reinterpret_cast<const uint4*>(prow);
+  for (int hi = T - 1; hi >= 1;) {
+    const int lo = max(1, hi - (VT_BLK - 1)), cnt = hi - lo + 1;
+    for (int i = lane; i < cnt; i += 32) pbuf[i] = pg[lo + i];
+    __syncwarp();
+    if (lane == 0) {
+      const unsigned char* pb = reinterpret_cast<const unsigned char*>(pbuf);
+      for (int t = hi; t >= lo; --t) {
+        obuf[t - lo] = (unsigned char)s;
+        s = pb[(t - lo) * 16 + s];
+      }
+    }
+    __syncwarp();
+    for (int i = lane; i < cnt; i += 32) out[lo + i] = obuf[i];
+    s = __shfl_sync(0xffffffffu, s, 0);
+    hi = lo - 1;
+    __syncwarp();
+  }
+  if (lane == 0) out[0] = (unsigned char)s;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
 static int g_L = 0;          // 0: choose per call
@@ -2278,10 +2385,46 @@ int grad(const float* inputs, int num_models, int batch, int T, const float* A, 
   return 0;
 }
 
+size_t viterbi_workspace_size(int num_models, int batch, int T) {
+  if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
+  const size_t NBT = (size_t)num_models * batch * T;
+  return align_up(NBT * Q * sizeof(float), 256) + align_up(NBT * 16, 256);
+}
+
+int viterbi(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
+            const float* codon5, const float* hints, unsigned flags, unsigned char* path, float* score, void* workspace,
+            size_t workspace_bytes, cudaStream_t st) {
+  HMM_REQUIRE(A && pi && path, "genepred_viterbi: null A / pi / path");
+  const size_t need = viterbi_workspace_size(num_models, batch, T);
+  if (!workspace || workspace_bytes < need) {
+    set_error("genepred_viterbi: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+    return HMM_B200_EWORKSPACE;
+  }
+  HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred_viterbi: workspace must be 256-byte aligned");
+  float* E = static_cast<float*>(workspace);
+  unsigned char* psi = static_cast<unsigned char*>(workspace) + align_up((size_t)num_models * batch * T * Q * sizeof(float), 256);
+  int rc = emission(inputs, num_models, batch, T, Bfull, codon5, hints, flags, E, st);
+  if (rc) return rc;
+  viterbi_kernel<<<num_models * batch, 32, 0, st>>>(E, A, pi, batch, T, psi, path, score);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace gene15
 }  // namespace hmm
 
 extern "C" {
+
+size_t hmm_b200_genepred_viterbi_workspace_size(int num_models, int batch, int T) {
+  return hmm::gene15::viterbi_workspace_size(num_models, batch, T);
+}
+
+int hmm_b200_genepred_viterbi(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
+                              const float* Bfull, const float* codon5, const float* end_hints, unsigned flags,
+                              unsigned char* path, float* score, void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::gene15::viterbi(inputs, num_models, batch, T, A, pi, Bfull, codon5, end_hints, flags, path, score, workspace,
+                              workspace_bytes, static_cast<cudaStream_t>(stream));
+}
 
 size_t hmm_b200_genepred_grad_workspace_size(int num_models, int batch, int T) {
   return hmm::gene15::grad_workspace_size(num_models, batch, T);

@@ -111,6 +111,29 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
     return res
 
 
+def genepred_viterbi(inputs, A, pi, Bfull, codon, end_hints=None, training=False):
+    """Most probable state path of the 15-state gene HMM (hmm_b200_genepred_viterbi).  inputs (k,B,T,20) CUDA.
+    Returns (path (k,B,T) uint8, score (k,B) float32 = log joint probability of the path)."""
+    lib = _lib.load()
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    k, B, T, _ = inputs.shape
+    inputs = _req(inputs, "inputs")
+    dev = inputs.device
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, 15))
+    with torch.cuda.device(dev):
+        path = torch.empty((k, B, T), dtype=torch.uint8, device=dev)
+        score = torch.empty((k, B), dtype=torch.float32, device=dev)
+        ws = _workspace(lib.hmm_b200_genepred_viterbi_workspace_size(k, B, T), dev)
+        _lib.check(lib.hmm_b200_genepred_viterbi(
+            _ptr(inputs), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints), TRAINING if training else 0,
+            _ptr(path), _ptr(score), _ptr(ws), ws.numel(), _stream()))
+    return path, score
+
+
 def genepred_grad(inputs, A, pi, Bfull, codon, log_post, log_alpha_hat, grad_loglik, end_hints=None, training=False,
                   want_inputs=True, want_A=True, want_pi=True, want_B=True):
     """Gradient of sum(grad_loglik * loglik) of the fused gene-HMM evaluation (hmm_b200_genepred_grad).

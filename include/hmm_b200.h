@@ -131,6 +131,21 @@ int hmm_b200_genepred_grad(const float* inputs, int num_models, int batch, int T
                            void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * Viterbi decoding of the gene HMM: most probable state path.  The reference names Viterbi (MsaHmmCell.py:13) and
+ * prepares log_A_dense for it (:46-47) but ships no implementation; this is the max-product form of the recursion
+ * MsaHmmCell.py:73-106 over the same floored emissions / initial distribution, ties to the lowest state index.
+ *   path   (num_models, batch, T) uint8 state indices      score (num_models, batch) log joint of the path, or NULL
+ * The emission tensor is materialised in the workspace (this path is latency-bound: T dependent steps per sequence).
+ * --------------------------------------------------------------------------------------------------------- */
+size_t hmm_b200_genepred_viterbi_workspace_size(int num_models, int batch, int T);
+
+int hmm_b200_genepred_viterbi(const float* inputs, int num_models, int batch, int T,
+                              const float* A, const float* pi, const float* Bfull, const float* codon5,
+                              const float* end_hints, unsigned flags,
+                              unsigned char* path, float* score,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Sequence sharding over GPUs (one genome-length sequence cut into contiguous shards, one per rank).  Replaces
  * the reference's chunk combine with the chunks living on different devices:
  *   _get_total_forward_from_chunks / _get_total_backward_from_chunks   MsaHMMLayer.py:285-319, 384-419
