@@ -51,6 +51,7 @@ constexpr int G = 32;         // chunks per tile
 constexpr int HEAP = 2 * G;   // blocks per tile in heap order: [1] tile product, [2..G) inner nodes, [G..2G) chunks
 constexpr int MAX_SCAN_TILES = 60;    // K1's last CTA of a sequence scans up to this many tile matrices itself
 constexpr int K1_THREADS = G * 16;
+constexpr unsigned EMIT_LOG_FLOORED = 0x40000000u;   // internal flag of emission_kernel (not part of the C ABI)
 #ifndef HMM_K1_BLOCKS
 #define HMM_K1_BLOCKS 2               // CTAs of K1 per SM the register budget is sized for (1: 128 regs, 2: 64 regs)
 #endif
@@ -1573,9 +1574,11 @@ __global__ void __launch_bounds__(512) emission_kernel(const Args a, float* __re
   }
   __syncthreads();
   const size_t obase = ((size_t)n * T + t_lo) * Q;
+  const bool as_log = (a.flags & EMIT_LOG_FLOORED) != 0;   // Viterbi's operand: log max(E, eps)
   for (int i = tid; i < npos * Q; i += nt) {
     const int pos = i / Q, j = i - pos * Q;
-    out[obase + i] = X[tile_row_offset(a, pos, CS) + j];
+    const float v = X[tile_row_offset(a, pos, CS) + j];
+    out[obase + i] = as_log ? logf(fmaxf(v, kEps)) : v;
   }
 }
 
@@ -1787,26 +1790,30 @@ __global__ void __launch_bounds__(1024) grad_reduce_kernel(const float* __restri
 // the emission kernel's buffer 16 steps ahead of their use, back-pointers go to a byte table that the same warp walks
 // backwards through shared memory, 2048 steps at a time.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int VT_PF = 16;       // emission prefetch depth (steps)
-constexpr int VT_BLK = 2048;    // back-pointer steps staged per backtracking round
+constexpr int VT_PF = 16;       // steps per block = emission prefetch depth
+constexpr int VT_BLK = 2048;    // back-pointer steps staged per backtracking round (64 per lane)
+constexpr int VT_SEG = VT_BLK / 32;
 
+// Back-pointer table: step k (position t = k + 1) of state j is byte (k & 3) of word (k >> 2) * 16 + j, so that a lane
+// stores one word per 4 steps.
 __global__ void __launch_bounds__(32) viterbi_kernel(const float* __restrict__ E, const float* __restrict__ A,
                                                      const float* __restrict__ pi, int batch, int T,
-                                                     unsigned char* __restrict__ psi, unsigned char* __restrict__ path,
+                                                     unsigned* __restrict__ psi, size_t psi_words, unsigned char* __restrict__ path,
                                                      float* __restrict__ score) {
-  __shared__ uint4 pbuf[VT_BLK];
+  __shared__ unsigned pbuf[VT_BLK / 4 * 16];     // 2048 steps of back-pointers
+  __shared__ unsigned char comp[32][16];         // per segment: state at its first step given the state after its last step
   __shared__ unsigned char obuf[VT_BLK];
   const int n = blockIdx.x, m = n / batch, lane = threadIdx.x;
   const bool live = lane < Q;
   const int j = live ? lane : 0;
   const float NEG = -INFINITY;
   int src[3] = {0, 0, 0};
-  float la[3] = {NEG, NEG, NEG};
-  {
+  float la[3] = {NEG, NEG, NEG};   // dead lanes keep -inf on every in-edge: their delta stays -inf without a select
+  if (live) {
     int ns = 0;
     for (int i = 0; i < Q; ++i) {
       const float a = __ldg(A + (size_t)m * Q * Q + i * Q + j);
-      if (a > 0.f && ns < 3 && live) {
+      if (a > 0.f && ns < 3) {
         if (ns == 0) { src[0] = i; la[0] = logf(a); }
         else if (ns == 1) { src[1] = i; la[1] = logf(a); }
         else { src[2] = i; la[2] = logf(a); }
@@ -1815,39 +1822,55 @@ __global__ void __launch_bounds__(32) viterbi_kernel(const float* __restrict__ E
     }
   }
   const float* Erow = E + (size_t)n * T * Q + j;
-  unsigned char* prow = psi + (size_t)n * T * 16;
-  float delta = live ? logf(fmaxf(__ldg(pi + m * Q + j), kEps)) + logf(fmaxf(__ldg(Erow), kEps)) : NEG;
+  unsigned* pw = psi + (size_t)n * psi_words + (lane & 15);
+  float delta = live ? logf(fmaxf(__ldg(pi + m * Q + j), kEps)) + __ldg(Erow) : NEG;
   double offset = 0.0;
-  float ecur[VT_PF], enext[VT_PF];
+  const int K = T - 1;   // steps
+  // one step: the delta chain is shuffle -> add -> max -> max -> add; the back-pointer (lowest source among the maxima)
+  // is worked out beside it
+  auto step = [&](float e, unsigned& word, int byte) {
+    const float c0 = __shfl_sync(0xffffffffu, delta, src[0]) + la[0];
+    const float c1 = __shfl_sync(0xffffffffu, delta, src[1]) + la[1];
+    const float c2 = __shfl_sync(0xffffffffu, delta, src[2]) + la[2];
+    const float best = fmaxf(fmaxf(c0, c1), c2);
+    const int arg = (c0 == best) ? src[0] : (c1 == best) ? src[1] : src[2];
+    word |= (unsigned)arg << (8 * byte);
+    delta = best + e;
+  };
+  auto renorm = [&]() {   // keep the magnitudes small: take the running maximum out (exact bookkeeping in double)
+    float mx = delta;
 #pragma unroll
-  for (int u = 0; u < VT_PF; ++u) ecur[u] = (1 + u < T) ? __ldg(Erow + (size_t)(1 + u) * Q) : 1.f;
-  for (int tb = 1; tb < T; tb += VT_PF) {
+    for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    delta -= mx;
+    offset += (double)mx;
+  };
+  // E holds log max(E_t, eps) (emission_kernel, EMIT_LOG_FLOORED).  Two register sets alternate: while the chain consumes
+  // one block of VT_PF steps, the loads of the next block are in flight into the other set (no register moves)
+  float ea[VT_PF], eb[VT_PF];
+  auto run_block = [&](const float (&use)[VT_PF], float (&fill)[VT_PF], int kb) {   // steps kb .. kb + VT_PF - 1, all < K
 #pragma unroll
-    for (int u = 0; u < VT_PF; ++u) enext[u] = (tb + VT_PF + u < T) ? __ldg(Erow + (size_t)(tb + VT_PF + u) * Q) : 1.f;
+    for (int u = 0; u < VT_PF; ++u) fill[u] = (kb + VT_PF + u < K) ? __ldg(Erow + (size_t)(kb + VT_PF + u + 1) * Q) : 0.f;
 #pragma unroll
-    for (int u = 0; u < VT_PF; ++u) {
-      const int t = tb + u;
-      if (t < T) {   // warp-uniform
-        const float c0 = __shfl_sync(0xffffffffu, delta, src[0]) + la[0];
-        const float c1 = __shfl_sync(0xffffffffu, delta, src[1]) + la[1];
-        const float c2 = __shfl_sync(0xffffffffu, delta, src[2]) + la[2];
-        float best = c0;
-        int arg = src[0];
-        if (c1 > best) { best = c1; arg = src[1]; }
-        if (c2 > best) { best = c2; arg = src[2]; }
-        delta = live ? best + logf(fmaxf(ecur[u], kEps)) : NEG;
-        if (lane < 16) prow[(size_t)t * 16 + lane] = (unsigned char)arg;
-      }
+    for (int g4 = 0; g4 < VT_PF / 4; ++g4) {
+      unsigned word = 0;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) step(use[g4 * 4 + b], word, b);
+      if (lane < 16) pw[(size_t)((kb >> 2) + g4) * 16] = word;
     }
-    {   // keep the magnitudes small: take the running maximum out (exact bookkeeping in double)
-      float mx = delta;
+    renorm();
+  };
 #pragma unroll
-      for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      delta -= mx;
-      offset += (double)mx;
-    }
-#pragma unroll
-    for (int u = 0; u < VT_PF; ++u) ecur[u] = enext[u];
+  for (int u = 0; u < VT_PF; ++u) ea[u] = (u < K) ? __ldg(Erow + (size_t)(u + 1) * Q) : 0.f;
+  int kb = 0;
+  for (; kb + 2 * VT_PF <= K; kb += 2 * VT_PF) {
+    run_block(ea, eb, kb);
+    run_block(eb, ea, kb + VT_PF);
+  }
+  for (; kb < K; kb += 4) {   // tail: fewer than 2 * VT_PF steps, plain loads
+    unsigned word = 0;
+    for (int b = 0; b < 4 && kb + b < K; ++b) step(__ldg(Erow + (size_t)(kb + b + 1) * Q), word, b);
+    if (lane < 16) pw[(size_t)(kb >> 2) * 16] = word;
+    renorm();
   }
   // best final state, lowest index on ties
   float bv = delta;
@@ -1859,30 +1882,60 @@ __global__ void __launch_bounds__(32) viterbi_kernel(const float* __restrict__ E
     if (ov > bv || (ov == bv && os < bs)) { bv = ov; bs = os; }
   }
   if (lane == 0 && score) score[n] = (float)(offset + (double)bv);
-  // backtracking: s_{t-1} = psi_t(s_t)
+
+  // ---- backtracking: state before step k = psi_k(state after step k).  Rounds of VT_BLK steps from the end; inside a
+  // round every lane first composes the back-pointer maps of its own 64-step segment for all 15 end states (parallel),
+  // lane 0 chains the 32 segment maps, then every lane replays its segment from its now known end state ----
   __threadfence_block();
   __syncwarp();
-  int s = bs;
+  int s_after = bs;                          // state after the last step of the round = state at position hi_k + 1
   unsigned char* out = path + (size_t)n * T;
-  const uint4* pg = reinterpret_cast<const uint4*>(prow);
-  for (int hi = T - 1; hi >= 1;) {
-    const int lo = max(1, hi - (VT_BLK - 1)), cnt = hi - lo + 1;
-    for (int i = lane; i < cnt; i += 32) pbuf[i] = pg[lo + i];
+  if (lane == 0) out[T - 1] = (unsigned char)bs;
+  const unsigned* pg = psi + (size_t)n * psi_words;
+  const unsigned char* pb = reinterpret_cast<const unsigned char*>(pbuf);
+  for (int hi = K; hi > 0;) {                // steps [lo, hi) of this round; lo is a multiple of 4
+    const int lo = (hi > VT_BLK) ? ((hi - VT_BLK + 3) & ~3) : 0, cnt = hi - lo;
+    const int nw = ((cnt + 3) >> 2) * 16;
+    for (int i = lane; i < nw; i += 32) pbuf[i] = pg[(size_t)(lo >> 2) * 16 + i];
     __syncwarp();
-    if (lane == 0) {
-      const unsigned char* pb = reinterpret_cast<const unsigned char*>(pbuf);
-      for (int t = hi; t >= lo; --t) {
-        obuf[t - lo] = (unsigned char)s;
-        s = pb[(t - lo) * 16 + s];
+    // segment of this lane: local steps [a, b)
+    const int a = min(lane * VT_SEG, cnt), b = min(a + VT_SEG, cnt);
+    {
+      int st[Q];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) st[q] = q;
+      for (int k = b - 1; k >= a; --k) {
+        const unsigned char* row = pb + (size_t)(k >> 2) * 64 + (k & 3);
+#pragma unroll
+        for (int q = 0; q < Q; ++q) st[q] = row[st[q] * 4];
+      }
+#pragma unroll
+      for (int q = 0; q < Q; ++q) comp[lane][q] = (unsigned char)st[q];
+    }
+    __syncwarp();
+    // state after each segment's last step, from the last segment backwards
+    int mine = 0;
+    {
+      int cur = s_after;
+      for (int g = 31; g >= 0; --g) {
+        if (g == lane) mine = cur;
+        cur = comp[g][cur];
+      }
+      s_after = cur;                         // state before step lo = state after the previous round's last step
+    }
+    // replay: position of local step k is lo + k + 1; the state BEFORE step k is the state at position lo + k
+    {
+      int cur = mine;
+      for (int k = b - 1; k >= a; --k) {
+        cur = pb[(size_t)(k >> 2) * 64 + cur * 4 + (k & 3)];
+        obuf[k] = (unsigned char)cur;
       }
     }
     __syncwarp();
     for (int i = lane; i < cnt; i += 32) out[lo + i] = obuf[i];
-    s = __shfl_sync(0xffffffffu, s, 0);
-    hi = lo - 1;
     __syncwarp();
+    hi = lo;
   }
-  if (lane == 0) out[0] = (unsigned char)s;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -2385,10 +2438,12 @@ int grad(const float* inputs, int num_models, int batch, int T, const float* A, 
   return 0;
 }
 
+static size_t viterbi_psi_words(int T) { return (size_t)((T + 2) / 4 + 1) * 16; }   // words per sequence
+
 size_t viterbi_workspace_size(int num_models, int batch, int T) {
   if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
   const size_t NBT = (size_t)num_models * batch * T;
-  return align_up(NBT * Q * sizeof(float), 256) + align_up(NBT * 16, 256);
+  return align_up(NBT * Q * sizeof(float), 256) + align_up((size_t)num_models * batch * viterbi_psi_words(T) * 4, 256);
 }
 
 int viterbi(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
@@ -2402,10 +2457,10 @@ int viterbi(const float* inputs, int num_models, int batch, int T, const float* 
   }
   HMM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "genepred_viterbi: workspace must be 256-byte aligned");
   float* E = static_cast<float*>(workspace);
-  unsigned char* psi = static_cast<unsigned char*>(workspace) + align_up((size_t)num_models * batch * T * Q * sizeof(float), 256);
-  int rc = emission(inputs, num_models, batch, T, Bfull, codon5, hints, flags, E, st);
+  unsigned* psi = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(workspace) + align_up((size_t)num_models * batch * T * Q * sizeof(float), 256));
+  int rc = emission(inputs, num_models, batch, T, Bfull, codon5, hints, flags | EMIT_LOG_FLOORED, E, st);
   if (rc) return rc;
-  viterbi_kernel<<<num_models * batch, 32, 0, st>>>(E, A, pi, batch, T, psi, path, score);
+  viterbi_kernel<<<num_models * batch, 32, 0, st>>>(E, A, pi, batch, T, psi, viterbi_psi_words(T), path, score);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
