@@ -42,6 +42,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self._stop_evt = index, [], set(), None, threading.Event()
+        self.interval = float(os.environ.get("HMM_BENCH_SAMPLE_S", "0.005"))
 
     def run(self):
         try:
@@ -56,7 +57,7 @@ class ClockSampler(threading.Thread):
                 r = nv.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
                     else nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                 self.reasons |= {k for k, bit in names.items() if r & bit}
-                time.sleep(0.005)
+                time.sleep(self.interval)
         except Exception as e:  # noqa: BLE001
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
@@ -65,6 +66,25 @@ class ClockSampler(threading.Thread):
         self.join(timeout=2)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def bind_to_gpu_numa_node(index):
+    """Pins this process to the CPUs NVML reports as closest to GPU `index` (what NCCL does for its own threads).  Pinned
+    host buffers are placed on the NUMA node of the allocating thread; a buffer on the remote socket makes every PCIe copy
+    of the host-buffer path ~30 % slower (measured: 0.81 vs 1.05 ms per config-2 call, tools/e2e_bench_probe.py)."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(index)
+        before = sorted(os.sched_getaffinity(0))
+        nv.nvmlDeviceSetCpuAffinity(h)
+        after = sorted(os.sched_getaffinity(0))
+        if not after:
+            os.sched_setaffinity(0, before)
+            return "unchanged (empty set)"
+        return f"{len(before)} -> {len(after)} cpus"
+    except Exception as e:  # noqa: BLE001
+        return f"unavailable:{type(e).__name__}"
 
 
 def build_layer(dev):
@@ -451,7 +471,8 @@ def main():
     # ---- end-to-end through the public layer API with host buffers ----
     # (CPU tensor in -> CPU tensor out: the layer hands host buffers to hmm_b200_genepred_run_host, which slices the
     # batch and overlaps H2D, kernels and D2H; every step moves its own inputs up and its own posterior down)
-    # (30 untimed calls first: the first few dozen host-buffer calls of a process run ~50 % slower than steady state)
+    # (30 untimed calls first.  The same call is bimodal on the test boxes: 0.81 ms or 1.07 ms per call for a whole loop,
+    # clocks at maximum in both, raw C call 0.77-0.80 ms in both — tools/e2e_bench_probe.py; this leg reports what it sees)
     n_e2e_warm = 0 if args.no_e2e else max(30, args.warmup)
     for _ in range(n_e2e_warm):
         layer.state_posterior_log_probs(host_in)
