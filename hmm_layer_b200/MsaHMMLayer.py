@@ -191,12 +191,15 @@ class MsaHmmLayer(nn.Module):
         inputs = inputs.to(torch.float32)
         self.build(inputs.shape)
         cell = self.cell
-        diff = torch.is_grad_enabled() and _is_fused_gene_cell(cell) and inputs.is_cuda and (
+        diff = torch.is_grad_enabled() and inputs.is_cuda and (
             inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
         cell.recurrent_init(fresh=diff)
         _check_inputs(inputs, cell, self.parallel_factor)
-        if diff:
+        if diff and _is_fused_gene_cell(cell):
             loglik = _gene_loglik_diff(inputs, cell, training)
+        elif diff:   # any other cell: emissions, A and pi stay attached to the parameters' graph
+            E = cell.emission_probs(inputs, training=training)
+            loglik = ops.DenseLoglik.apply(E, cell.transitioner.A, cell.init_dist.reshape(cell.num_models, -1))
         elif _is_fused_gene_cell(cell):
             loglik = _gene_run(inputs, cell, None, training, want_post=False)["loglik"]
         else:

@@ -183,7 +183,7 @@ __global__ void cum_kernel(const float* __restrict__ hist_f, const float* __rest
 __global__ void finish_kernel(float* __restrict__ alpha, float* __restrict__ beta, float* __restrict__ post,
                               const float* __restrict__ hist_f, const float* __restrict__ part_f, const float* __restrict__ cum_f,
                               const float* __restrict__ cum_b, const float* __restrict__ loglik, int N, int T, int q, int ntile,
-                              int no_loglik, int keep_a, int keep_b) {
+                              int no_loglik, int keep_a, int keep_b, int norm_a) {
   const size_t row = blockIdx.x;           // (n, t)
   const int n = (int)(row / T), t = (int)(row - (size_t)n * T);
   float S = 1.f, cf = 0.f, cb = 0.f;
@@ -201,7 +201,7 @@ __global__ void finish_kernel(float* __restrict__ alpha, float* __restrict__ bet
     if (alpha) { la = logf(alpha[i] * invS) + cf; }
     if (beta) { lb = logf(beta[i]) + cb; }
     if (post) post[i] = la + lb - ll;
-    if (alpha && keep_a) alpha[i] = la;
+    if (alpha && keep_a) alpha[i] = norm_a ? la - cf : la;   // norm_a: log of the normalised forward vector (HMM_B200_ALPHA_NORMALIZED)
     if (beta && keep_b) beta[i] = lb;
   }
 }
@@ -351,7 +351,8 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     finish_kernel<<<(unsigned)(N * T), 128, 0, st>>>(need_f ? out_alpha : nullptr, need_b ? out_beta : nullptr, out_post,
                                                      F(l.hist[0]), part_f, F(l.cum[0]), F(l.cum[1]), llbuf, (int)N, T, q, ntile,
                                                      (flags & HMM_B200_NO_LOGLIK) ? 1 : 0,
-                                                     (flags & HMM_B200_ALPHA_SCRATCH) ? 0 : 1, (flags & HMM_B200_BETA_SCRATCH) ? 0 : 1);
+                                                     (flags & HMM_B200_ALPHA_SCRATCH) ? 0 : 1, (flags & HMM_B200_BETA_SCRATCH) ? 0 : 1,
+                                                     (flags & HMM_B200_ALPHA_NORMALIZED) ? 1 : 0);
   }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;

@@ -308,7 +308,7 @@ def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
     return E
 
 
-def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_loglik=False):
+def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_loglik=False, alpha_normalized=False):
     """Generic dense HMM evaluation from materialised emissions E (k,B,T,q), A (k,q,q), pi (k,q).
     Returns dict with the requested tensors ('post','alpha','beta' each (k,B,T,q)) and 'loglik' (k,B)."""
     lib = _lib.load()
@@ -326,7 +326,8 @@ def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_l
         beta = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if need_b else None
         post = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if want_post else None
         ws = _workspace(lib.hmm_b200_dense_workspace_size(k, B, T, q), dev)
-        flags = (NO_LOGLIK if no_loglik else 0) | (0 if want_alpha else ALPHA_SCRATCH) | (0 if want_beta else BETA_SCRATCH)
+        flags = (NO_LOGLIK if no_loglik else 0) | (0 if want_alpha else ALPHA_SCRATCH) | (0 if want_beta else BETA_SCRATCH) \
+            | (ALPHA_NORMALIZED if alpha_normalized else 0)
         _lib.check(lib.hmm_b200_dense_run(_ptr(E), _ptr(A), _ptr(At), _ptr(pi), k, B, T, q, flags,
                                           _ptr(post), _ptr(alpha), _ptr(beta), _ptr(res["loglik"]), _ptr(ws), ws.numel(), _stream()))
     if want_post:
@@ -336,6 +337,43 @@ def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_l
     if want_beta:
         res["beta"] = beta
     return res
+
+
+class DenseLoglik(torch.autograd.Function):
+    """loglik (k,B) of the generic dense HMM, differentiable w.r.t. E (k,B,T,q), A (k,q,q) and pi (k,q) — training
+    profile-HMM models through MsaHmmLayer.forward (the reference differentiates its Python loop, MsaHmmCell.py:73-106).
+    Forward = one dense_run keeping log posterior and normalised forward vectors; backward = the expected-count closed
+    form: dE = gamma / E, dA = sum_t alpha-hat_{t-1}^T (gamma_t / (alpha-hat_{t-1} A)), dpi = gamma_0 / pi,
+    floored factors pass no gradient.  The two contractions over (batch x time) are plain library GEMMs (cuBLAS)."""
+    EPS = 1e-16
+
+    @staticmethod
+    def forward(ctx, E, A, pi):
+        r = dense_run(E, A, pi, want_post=True, want_alpha=True, alpha_normalized=True)
+        ctx.save_for_backward(E, A, pi, r["post"], r["alpha"])
+        return r["loglik"]
+
+    @staticmethod
+    def backward(ctx, g):
+        E, A, pi, post, ahat = ctx.saved_tensors
+        k, B, T, q = E.shape
+        eps = DenseLoglik.EPS
+        gam = torch.exp(post) * g.reshape(k, B, 1, 1).to(torch.float32)
+        gE = gA = gpi = None
+        if ctx.needs_input_grad[0]:
+            gE = torch.where(E > eps, gam / E.clamp_min(eps), torch.zeros_like(gam))
+        if ctx.needs_input_grad[2]:
+            p = pi.reshape(k, 1, q)
+            gpi = torch.where(p > eps, gam[:, :, 0] / p.clamp_min(eps), torch.zeros_like(gam[:, :, 0])).sum(1).reshape(pi.shape)
+        if ctx.needs_input_grad[1]:
+            if T > 1:
+                ah = torch.exp(ahat[:, :, :-1]).reshape(k, B * (T - 1), q)
+                R = torch.bmm(ah, A)
+                gd = torch.where(R > eps, gam[:, :, 1:].reshape(k, B * (T - 1), q) / R.clamp_min(eps), torch.zeros_like(R))
+                gA = torch.bmm(ah.transpose(1, 2), gd)
+            else:
+                gA = torch.zeros_like(A)
+        return gE, gA, gpi
 
 
 def cell_step(emission_probs, scaled, loglik, A, num_models, reverse=False, init=False):
