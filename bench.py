@@ -473,7 +473,7 @@ def main():
     # batch and overlaps H2D, kernels and D2H; every step moves its own inputs up and its own posterior down)
     # (30 untimed calls first.  The same call is bimodal on the test boxes: 0.81 ms or 1.07 ms per call for a whole loop,
     # clocks at maximum in both, raw C call 0.77-0.80 ms in both — tools/e2e_bench_probe.py; this leg reports what it sees)
-    n_e2e_warm = 0 if args.no_e2e else max(30, args.warmup)
+    n_e2e_warm = 0 if args.no_e2e else max(int(os.environ.get("HMM_BENCH_E2E_WARM", "30")), args.warmup)
     for _ in range(n_e2e_warm):
         layer.state_posterior_log_probs(host_in)
     n_e2e = 0 if args.no_e2e else max(3, min(args.steps, 50))

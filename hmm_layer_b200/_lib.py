@@ -12,6 +12,7 @@ EXPORTS = [
     "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read", "hmm_b200_debug_phases",
     "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_prepare_codon", "hmm_b200_genepred_run",
     "hmm_b200_genepred_host_scratch_size", "hmm_b200_genepred_run_host",
+    "hmm_b200_genepred_run_compact", "hmm_b200_genepred_run_host_compact",
     "hmm_b200_genepred_grad_workspace_size", "hmm_b200_genepred_grad",
     "hmm_b200_genepred_viterbi_workspace_size", "hmm_b200_genepred_viterbi",
     "hmm_b200_genepred_emission", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
@@ -49,6 +50,8 @@ def load():
     lib.hmm_b200_genepred_host_scratch_size.restype = ctypes.c_size_t
     lib.hmm_b200_genepred_host_scratch_size.argtypes = [ctypes.c_int] * 3
     lib.hmm_b200_genepred_run_host.argtypes = lib.hmm_b200_genepred_run.argtypes
+    lib.hmm_b200_genepred_run_compact.argtypes = [c_fp] + lib.hmm_b200_genepred_run.argtypes
+    lib.hmm_b200_genepred_run_host_compact.argtypes = [c_fp] + lib.hmm_b200_genepred_run.argtypes
     lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,
                                                ctypes.c_uint, c_fp, c_fp]
     ci = ctypes.c_int

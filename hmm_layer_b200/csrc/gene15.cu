@@ -86,6 +86,9 @@ struct Args {
   // seq_total; halo nucleotides and boundary vectors come from the neighbours.
   int seq_off, seq_total;
   const float* halo;   // [NB][4][5] nucleotide flags of positions -2,-1 (left) and T,T+1 (right) or NULL
+  // compact wire format: when cls16 is set, `inputs` is NULL and K1 unpacks its tile itself
+  const unsigned short* cls16;   // [NB][T][15] class probabilities as bf16 bit patterns
+  const unsigned char* nuc8;     // [NB][T] nucleotide codes 0..3 = A,C,G,T, anything else = N
   float* Mh;   // [NB][P][HEAP][256] per tile: product tree in heap order (node k = node 2k . node 2k+1)
   float* Mt;   // [NB][P][256] tile matrices (= heap node 1), contiguous per sequence for the top-level scan
   float* bvf;  // [NB][P][16] forward boundary vector entering tile p, slot 15 = exponent (int bits)
@@ -750,9 +753,11 @@ __global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(con
     if (tid == 0) {
       mbar_init(&S.bar, 1);
       mbar_init_fence();
-      const unsigned bytes = (unsigned)n_in * SIN * sizeof(float);
-      mbar_expect_tx(&S.bar, bytes);
-      bulk_g2s(IN, a.inputs + ((size_t)n * T + t_in0) * SIN, bytes, &S.bar);
+      if (!a.cls16) {
+        const unsigned bytes = (unsigned)n_in * SIN * sizeof(float);
+        mbar_expect_tx(&S.bar, bytes);
+        bulk_g2s(IN, a.inputs + ((size_t)n * T + t_in0) * SIN, bytes, &S.bar);
+      }
     }
     HMM_MARK(cta, 9);
     if (tid < 23) S.Aw[tid] = aw;
@@ -766,9 +771,24 @@ __global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(con
   }
   __syncthreads();            // mbarrier initialised, parameters in place
   HMM_MARK(cta, 7);
-  mbar_wait(&S.bar, 0);
-  HMM_MARK(cta, 8);
-  codes_from_smem(a, codes, IN, n, t_lo, npos, t_in0, n_in);
+  if (a.cls16) {
+    // compact wire format: bf16 class probabilities -> the fp32 rows the emission reads, nucleotide codes as they are
+    const unsigned short* src = a.cls16 + ((size_t)n * T + t_in0) * Q;
+    for (int i = tid; i < n_in * Q; i += K1_THREADS) {
+      const int pos = i / Q, c = i - pos * Q;
+      IN[pos * SIN + c] = __uint_as_float((unsigned)__ldg(src + i) << 16);
+    }
+    for (int i = tid; i < n_in; i += K1_THREADS) IN[i * SIN + Q] = 0.f;   // slot 15 meets B[q][15] = 0: must not be NaN
+    const unsigned char* nc = a.nuc8 + (size_t)n * T;
+    for (int i = tid; i < npos + 4; i += K1_THREADS) {
+      const int t = t_lo - 2 + i;
+      codes[i] = (signed char)((t >= 0 && t < T) ? min((int)__ldg(nc + t), 4) : 4);   // outside the sequence: 1/4 each
+    }
+  } else {
+    mbar_wait(&S.bar, 0);
+    HMM_MARK(cta, 8);
+    codes_from_smem(a, codes, IN, n, t_lo, npos, t_in0, n_in);
+  }
   __syncthreads();
   HMM_MARK(cta, 1);
 
@@ -2061,7 +2081,7 @@ int set_tuning(int L, int k2_threads, int dense_path) {
 
 static int fill_args(Args& a, const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
                      const float* Bfull, const float* codon5, const float* hints, unsigned flags) {
-  HMM_REQUIRE(inputs && Bfull && codon5, "genepred: null input pointer");
+  HMM_REQUIRE(Bfull && codon5, "genepred: null input pointer");
   HMM_REQUIRE(num_models > 0 && batch > 0 && T > 0, "genepred: num_models, batch and T must be positive (got %d,%d,%d)",
               num_models, batch, T);
   HMM_REQUIRE((reinterpret_cast<uintptr_t>(inputs) & 15) == 0, "genepred: inputs must be 16-byte aligned");
@@ -2071,6 +2091,7 @@ static int fill_args(Args& a, const float* inputs, int num_models, int batch, in
   a.num_models = num_models; a.batch = batch; a.T = T; a.flags = flags;
   a.seq_off = 0; a.seq_total = T; a.halo = nullptr; a.dbg = g_dbg;
   a.in_f = nullptr; a.in_r = nullptr;
+  a.cls16 = nullptr; a.nuc8 = nullptr;
   return 0;
 }
 
@@ -2152,10 +2173,14 @@ static int launch_boundary(const Args& a, const Layout& l, int NB, int mode, flo
 
 int run(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
         const float* codon5, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
-        float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+        float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st, const unsigned short* cls16 = nullptr,
+        const unsigned char* nuc8 = nullptr) {
   Args a{};
   int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
   if (rc) return rc;
+  HMM_REQUIRE((inputs != nullptr) != (cls16 != nullptr), "genepred: give either fp32 inputs or the compact pair");
+  HMM_REQUIRE(!cls16 || nuc8, "genepred: compact inputs need the nucleotide codes");
+  a.cls16 = cls16; a.nuc8 = nuc8;
   HMM_REQUIRE(A && pi, "genepred: null A / pi");
   HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred: no output requested");
   const int NB = num_models * batch;
@@ -2261,8 +2286,10 @@ size_t host_scratch_size(int num_models, int batch, int T) {
 
 int run_host(const float* h_inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
              const float* codon5, const float* h_hints, unsigned flags, float* h_post, float* h_alpha, float* h_beta,
-             float* h_loglik, void* scratch, size_t scratch_bytes, cudaStream_t st) {
-  HMM_REQUIRE(h_inputs && A && pi && Bfull && codon5, "genepred run_host: null input pointer");
+             float* h_loglik, void* scratch, size_t scratch_bytes, cudaStream_t st, const unsigned short* h_cls16 = nullptr,
+             const unsigned char* h_nuc8 = nullptr) {
+  HMM_REQUIRE(((h_inputs != nullptr) != (h_cls16 != nullptr)) && (!h_cls16 || h_nuc8) && A && pi && Bfull && codon5,
+              "genepred run_host: null input pointer (fp32 inputs, or the compact pair)");
   HMM_REQUIRE(num_models > 0 && batch > 0 && T > 0, "genepred run_host: num_models, batch and T must be positive");
   HMM_REQUIRE(h_post || h_alpha || h_beta || h_loglik, "genepred run_host: no output requested");
   const HostLayout h = host_layout(num_models, batch, T);
@@ -2290,13 +2317,22 @@ int run_host(const float* h_inputs, int num_models, int batch, int T, const floa
       const int nb = batch - b0 < h.slice ? batch - b0 : h.slice, buf = it & 1;
       const size_t seq0 = (size_t)m * batch + b0, rows = (size_t)nb * T;
       if (it >= 2) HMM_CUDA_OK(cudaStreamWaitEvent(p.s_in, p.ev_k[buf], 0));      // the kernels of slice it-2 read this buffer
-      HMM_CUDA_OK(cudaMemcpyAsync(F(h.in[buf]), h_inputs + seq0 * T * SIN, rows * SIN * sizeof(float), cudaMemcpyHostToDevice, p.s_in));
+      // compact wire format: 30 + 1 B / position up instead of 80; both pieces land in the slice's input buffer
+      unsigned short* d_cls = reinterpret_cast<unsigned short*>(F(h.in[buf]));
+      unsigned char* d_nuc = reinterpret_cast<unsigned char*>(F(h.in[buf])) + align_up(rows * Q * sizeof(unsigned short), 256);
+      if (h_cls16) {
+        HMM_CUDA_OK(cudaMemcpyAsync(d_cls, h_cls16 + seq0 * T * Q, rows * Q * sizeof(unsigned short), cudaMemcpyHostToDevice, p.s_in));
+        HMM_CUDA_OK(cudaMemcpyAsync(d_nuc, h_nuc8 + seq0 * T, rows, cudaMemcpyHostToDevice, p.s_in));
+      } else {
+        HMM_CUDA_OK(cudaMemcpyAsync(F(h.in[buf]), h_inputs + seq0 * T * SIN, rows * SIN * sizeof(float), cudaMemcpyHostToDevice, p.s_in));
+      }
       HMM_CUDA_OK(cudaEventRecord(p.ev_in[buf], p.s_in));
       HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_in[buf], 0));
       if (it >= 2) HMM_CUDA_OK(cudaStreamWaitEvent(st, p.ev_out[buf], 0));        // slice it-2's outputs have left
-      rc = run(F(h.in[buf]), 1, nb, T, A + (size_t)m * Q * Q, pi + (size_t)m * Q, Bfull + (size_t)m * Q * Q, codon5,
+      rc = run(h_cls16 ? nullptr : F(h.in[buf]), 1, nb, T, A + (size_t)m * Q * Q, pi + (size_t)m * Q, Bfull + (size_t)m * Q * Q, codon5,
                d_hints ? d_hints + seq0 * 2 * Q : nullptr, flags, h_post ? F(h.post[buf]) : nullptr,
-               h_alpha ? F(h.alpha[buf]) : nullptr, h_beta ? F(h.beta[buf]) : nullptr, d_ll + seq0, ws + h.ws[buf], h.ws_bytes, st);
+               h_alpha ? F(h.alpha[buf]) : nullptr, h_beta ? F(h.beta[buf]) : nullptr, d_ll + seq0, ws + h.ws[buf], h.ws_bytes, st,
+               h_cls16 ? d_cls : nullptr, h_cls16 ? d_nuc : nullptr);
       if (rc) return rc;
       HMM_CUDA_OK(cudaEventRecord(p.ev_k[buf], st));
       HMM_CUDA_OK(cudaStreamWaitEvent(p.s_out, p.ev_k[buf], 0));
@@ -2323,7 +2359,7 @@ static int shard_args(Args& a, Layout& l, const float* inputs, int num_models, i
                       const float* hints, unsigned flags, void* workspace, size_t workspace_bytes) {
   int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
   if (rc) return rc;
-  HMM_REQUIRE(A && pi, "genepred shard: null A / pi");
+  HMM_REQUIRE(inputs && A && pi, "genepred shard: null inputs / A / pi");
   HMM_REQUIRE(seq_off >= 0 && seq_total >= seq_off + T, "genepred shard: positions [%d, %d) outside a sequence of length %d",
               seq_off, seq_off + T, seq_total);
   HMM_REQUIRE(halo || (seq_off == 0 && seq_total == T), "genepred shard: a proper shard needs the 2+2 halo nucleotides");
@@ -2390,7 +2426,7 @@ int emission(const float* inputs, int num_models, int batch, int T, const float*
   Args a{};
   int rc = fill_args(a, inputs, num_models, batch, T, nullptr, nullptr, Bfull, codon5, hints, flags);
   if (rc) return rc;
-  HMM_REQUIRE(out_E, "genepred_emission: null output");
+  HMM_REQUIRE(inputs && out_E, "genepred_emission: null inputs / output");
   set_L(a, 32);
   const size_t sm = ((sizeof(EmisSmem) + 15) / 16) * 16 + (size_t)G * (a.L * QP + 4) * sizeof(float) + (((size_t)G * a.L + 4 + 15) / 16) * 16;
   rc = set_smem(emission_kernel, SLOT_EM, sm); if (rc) return rc;
@@ -2411,7 +2447,7 @@ int grad(const float* inputs, int num_models, int batch, int T, const float* A, 
   Args a{};
   int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
   if (rc) return rc;
-  HMM_REQUIRE(A && pi, "genepred_grad: null A / pi");
+  HMM_REQUIRE(inputs && A && pi, "genepred_grad: null inputs / A / pi");
   HMM_REQUIRE(log_post && log_ahat && grad_loglik, "genepred_grad: null log_post / log_alpha_hat / grad_loglik");
   HMM_REQUIRE(grad_inputs || grad_A || grad_pi || grad_Bfull, "genepred_grad: no gradient requested");
   HMM_REQUIRE(!grad_inputs || (reinterpret_cast<uintptr_t>(grad_inputs) & 15) == 0, "genepred_grad: grad_inputs must be 16-byte aligned");
@@ -2469,6 +2505,24 @@ int viterbi(const float* inputs, int num_models, int batch, int T, const float* 
 }  // namespace hmm
 
 extern "C" {
+
+int hmm_b200_genepred_run_compact(const unsigned short* class_probs_bf16, const unsigned char* nuc_codes, int num_models, int batch,
+                                  int T, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                  const float* end_hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
+                                  float* loglik, void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::gene15::run(nullptr, num_models, batch, T, A, pi, Bfull, codon5, end_hints, flags, out_post, out_alpha, out_beta,
+                          loglik, workspace, workspace_bytes, static_cast<cudaStream_t>(stream), class_probs_bf16, nuc_codes);
+}
+
+int hmm_b200_genepred_run_host_compact(const unsigned short* host_class_probs_bf16, const unsigned char* host_nuc_codes,
+                                       int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
+                                       const float* codon5, const float* host_end_hints, unsigned flags, float* host_out_post,
+                                       float* host_out_alpha, float* host_out_beta, float* host_loglik, void* device_scratch,
+                                       size_t device_scratch_bytes, void* stream) {
+  return hmm::gene15::run_host(nullptr, num_models, batch, T, A, pi, Bfull, codon5, host_end_hints, flags, host_out_post,
+                               host_out_alpha, host_out_beta, host_loglik, device_scratch, device_scratch_bytes,
+                               static_cast<cudaStream_t>(stream), host_class_probs_bf16, host_nuc_codes);
+}
 
 size_t hmm_b200_genepred_viterbi_workspace_size(int num_models, int batch, int T) {
   return hmm::gene15::viterbi_workspace_size(num_models, batch, T);

@@ -111,6 +111,57 @@ def genepred_run(inputs, A, pi, Bfull, codon, end_hints=None, training=False, no
     return res
 
 
+def pack_compact(inputs):
+    """(k,B,T,20) fp32 reference layout -> (class probabilities (k,B,T,15) bf16, nucleotide codes (k,B,T) uint8:
+    0..3 = A,C,G,T, 4 = N) — the compact wire format of hmm_b200_genepred_run_compact.  Works on CPU or CUDA tensors;
+    rows that are neither one-hot nor N cannot be expressed and raise."""
+    if inputs.dim() != 4 or inputs.shape[-1] != 20:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, 20), got {tuple(inputs.shape)}")
+    nuc = inputs[..., 15:]
+    hard = ((nuc == 0) | (nuc == 1)).all(-1) & (nuc.sum(-1) == 1)
+    if not bool(hard.all()):
+        raise ValueError("the compact format needs one-hot (or N) nucleotide rows")
+    return inputs[..., :15].to(torch.bfloat16).contiguous(), nuc.argmax(-1).to(torch.uint8).contiguous()
+
+
+def genepred_run_compact(class_probs, nuc_codes, A, pi, Bfull, codon, end_hints=None, training=False, no_loglik=False,
+                         want_post=True, want_alpha=False, want_beta=False):
+    """The fused evaluation from the compact wire format (bf16 class probabilities (k,B,T,15) + uint8 nucleotide codes
+    (k,B,T)).  CUDA tensors: device path; CPU tensors (ideally pinned): pipelined host path, pinned CPU results."""
+    lib = _lib.load()
+    if class_probs.dim() != 4 or class_probs.shape[-1] != 15 or class_probs.dtype != torch.bfloat16:
+        raise ValueError("class_probs must be a bfloat16 tensor of shape (num_models, batch, T, 15)")
+    k, B, T, _ = class_probs.shape
+    if tuple(nuc_codes.shape) != (k, B, T) or nuc_codes.dtype != torch.uint8 or nuc_codes.device != class_probs.device:
+        raise ValueError("nuc_codes must be a uint8 tensor of shape (num_models, batch, T) on the same device")
+    class_probs, nuc_codes = class_probs.contiguous(), nuc_codes.contiguous()
+    A = _req(A, "A", (k, 15, 15)); pi = _req(pi.reshape(k, 15), "pi", (k, 15))
+    Bfull = _req(Bfull, "Bfull", (k, 15, 15)); codon = _codon5(codon)
+    dev, host = A.device, not class_probs.is_cuda
+    if end_hints is not None:
+        end_hints = end_hints.to(torch.float32).contiguous() if host else _req(end_hints, "end_hints", (k, B, 2, 15))
+    flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+    with torch.cuda.device(dev):
+        kw = dict(dtype=torch.float32, pin_memory=True) if host else dict(dtype=torch.float32, device=dev)
+        res = {}
+        for name, want in (("post", want_post), ("alpha", want_alpha), ("beta", want_beta)):
+            if want:
+                res[name] = torch.empty((k, B, T, 15), **kw)
+        res["loglik"] = torch.empty((k, B), **kw)
+        if host:
+            ws = _workspace(lib.hmm_b200_genepred_host_scratch_size(k, B, T), dev)
+            fn = lib.hmm_b200_genepred_run_host_compact
+        else:
+            ws = _workspace(lib.hmm_b200_genepred_workspace_size(k, B, T), dev)
+            fn = lib.hmm_b200_genepred_run_compact
+        _lib.check(fn(_ptr(class_probs), _ptr(nuc_codes), k, B, T, _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+                      flags, _ptr(res.get("post")), _ptr(res.get("alpha")), _ptr(res.get("beta")), _ptr(res["loglik"]),
+                      _ptr(ws), ws.numel(), _stream()))
+        if host:
+            torch.cuda.current_stream(dev).synchronize()
+    return res
+
+
 def genepred_viterbi(inputs, A, pi, Bfull, codon, end_hints=None, training=False):
     """Most probable state path of the 15-state gene HMM (hmm_b200_genepred_viterbi).  inputs (k,B,T,20) CUDA.
     Returns (path (k,B,T) uint8, score (k,B) float32 = log joint probability of the path)."""

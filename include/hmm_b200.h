@@ -102,6 +102,30 @@ int hmm_b200_genepred_run_host(const float* host_inputs, int num_models, int bat
                                float* host_out_post, float* host_out_alpha, float* host_out_beta, float* host_loglik,
                                void* device_scratch, size_t device_scratch_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Compact wire format of the same evaluation.  The reference's layout — 15 fp32 class probabilities
+ * followed by a 5-wide fp32 one-hot of the nucleotide (gene_pred_hmm_emitter.py:239-240, 80 B / position) — is dictated
+ * by its emitter's slicing; callers that produce the class probabilities in bf16 (the upstream network's dtype) and
+ * hold the sequence as bytes hand over 31 B / position instead:
+ *   class_probs_bf16 (num_models, batch, T, 15)  bf16 bit patterns
+ *   nuc_codes        (num_models, batch, T)      0..3 = A,C,G,T, anything else = N (1/4 on each base, kmer.py:21-25)
+ * Results are those of hmm_b200_genepred_run on the fp32 expansion of exactly these values.  Workspace / scratch sizes
+ * are the ones of the fp32 entry points.  Sequence sharding is not offered in this format.
+ * --------------------------------------------------------------------------------------------------------- */
+int hmm_b200_genepred_run_compact(const unsigned short* class_probs_bf16, const unsigned char* nuc_codes,
+                                  int num_models, int batch, int T,
+                                  const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                  const float* end_hints, unsigned flags,
+                                  float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                                  void* workspace, size_t workspace_bytes, void* stream);
+
+int hmm_b200_genepred_run_host_compact(const unsigned short* host_class_probs_bf16, const unsigned char* host_nuc_codes,
+                                       int num_models, int batch, int T,
+                                       const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                       const float* host_end_hints, unsigned flags,
+                                       float* host_out_post, float* host_out_alpha, float* host_out_beta, float* host_loglik,
+                                       void* device_scratch, size_t device_scratch_bytes, void* stream);
+
 /* Stand-alone emission (cell.emission_probs API parity): out_E (num_models, batch, T, 15). */
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
                                const float* Bfull, const float* codon5, const float* end_hints,
