@@ -471,11 +471,14 @@ def main():
     # ---- end-to-end through the public layer API with host buffers ----
     # (CPU tensor in -> CPU tensor out: the layer hands host buffers to hmm_b200_genepred_run_host, which slices the
     # batch and overlaps H2D, kernels and D2H; every step moves its own inputs up and its own posterior down)
-    # (30 untimed calls first.  The same call is bimodal on the test boxes: 0.81 ms or 1.07 ms per call for a whole loop,
-    # clocks at maximum in both, raw C call 0.77-0.80 ms in both — tools/e2e_bench_probe.py; this leg reports what it sees)
-    n_e2e_warm = 0 if args.no_e2e else max(int(os.environ.get("HMM_BENCH_E2E_WARM", "30")), args.warmup)
+    # The warm-up calls hold on to their result exactly like the timed loop does, so that the two pinned output buffers the
+    # loop alternates between exist before the clock starts: torch's caching host allocator otherwise takes its second
+    # 32 MB block with a ~15 ms cudaHostAlloc INSIDE the timed region (+0.3 ms per call over 50 calls — this was the
+    # "1.08 ms" of earlier rounds; tools/e2e_bench_probe.py, tools/e2e_bisect.py)
+    n_e2e_warm = 0 if args.no_e2e else max(10, args.warmup)
+    host_post = None
     for _ in range(n_e2e_warm):
-        layer.state_posterior_log_probs(host_in)
+        host_post = layer.state_posterior_log_probs(host_in)
     n_e2e = 0 if args.no_e2e else max(3, min(args.steps, 50))
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
