@@ -51,8 +51,18 @@ def _gene_loglik_diff(inputs, cell, training):
     trace its Python loop, MsaHmmCell.py:73-106).  A, pi and B stay attached to the parameters' graph; the kernels'
     closed-form gradient (ops.GenePredLoglik) supplies d loglik / d (inputs, A, pi, Bfull)."""
     em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
-    pi = cell.init_dist.reshape(cell.num_models, -1)
-    return ops.GenePredLoglik.apply(inputs, tr.A, pi, em.make_B_full(), em.codon5(inputs.device), None, training)
+    if _fused_params_ok(cell, em, tr):   # A, pi, B and their backward in one launch each instead of ~40 small ones
+        A, pi, Bfull = ops.GeneParams.apply(tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)
+    else:
+        A, pi, Bfull = tr.A, cell.init_dist.reshape(cell.num_models, -1), em.make_B_full()
+    return ops.GenePredLoglik.apply(inputs, A, pi, Bfull, em.codon5(inputs.device), None, training)
+
+
+def _fused_params_ok(cell, em, tr):
+    return (type(em) is GenePredHMMEmitter and em.share_intron_parameters and em.emission_kernel is not None
+            and tuple(em.emission_kernel.shape) == (cell.num_models, 13, 15) and em.emission_kernel.is_cuda
+            and tr.transition_kernel.numel() == 23 and tr.num_models == cell.num_models
+            and tr.starting_distribution_kernel.numel() == 15)
 
 
 def _priors(cell, result, return_prior):
@@ -193,9 +203,11 @@ class MsaHmmLayer(nn.Module):
         cell = self.cell
         diff = torch.is_grad_enabled() and inputs.is_cuda and (
             inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
-        cell.recurrent_init(fresh=diff)
+        fused_gene = _is_fused_gene_cell(cell)
+        cell.recurrent_init(fresh=diff and not (fused_gene and _fused_params_ok(
+            cell, cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner))))
         _check_inputs(inputs, cell, self.parallel_factor)
-        if diff and _is_fused_gene_cell(cell):
+        if diff and fused_gene:
             loglik = _gene_loglik_diff(inputs, cell, training)
         elif diff:   # any other cell: emissions, A and pi stay attached to the parameters' graph
             E = cell.emission_probs(inputs, training=training)

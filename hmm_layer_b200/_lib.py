@@ -15,6 +15,7 @@ EXPORTS = [
     "hmm_b200_genepred_run_compact", "hmm_b200_genepred_run_host_compact",
     "hmm_b200_genepred_grad_workspace_size", "hmm_b200_genepred_grad",
     "hmm_b200_genepred_viterbi_workspace_size", "hmm_b200_genepred_viterbi",
+    "hmm_b200_genepred_params", "hmm_b200_genepred_params_grad",
     "hmm_b200_genepred_emission", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
     "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_cell_step",
 ]
@@ -55,6 +56,8 @@ def load():
     lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,
                                                ctypes.c_uint, c_fp, c_fp]
     ci = ctypes.c_int
+    lib.hmm_b200_genepred_params.argtypes = [c_fp, c_fp, c_fp, ci, c_fp, c_fp, c_fp, c_fp]
+    lib.hmm_b200_genepred_params_grad.argtypes = [c_fp, c_fp, c_fp, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_viterbi_workspace_size.restype = ctypes.c_size_t
     lib.hmm_b200_genepred_viterbi_workspace_size.argtypes = [ctypes.c_int] * 3
     lib.hmm_b200_genepred_viterbi.argtypes = [c_fp, ci, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_uint, c_fp, c_fp,

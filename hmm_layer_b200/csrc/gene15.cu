@@ -1959,6 +1959,106 @@ __global__ void __launch_bounds__(32) viterbi_kernel(const float* __restrict__ E
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Parameter construction of the gene model in one launch (training steps rebuild A, pi, B from the kernels every call,
+// gene_pred_hmm_transitioner.py:66-112 via Transitioner.py:337-380, gene_pred_hmm_emitter.py:65,87-91,115-116; as ~20 small
+// PyTorch ops plus their autograd that is the bulk of a training step's host time):
+//   A[i][j]   = (s + 1e-16) / (sum over i's out-edges of (s + 1e-16) + 1e-16),  s = softmax over the 15 dense entries of
+//               row i, absent entries at -1000, kernel values clamped at -999 (the reference's guards)
+//   pi        = softmax(starting distribution kernel);   Bfull = softmax rows of the emission kernel, intron row x 3
+// and its backward.  One CTA; thread = one output row.  The same kernels serve every model (A, pi) / one per model (B).
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) params_kernel(const float* __restrict__ tk, const float* __restrict__ sk,
+                                                    const float* __restrict__ ek, int num_models, float* __restrict__ A,
+                                                    float* __restrict__ pi, float* __restrict__ Bfull) {
+  const int tid = threadIdx.x;
+  if (tid < Q) {   // row tid of A
+    float kv[3]; int dst[3]; int deg = 0;
+    for (int e = 0; e < NEDGE; ++e)
+      if (ESRC[e] == tid && deg < 3) { kv[deg] = fmaxf(__ldg(tk + e), -999.f); dst[deg] = EDST[e]; ++deg; }
+    float mx = -1000.f;
+    for (int d = 0; d < deg; ++d) mx = fmaxf(mx, kv[d]);
+    float den = (float)(Q - deg) * expf(-1000.f - mx), p[3], z = 1e-16f;
+    for (int d = 0; d < deg; ++d) { p[d] = expf(kv[d] - mx); den += p[d]; }
+    for (int d = 0; d < deg; ++d) { p[d] = p[d] / den + 1e-16f; z += p[d]; }
+    for (int m = 0; m < num_models; ++m) {
+      float* row = A + ((size_t)m * Q + tid) * Q;
+      for (int j = 0; j < Q; ++j) row[j] = 0.f;
+      for (int d = 0; d < deg; ++d) row[dst[d]] = p[d] / z;
+    }
+  } else if (tid == 32) {
+    float mx = -INFINITY, den = 0.f, v[Q];
+    for (int j = 0; j < Q; ++j) mx = fmaxf(mx, __ldg(sk + j));
+    for (int j = 0; j < Q; ++j) { v[j] = expf(__ldg(sk + j) - mx); den += v[j]; }
+    for (int m = 0; m < num_models; ++m)
+      for (int j = 0; j < Q; ++j) pi[m * Q + j] = v[j] / den;
+  }
+  // emission rows: 13 kernel rows per model -> 15 state rows (rows 1,2,3 = kernel row 1)
+  for (int r = tid; r < num_models * Q; r += blockDim.x) {
+    const int m = r / Q, st = r - m * Q, kr = st == 0 ? 0 : (st <= 3 ? 1 : st - 2);
+    const float* src = ek + ((size_t)m * 13 + kr) * Q;
+    float mx = -INFINITY, den = 0.f, v[Q];
+    for (int j = 0; j < Q; ++j) mx = fmaxf(mx, __ldg(src + j));
+    for (int j = 0; j < Q; ++j) { v[j] = expf(__ldg(src + j) - mx); den += v[j]; }
+    for (int j = 0; j < Q; ++j) Bfull[(size_t)r * Q + j] = v[j] / den;
+  }
+}
+
+__global__ void __launch_bounds__(64) params_grad_kernel(const float* __restrict__ tk, const float* __restrict__ sk,
+                                                         const float* __restrict__ ek, int num_models,
+                                                         const float* __restrict__ gA, const float* __restrict__ gpi,
+                                                         const float* __restrict__ gB, float* __restrict__ gtk,
+                                                         float* __restrict__ gsk, float* __restrict__ gek) {
+  const int tid = threadIdx.x;
+  if (tid < Q && gtk) {
+    float kv[3], raw[3], g[3]; int eid[3]; int deg = 0;
+    for (int e = 0; e < NEDGE; ++e)
+      if (ESRC[e] == tid && deg < 3) {
+        raw[deg] = __ldg(tk + e); kv[deg] = fmaxf(raw[deg], -999.f); eid[deg] = e;
+        float acc = 0.f;
+        if (gA) for (int m = 0; m < num_models; ++m) acc += __ldg(gA + ((size_t)m * Q + tid) * Q + EDST[e]);
+        g[deg] = acc; ++deg;
+      }
+    float mx = -1000.f;
+    for (int d = 0; d < deg; ++d) mx = fmaxf(mx, kv[d]);
+    float den = (float)(Q - deg) * expf(-1000.f - mx), sft[3], p[3], z = 1e-16f;
+    for (int d = 0; d < deg; ++d) { sft[d] = expf(kv[d] - mx); den += sft[d]; }
+    for (int d = 0; d < deg; ++d) { sft[d] /= den; p[d] = sft[d] + 1e-16f; z += p[d]; }
+    // A_e = p_e / z:  dL/dp_e = (g_e - sum_e' g_e' A_e') / z;  p = s + const;  s = softmax (absent entries carry no gradient)
+    float dot = 0.f;
+    for (int d = 0; d < deg; ++d) dot += g[d] * (p[d] / z);
+    float ds[3], sdot = 0.f;
+    for (int d = 0; d < deg; ++d) { ds[d] = (g[d] - dot) / z; sdot += sft[d] * ds[d]; }
+    for (int d = 0; d < deg; ++d) gtk[eid[d]] = (raw[d] >= -999.f) ? sft[d] * (ds[d] - sdot) : 0.f;
+  } else if (tid == 32 && gsk) {
+    float mx = -INFINITY, den = 0.f, v[Q], g[Q], dot = 0.f;
+    for (int j = 0; j < Q; ++j) mx = fmaxf(mx, __ldg(sk + j));
+    for (int j = 0; j < Q; ++j) { v[j] = expf(__ldg(sk + j) - mx); den += v[j]; }
+    for (int j = 0; j < Q; ++j) {
+      float acc = 0.f;
+      if (gpi) for (int m = 0; m < num_models; ++m) acc += __ldg(gpi + m * Q + j);
+      g[j] = acc; v[j] /= den; dot += v[j] * acc;
+    }
+    for (int j = 0; j < Q; ++j) gsk[j] = v[j] * (g[j] - dot);
+  }
+  if (gek) {
+    for (int r = tid; r < num_models * 13; r += blockDim.x) {
+      const int m = r / 13, kr = r - m * 13;
+      const float* src = ek + (size_t)r * Q;
+      float mx = -INFINITY, den = 0.f, v[Q], g[Q], dot = 0.f;
+      for (int j = 0; j < Q; ++j) mx = fmaxf(mx, __ldg(src + j));
+      for (int j = 0; j < Q; ++j) { v[j] = expf(__ldg(src + j) - mx); den += v[j]; }
+      const int s0 = kr == 0 ? 0 : (kr == 1 ? 1 : kr + 2), ns = kr == 1 ? 3 : 1;
+      for (int j = 0; j < Q; ++j) {
+        float acc = 0.f;
+        if (gB) for (int u = 0; u < ns; ++u) acc += __ldg(gB + ((size_t)m * Q + s0 + u) * Q + j);
+        g[j] = acc; v[j] /= den; dot += v[j] * acc;
+      }
+      for (int j = 0; j < Q; ++j) gek[(size_t)r * Q + j] = v[j] * (g[j] - dot);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
 static int g_L = 0;          // 0: choose per call
@@ -2501,10 +2601,40 @@ int viterbi(const float* inputs, int num_models, int batch, int T, const float* 
   return 0;
 }
 
+int params(const float* tk, const float* sk, const float* ek, int num_models, float* A, float* pi, float* Bfull, cudaStream_t st) {
+  HMM_REQUIRE(tk && sk && ek && A && pi && Bfull && num_models > 0, "genepred_params: null pointer");
+  params_kernel<<<1, 64, 0, st>>>(tk, sk, ek, num_models, A, pi, Bfull);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int params_grad(const float* tk, const float* sk, const float* ek, int num_models, const float* gA, const float* gpi,
+                const float* gB, float* gtk, float* gsk, float* gek, cudaStream_t st) {
+  HMM_REQUIRE(tk && sk && ek && num_models > 0, "genepred_params_grad: null pointer");
+  params_grad_kernel<<<1, 64, 0, st>>>(tk, sk, ek, num_models, gA, gpi, gB, gtk, gsk, gek);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace gene15
 }  // namespace hmm
 
 extern "C" {
+
+int hmm_b200_genepred_params(const float* transition_kernel, const float* start_kernel, const float* emission_kernel,
+                             int num_models, float* A, float* pi, float* Bfull, void* stream) {
+  return hmm::gene15::params(transition_kernel, start_kernel, emission_kernel, num_models, A, pi, Bfull,
+                             static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_params_grad(const float* transition_kernel, const float* start_kernel, const float* emission_kernel,
+                                  int num_models, const float* grad_A, const float* grad_pi, const float* grad_Bfull,
+                                  float* grad_transition_kernel, float* grad_start_kernel, float* grad_emission_kernel,
+                                  void* stream) {
+  return hmm::gene15::params_grad(transition_kernel, start_kernel, emission_kernel, num_models, grad_A, grad_pi, grad_Bfull,
+                                  grad_transition_kernel, grad_start_kernel, grad_emission_kernel,
+                                  static_cast<cudaStream_t>(stream));
+}
 
 int hmm_b200_genepred_run_compact(const unsigned short* class_probs_bf16, const unsigned char* nuc_codes, int num_models, int batch,
                                   int T, const float* A, const float* pi, const float* Bfull, const float* codon5,

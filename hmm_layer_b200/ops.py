@@ -222,6 +222,47 @@ def genepred_grad(inputs, A, pi, Bfull, codon, log_post, log_alpha_hat, grad_log
     return res
 
 
+class GeneParams(torch.autograd.Function):
+    """(transition kernel (1,23), starting distribution kernel (1,1,15), emission kernel (k,13,15)) -> A (k,15,15),
+    pi (k,15), Bfull (k,15,15) of the 15-state gene model in one launch, with its backward in one launch
+    (hmm_b200_genepred_params / _params_grad).  Same arithmetic as GenePredHMMTransitioner.make_A /
+    make_initial_distribution and SimpleGenePredHMMEmitter.make_B_full, which stay the reference-shaped API."""
+
+    @staticmethod
+    def forward(ctx, tk, sk, ek):
+        lib = _lib.load()
+        tk, sk, ek = _req(tk, "transition_kernel"), _req(sk, "start_kernel"), _req(ek, "emission_kernel")
+        k = ek.shape[0]
+        if tk.numel() != 23 or sk.numel() != 15 or tuple(ek.shape) != (k, 13, 15):
+            raise ValueError("GeneParams: kernels of the single-copy 15-state gene model expected (23 / 15 / (k,13,15))")
+        dev = ek.device
+        with torch.cuda.device(dev):
+            A = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+            pi = torch.empty((k, 15), dtype=torch.float32, device=dev)
+            Bfull = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+            _lib.check(lib.hmm_b200_genepred_params(_ptr(tk), _ptr(sk), _ptr(ek), k, _ptr(A), _ptr(pi), _ptr(Bfull), _stream()))
+        ctx.save_for_backward(tk, sk, ek)
+        ctx.shapes = (tk.shape, sk.shape)
+        return A, pi, Bfull
+
+    @staticmethod
+    def backward(ctx, gA, gpi, gB):
+        lib = _lib.load()
+        tk, sk, ek = ctx.saved_tensors
+        k, dev = ek.shape[0], ek.device
+        need = ctx.needs_input_grad
+        c = lambda g: None if g is None else g.contiguous().to(torch.float32)
+        gA, gpi, gB = c(gA), c(gpi), c(gB)
+        with torch.cuda.device(dev):
+            gtk = torch.empty(23, dtype=torch.float32, device=dev) if need[0] else None
+            gsk = torch.empty(15, dtype=torch.float32, device=dev) if need[1] else None
+            gek = torch.empty((k, 13, 15), dtype=torch.float32, device=dev) if need[2] else None
+            if need[0] or need[1] or need[2]:
+                _lib.check(lib.hmm_b200_genepred_params_grad(_ptr(tk), _ptr(sk), _ptr(ek), k, _ptr(gA), _ptr(gpi), _ptr(gB),
+                                                             _ptr(gtk), _ptr(gsk), _ptr(gek), _stream()))
+        return (None if gtk is None else gtk.reshape(ctx.shapes[0]), None if gsk is None else gsk.reshape(ctx.shapes[1]), gek)
+
+
 class GenePredLoglik(torch.autograd.Function):
     """loglik (k,B) of the fused gene HMM, differentiable w.r.t. inputs (class probabilities), A, pi and Bfull.
     Forward = one fused evaluation that also keeps log posterior and normalised forward vectors; backward = the

@@ -154,6 +154,20 @@ int hmm_b200_genepred_grad(const float* inputs, int num_models, int batch, int T
                            float* grad_inputs, float* grad_A, float* grad_pi, float* grad_Bfull,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* Parameter construction of the 15-state gene model in one launch, and its backward (a training step rebuilds A, pi, B
+ * from the kernels on every call: GenePredHMMTransitioner.make_A / make_initial_distribution
+ * gene_pred_hmm_transitioner.py:66-112 through make_transition_matrix_from_indices Transitioner.py:337-380, and
+ * SimpleGenePredHMMEmitter.make_B gene_pred_hmm_emitter.py:87-91 with the intron row repeated :115-116).
+ *   transition_kernel (23)  in the edge order of GenePredHMMTransitioner.make_transition_indices (k = 1)
+ *   start_kernel (15)       emission_kernel (num_models, 13, 15)
+ *   -> A (num_models,15,15), pi (num_models,15), Bfull (num_models,15,15).  grad_* inputs of the backward may be NULL. */
+int hmm_b200_genepred_params(const float* transition_kernel, const float* start_kernel, const float* emission_kernel,
+                             int num_models, float* A, float* pi, float* Bfull, void* stream);
+int hmm_b200_genepred_params_grad(const float* transition_kernel, const float* start_kernel, const float* emission_kernel,
+                                  int num_models, const float* grad_A, const float* grad_pi, const float* grad_Bfull,
+                                  float* grad_transition_kernel, float* grad_start_kernel, float* grad_emission_kernel,
+                                  void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------
  * Viterbi decoding of the gene HMM: most probable state path.  The reference names Viterbi (MsaHmmCell.py:13) and
  * prepares log_A_dense for it (:46-47) but ships no implementation; this is the max-product form of the recursion

@@ -169,3 +169,27 @@ def test_grad_identities_config2_size():
     (ll * dev(w)).sum().backward()
     for a, b in zip(g1, (xg, Ag, pig, Bg)):
         assert torch.equal(a, b.grad)
+
+
+def test_fused_parameter_construction_matches_torch_construction():
+    """ops.GeneParams (one launch forward, one backward) against the PyTorch construction the classes expose
+    (make_A / make_initial_distribution / make_B_full): values and gradients."""
+    layer, em, tr = make_layer()
+    g = torch.Generator().manual_seed(11)
+    with torch.no_grad():
+        tr.transition_kernel.add_(0.3 * torch.randn(tr.transition_kernel.shape, generator=g).cuda())
+    wA, wpi, wB = [torch.randn(s, generator=g).cuda() for s in ((1, 15, 15), (1, 15), (1, 15, 15))]
+    A, pi, Bf = ops.GeneParams.apply(tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)
+    ((A * wA).sum() + (pi * wpi).sum() + (Bf * wB).sum()).backward()
+    got = [p.grad.clone() for p in (tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)]
+    for p in (tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel):
+        p.grad = None
+    em.recurrent_init()
+    A2, pi2, B2 = tr.make_A(), tr.make_initial_distribution().reshape(1, 15), em.make_B_full()
+    ((A2 * wA).sum() + (pi2 * wpi).sum() + (B2 * wB).sum()).backward()
+    ref = [p.grad for p in (tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)]
+    assert torch.allclose(A, A2, rtol=1e-6, atol=1e-9) and torch.allclose(pi, pi2, rtol=1e-6) and torch.allclose(Bf, B2, rtol=1e-6)
+    assert ((A == 0) == (A2 == 0)).all()
+    for a, b in zip(got, ref):
+        assert tuple(a.shape) == tuple(b.shape)
+        assert (a - b).abs().max() <= 1e-5 * b.abs().max() + 1e-9
