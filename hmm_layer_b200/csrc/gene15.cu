@@ -2125,7 +2125,11 @@ static int choose_L(int NB, int T, bool full) {
     const int c1 = ctas_per_sm(k1_smem_bytes(L, P), HMM_K1_BLOCKS), c2 = ctas_per_sm(k2_smem_bytes(L, full), 4);
     const long long r1 = (tiles + (long long)sms * c1 - 1) / ((long long)sms * c1);
     const long long r2 = (tiles + (long long)sms * c2 - 1) / ((long long)sms * c2);
-    const double t1 = 7000.0 + 330.0 * L * c1, t2 = 4500.0 + 200.0 * L + 60.0 * L * (c2 - 1);
+    // CTAs that actually share an SM: fewer tiles than SMs run alone whatever the occupancy limit says.  Co-resident
+    // CTAs serialise their per-position work and overlap about half of their fixed part (r1i sweeps: B = 8 / 32 / 64)
+    const long long per_sm = (tiles + sms - 1) / sms;
+    const int e1 = (int)(per_sm < c1 ? per_sm : c1), e2 = (int)(per_sm < c2 ? per_sm : c2);
+    const double t1 = 7000.0 * (1.0 + 0.5 * (e1 - 1)) + 330.0 * L * e1, t2 = 4500.0 + 200.0 * L + 60.0 * L * (e2 - 1);
     const double cost = (double)r1 * t1 + (double)r2 * t2;
     if (cost < best) { best = cost; bestL = L; }
   }
