@@ -53,7 +53,9 @@ constexpr int MAX_SCAN_TILES = 60;    // K1's last CTA of a sequence scans up to
 constexpr int K1_THREADS = G * 16;
 constexpr unsigned EMIT_LOG_FLOORED = 0x40000000u;   // internal flag of emission_kernel (not part of the C ABI)
 #ifndef HMM_K1_BLOCKS
+#ifndef HMM_K1_BLOCKS
 #define HMM_K1_BLOCKS 2               // CTAs of K1 per SM the register budget is sized for (1: 128 regs, 2: 64 regs)
+#endif
 #endif
 constexpr int MAX_L = 40;             // longest chunk (shared memory bound)
 constexpr int DIV_SHIFT = 21;         // i / L == (i * mL) >> 21 for i < 4096, L <= 48
@@ -718,7 +720,10 @@ __host__ __device__ inline size_t k1_smem_bytes(int L, int P) {
   return ((sizeof(K1Smem) + 15) / 16) * 16 + k1_union_bytes(L, P) + (((size_t)G * L + 4 + 15) / 16) * 16;
 }
 
-__global__ void __launch_bounds__(K1_THREADS, HMM_K1_BLOCKS) products_kernel(const Args a) {
+// BLOCKS = CTAs per SM the register budget is sized for: 2 (64 registers) when two tiles fit an SM's shared memory, 1 (128
+// registers, no spills) for the long chunks that leave room for one
+template <int BLOCKS>
+__global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem[];
   K1Smem& S = *reinterpret_cast<K1Smem*>(smem);
   float* U = reinterpret_cast<float*>(smem + ((sizeof(K1Smem) + 15) / 16) * 16);
@@ -2207,7 +2212,7 @@ static void set_L(Args& a, int L) {
 }
 
 // raises a kernel's dynamic shared memory limit when this call needs more than any earlier one (slot = kernel id)
-static size_t g_smem_set[7] = {0, 0, 0, 0, 0, 0, 0};
+static size_t g_smem_set[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 template <typename K>
 static int set_smem(K kernel, int slot, size_t bytes) {
   if (bytes <= g_smem_set[slot]) return 0;
@@ -2245,6 +2250,19 @@ int prepare_codon(const float* codon64, float* codon5, cudaStream_t st) {
   HMM_REQUIRE(codon64 && codon5, "prepare_codon: null pointer");
   prepare_codon_kernel<<<1, 256, 0, st>>>(codon64, codon5);
   HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+enum { SLOT_K1B = 7 };
+static int launch_products(const Args& a, int NB, cudaStream_t st) {
+  const size_t sm1 = k1_smem_bytes(a.L, a.P);
+  if (ctas_per_sm(sm1, HMM_K1_BLOCKS) >= 2) {
+    int rc = set_smem(products_kernel<2>, SLOT_K1, sm1); if (rc) return rc;
+    products_kernel<2><<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
+  } else {
+    int rc = set_smem(products_kernel<1>, SLOT_K1B, sm1); if (rc) return rc;
+    products_kernel<1><<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
+  }
   return 0;
 }
 
@@ -2300,13 +2318,12 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = loglik;
 
   const size_t sm1 = k1_smem_bytes(a.L, a.P), sm2 = k2_smem_bytes(a.L, full);
-  rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
   if (need_k2 && !full) { rc = set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc; }
   if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
   if (a.top_scan) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
 
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
-  products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
+  rc = launch_products(a, NB, st); if (rc) return rc;
   if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   if (!a.top_scan) {
     rc = launch_boundary(a, l, NB, 0, nullptr, false, workspace, st); if (rc) return rc;
@@ -2487,8 +2504,7 @@ int shard_reduce(const float* inputs, int num_models, int batch, int T, int seq_
   HMM_REQUIRE(block_out, "genepred shard_reduce: null output");
   const int NB = num_models * batch;
   const size_t sm1 = k1_smem_bytes(a.L, a.P);
-  rc = set_smem(products_kernel, SLOT_K1, sm1); if (rc) return rc;
-  products_kernel<<<dim3(a.P, NB), K1_THREADS, sm1, st>>>(a);
+  rc = launch_products(a, NB, st); if (rc) return rc;
   rc = launch_boundary(a, l, NB, 1, block_out, false, workspace, st); if (rc) return rc;
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
