@@ -26,7 +26,7 @@ NBUF = 8                              # rotating input/output sets: 8 x 44.8 MB 
 # (profiles/r1c_ncu_summary.txt: products 25.71 + 7.03 MB, finalize 58.79 + 1.68 MB).  ncu flushes the caches before
 # every kernel, so the L2-resident workspace K1 hands to K2 (emission rows 20.5 MB + product trees 37 MB) shows up as
 # DRAM traffic there; in the back-to-back bench those reads are L2 hits.
-NCU_TRAFFIC_BYTES = 93.22e6
+NCU_TRAFFIC_BYTES = 65.42e6
 
 
 def peaks():
@@ -526,7 +526,7 @@ def main():
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": NCU_TRAFFIC_BYTES,
-                         "traffic_note": "ncu cold-cache capture r1c: includes 57 MB of K1->K2 workspace that is L2-resident outside the profiler",
+                         "traffic_note": "ncu cold-cache capture r1j (profiles/r1j_ncu_summary.txt): K1 reads 25.7 MB of inputs, K2 reads 39.4 MB (emission rows + product trees written by K1; L2-resident outside the profiler); the 19.2 MB of log posterior are still in L2 when the capture ends (0.3 MB of DRAM writes)",
                          "peak_source": peak_src,
                          "scope": "the fused pass = 2 launches (products_kernel, finalize_kernel); algorithmic bytes = 140 B/position x 319968 positions = 44.8 MB per pass; duration = sum of the two kernels' CUDA-event times",
                          "kernel_ms": {"products_kernel": ker[0], "finalize_kernel": ker[1]}},
