@@ -23,9 +23,9 @@ WORKLOAD = dict(num_models=1, batch=32, T=9999, q=15)
 BYTES_PER_POSITION = 140.0            # 80 B inputs read once + 60 B log-posterior written once
 NBUF = 8                              # rotating input/output sets: 8 x 44.8 MB = 358 MB > 126 MB L2
 # dram__bytes_read.sum + dram__bytes_write.sum of the two kernels of one pass, from the committed ncu --set full capture
-# (profiles/r1c_ncu_summary.txt: products 25.71 + 7.03 MB, finalize 58.79 + 1.68 MB).  ncu flushes the caches before
-# every kernel, so the L2-resident workspace K1 hands to K2 (emission rows 20.5 MB + product trees 37 MB) shows up as
-# DRAM traffic there; in the back-to-back bench those reads are L2 hits.
+# (profiles/r1j_ncu_summary.txt, chunk length 35: products 25.68 + 0.22 MB, finalize 39.44 + 0.08 MB).  ncu flushes the
+# caches before every kernel, so the L2-resident workspace K1 hands to K2 (emission rows + product trees) shows up as
+# DRAM reads there; in the back-to-back bench those reads are L2 hits.
 NCU_TRAFFIC_BYTES = 65.42e6
 
 
