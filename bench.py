@@ -29,6 +29,28 @@ NBUF = 8                              # rotating input/output sets: 8 x 44.8 MB 
 NCU_TRAFFIC_BYTES = 65.42e6
 
 
+_STDOUT_FD = None
+
+
+def quiet_stdout():
+    """Everything written to fd 1 before the result (NCCL prints its version banner there) goes to stderr instead:
+    stdout carries exactly one JSON line."""
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_json(obj):
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.dup2(_STDOUT_FD, 1)
+    print(json.dumps(obj), flush=True)
+    if _STDOUT_FD is not None:
+        os.dup2(2, 1)
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -123,7 +145,7 @@ def run_reference(args, rank):
     dt = (time.perf_counter() - t0) / args.steps
     cells = syn.cells(k, B, T, q)
     v = cells / dt
-    print(json.dumps({
+    emit_json(({
         "impl": "reference", "metric": "hmm_cells_per_s", "value": v, "unit": "cells/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -213,7 +235,7 @@ def run_config4(args, rank, world, local):
     if rank == 0:
         peak, src = tensor_peak()
         alg_tflops = 2.0 * cells / (ms_step * 1e-3) / 1e12          # 2 FLOP per cell per direction
-        print(json.dumps({
+        emit_json(({
             "metric": "hmm_cells_per_s", "value": world * cells / (ms_step * 1e-3), "unit": "cells/s", "n_gpus": world,
             "steps": steps, "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 (bf16-pair tensor-core products, fp32 accumulation)", "data": "synthetic",
@@ -300,7 +322,7 @@ def run_config5(args, rank, world, local):
     if rank == 0:
         peak, src = peaks()
         achieved = BYTES_PER_POSITION * T / (ms_step * 1e-3) / 1e9
-        print(json.dumps({
+        emit_json(({
             "metric": "hmm_cells_per_s", "value": cells / (ms_step * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": steps,
             "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
@@ -370,7 +392,7 @@ def run_train(args, rank, world, local):
         peak, src = peaks()
         alg = 140.0 * k * B * T     # 80 B inputs read + 60 B class-probability gradient written per position
         achieved = world * alg / (ms_step * 1e-3) / 1e9
-        print(json.dumps({
+        emit_json(({
             "metric": "hmm_cells_per_s", "value": world * syn.cells(k, B, T, q) / (ms_step * 1e-3), "unit": "cells/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 10), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -390,6 +412,7 @@ def run_train(args, rank, world, local):
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", type=int, default=2, choices=[2, 4, 5],
                     help="BASELINE config (2 = headline; 4 = learnMSA sizes; 5 = one 1 Mbp sequence sharded over the GPUs)")
@@ -544,7 +567,7 @@ def main():
             dt = time.perf_counter() - t0
             line["cpu_baseline"] = {"value": syn.cells(k, 8, T, q) / dt, "unit": "cells/s", "cores": torch.get_num_threads(),
                                     "kind": "port", "sample": f"8 of the 32 sequences x 9999 bp, one pass ({dt:.1f} s); torch CPU port of the reference path (oracle/ref_port.py)"}
-        print(json.dumps(line))
+        emit_json((line))
     if world > 1:
         dist.destroy_process_group()
 
