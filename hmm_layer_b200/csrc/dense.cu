@@ -149,6 +149,77 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs a) {
   }
 }
 
+// Persistent recurrence for small state counts (q < 192: config 1's q = 67, multi-copy gene models): ONE launch runs all T
+// steps of one sequence and direction per CTA — the transition matrix stays resident in shared memory, the state vector
+// never leaves the SM, the next step's emission row is loaded while the current step computes, the row sum is a warp-shuffle
+// reduction.  Same arithmetic and the same stored quantities as step_kernel (un-normalised a_t / R_t, scale history, final
+// partial sums), so cum_kernel / finish_kernel are shared.  thread = state.
+struct SeqArgs {
+  const float* E; const float* A; const float* At; const float* pi;
+  float* store[2];   // forward: a_t, backward: R_t  (k, B, T, q) or NULL when the direction is not wanted
+  float* hist[2];    // (k, B, T)
+  float* part_f;     // (k, B, ntile): partial sums of the last forward state (slot 0 gets the sum, the rest zeros)
+  int k, B, T, q, ntile, dir0;   // dir0: direction of blockIdx.y == 0
+};
+
+__global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
+  extern __shared__ float sm[];
+  const int q = a.q, T = a.T, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+  float* As = sm;                 // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
+  float* xs = sm + (size_t)q * q; // current un-normalised state
+  float* red = xs + q;            // per-warp partial sums
+  const int seq = blockIdx.x, m = seq / a.B, d = a.dir0 + blockIdx.y;
+  const float* Am = (d == 0 ? a.A : a.At) + (size_t)m * q * q;
+  for (int i = tid; i < q * q; i += nt) As[i] = __ldg(Am + i);
+  const bool live = tid < q;
+  const float* Eseq = a.E + (size_t)seq * T * q + tid;
+  float* store = a.store[d] ? a.store[d] + (size_t)seq * T * q + tid : nullptr;
+  float* hist = a.hist[d] + (size_t)seq * T;
+  float S_in = 1.f;
+  float x = 0.f;
+  int t = d == 0 ? 0 : T - 1;
+  const int dt = d == 0 ? 1 : -1;
+  float e_next = live ? __ldg(Eseq + (size_t)t * q) : 0.f;
+  __syncthreads();
+  for (int s = 0; s < T; ++s, t += dt) {
+    const float e = e_next;
+    if (s + 1 < T && live) e_next = __ldg(Eseq + (size_t)(t + dt) * q);
+    float U;
+    if (s == 0) {
+      U = live ? (d == 0 ? __ldg(a.pi + (size_t)m * q + tid) : 1.f) : 0.f;
+    } else {
+      float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
+      if (live) {
+        const float* col = As + tid;
+        int i = 0;
+        for (; i + 3 < q; i += 4) {
+          u0 = fmaf(xs[i], col[(size_t)i * q], u0);
+          u1 = fmaf(xs[i + 1], col[(size_t)(i + 1) * q], u1);
+          u2 = fmaf(xs[i + 2], col[(size_t)(i + 2) * q], u2);
+          u3 = fmaf(xs[i + 3], col[(size_t)(i + 3) * q], u3);
+        }
+        for (; i < q; ++i) u0 = fmaf(xs[i], col[(size_t)i * q], u0);
+      }
+      U = ((u0 + u1) + (u2 + u3)) * (1.0f / S_in);
+    }
+    const float R = fmaxf(U, kEps);
+    x = live ? fmaxf(e, kEps) * R : 0.f;
+    if (store && live) store[(size_t)t * q] = d ? R : x;
+    if (tid == 0) hist[t] = S_in;
+    float v = x;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();                 // everyone has read xs of the previous step
+    if (live) xs[tid] = x;
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float tot = 0.f;
+    for (int w = 0; w < nw; ++w) tot += red[w];
+    S_in = tot;
+  }
+  if (d == 0 && tid < a.ntile) a.part_f[(size_t)seq * a.ntile + tid] = tid == 0 ? S_in : 0.f;
+}
+
 // per sequence: cumulative log scales (double) and the log-likelihood.
 //   forward:  hist[t] = S_{t-1} (1 at t = 0), final = partial sums of the last state  ->  cum_f[t] = sum_{tau<=t} log S_tau
 //   backward: hist[t] = S_{t+1} (1 at t = T-1)                                        ->  cum_b[t] = sum_{tau>t} log S_tau
@@ -326,7 +397,26 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     const int rc = dense_tc::run_steps(E, A, pi, k, B, T, q, need_f, need_b, out_alpha, out_beta, part, hist, ws + l.extra, st);
     if (rc) return rc;
   }
-  for (int d = 0; d < 2 && !tc; ++d) {
+  // small q: one persistent launch for all steps of both directions (seq_kernel); g_path == 1 keeps the per-step engine
+  const size_t seq_smem = ((size_t)q * q + q + 8) * sizeof(float);
+  const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024 && N <= 2147483647ull;
+  if (seq) {
+    static size_t smem_set = 0;
+    if (seq_smem > smem_set) {
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      smem_set = seq_smem;
+    }
+    SeqArgs a;
+    a.E = E; a.A = A; a.At = At; a.pi = pi;
+    a.store[0] = need_f ? out_alpha : nullptr; a.store[1] = need_b ? out_beta : nullptr;
+    a.hist[0] = F(l.hist[0]); a.hist[1] = F(l.hist[1]);
+    a.part_f = F(l.part[0][T & 1]);
+    a.k = k; a.B = B; a.T = T; a.q = q; a.ntile = ntile;
+    a.dir0 = need_f ? 0 : 1;
+    const int nthreads = ((q + 31) / 32) * 32;
+    seq_kernel<<<dim3((unsigned)N, (need_f && need_b) ? 2 : 1), nthreads, seq_smem, st>>>(a);
+  }
+  for (int d = 0; d < 2 && !tc && !seq; ++d) {
     if ((d == 0 && !need_f) || (d == 1 && !need_b)) continue;
     init_state_kernel<<<ig, ib, 0, st>>>(F(l.st[d][0]), d == 0 ? pi : nullptr, k, B, q);
     for (int s = 0; s < T; ++s) {
