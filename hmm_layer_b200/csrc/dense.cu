@@ -162,12 +162,15 @@ struct SeqArgs {
   int k, B, T, q, ntile, dir0;   // dir0: direction of blockIdx.y == 0
 };
 
+// QR > 0: the thread keeps its column of A in QR registers (q <= QR) and reads the state vector as float4 broadcasts;
+// QR == 0: the column is walked in shared memory (any q < 192)
+template <int QR>
 __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   extern __shared__ float sm[];
   const int q = a.q, T = a.T, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
-  float* As = sm;                 // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
-  float* xs = sm + (size_t)q * q; // current un-normalised state
-  float* red = xs + q;            // per-warp partial sums
+  float* xs = sm;                 // current un-normalised state, padded to 192 floats (16-byte aligned float4 reads)
+  float* red = sm + 192;          // per-warp partial sums
+  float* As = sm + 200;           // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
   const int seq = blockIdx.x, m = seq / a.B, d = a.dir0 + blockIdx.y;
   const float* Am = (d == 0 ? a.A : a.At) + (size_t)m * q * q;
   for (int i = tid; i < q * q; i += nt) As[i] = __ldg(Am + i);
@@ -179,17 +182,28 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   float x = 0.f;
   int t = d == 0 ? 0 : T - 1;
   const int dt = d == 0 ? 1 : -1;
-  float e_next = live ? __ldg(Eseq + (size_t)t * q) : 0.f;
   __syncthreads();
-  for (int s = 0; s < T; ++s, t += dt) {
-    const float e = e_next;
-    if (s + 1 < T && live) e_next = __ldg(Eseq + (size_t)(t + dt) * q);
+  float acol[QR > 0 ? QR : 1];
+  if (QR > 0) {
+#pragma unroll
+    for (int i = 0; i < QR; ++i) acol[i] = (live && i < q) ? As[(size_t)i * q + tid] : 0.f;
+    for (int i = q + tid; i < QR; i += nt) xs[i] = 0.f;   // the float4 reads run up to QR
+  }
+  auto step = [&](float e, int s) {
     float U;
     if (s == 0) {
       U = live ? (d == 0 ? __ldg(a.pi + (size_t)m * q + tid) : 1.f) : 0.f;
     } else {
       float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
-      if (live) {
+      if (QR > 0) {
+        const float4* x4 = reinterpret_cast<const float4*>(xs);
+#pragma unroll
+        for (int i = 0; i < QR / 4; ++i) {
+          const float4 v = x4[i];
+          u0 = fmaf(v.x, acol[4 * i], u0); u1 = fmaf(v.y, acol[4 * i + 1], u1);
+          u2 = fmaf(v.z, acol[4 * i + 2], u2); u3 = fmaf(v.w, acol[4 * i + 3], u3);
+        }
+      } else if (live) {
         const float* col = As + tid;
         int i = 0;
         for (; i + 3 < q; i += 4) {
@@ -216,6 +230,28 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
     float tot = 0.f;
     for (int w = 0; w < nw; ++w) tot += red[w];
     S_in = tot;
+    t += dt;
+  };
+  // emission rows are loaded a block of SEQ_PF steps ahead into alternating register sets (a step is shorter than a
+  // DRAM round trip)
+  constexpr int SEQ_PF = 8;
+  float ea[SEQ_PF], eb[SEQ_PF];
+  const int t_first = t;
+  auto load_block = [&](float (&dst)[SEQ_PF], int s0) {
+#pragma unroll
+    for (int u = 0; u < SEQ_PF; ++u)
+      dst[u] = (live && s0 + u < T) ? __ldg(Eseq + (size_t)(t_first + (s0 + u) * dt) * q) : 0.f;
+  };
+  auto run_block = [&](const float (&use)[SEQ_PF], float (&fill)[SEQ_PF], int s0) {
+    load_block(fill, s0 + SEQ_PF);
+#pragma unroll
+    for (int u = 0; u < SEQ_PF; ++u)
+      if (s0 + u < T) step(use[u], s0 + u);
+  };
+  load_block(ea, 0);
+  for (int s0 = 0; s0 < T; s0 += 2 * SEQ_PF) {
+    run_block(ea, eb, s0);
+    if (s0 + SEQ_PF < T) run_block(eb, ea, s0 + SEQ_PF);
   }
   if (d == 0 && tid < a.ntile) a.part_f[(size_t)seq * a.ntile + tid] = tid == 0 ? S_in : 0.f;
 }
@@ -223,29 +259,49 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
 // per sequence: cumulative log scales (double) and the log-likelihood.
 //   forward:  hist[t] = S_{t-1} (1 at t = 0), final = partial sums of the last state  ->  cum_f[t] = sum_{tau<=t} log S_tau
 //   backward: hist[t] = S_{t+1} (1 at t = T-1)                                        ->  cum_b[t] = sum_{tau>t} log S_tau
-__global__ void cum_kernel(const float* __restrict__ hist_f, const float* __restrict__ part_f, const float* __restrict__ hist_b,
-                           float* __restrict__ cum_f, float* __restrict__ cum_b, float* __restrict__ loglik, int N, int T, int ntile) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(32) cum_kernel(const float* __restrict__ hist_f, const float* __restrict__ part_f,
+                                                 const float* __restrict__ hist_b, float* __restrict__ cum_f,
+                                                 float* __restrict__ cum_b, float* __restrict__ loglik, int N, int T, int ntile) {
+  // one warp per sequence: lane l owns the contiguous steps [l * seg, (l + 1) * seg); segment sums in double, a warp
+  // prefix / suffix scan over the 32 sums, then the running sums inside each segment (same order of additions for every
+  // launch: deterministic)
+  const int n = blockIdx.x, lane = threadIdx.x;
   if (n >= N) return;
+  const int seg = (T + 31) / 32, lo = min(T, lane * seg), hi = min(T, lo + seg);
   if (hist_f) {
     const float* h = hist_f + (size_t)n * T;
-    double c = 0.0;
-    for (int t = 0; t < T; ++t) {
-      float s;
-      if (t + 1 < T) s = h[t + 1];
-      else { s = 0.f; for (int i = 0; i < ntile; ++i) s += part_f[(size_t)n * ntile + i]; }
-      c += log((double)s);
-      if (cum_f) cum_f[(size_t)n * T + t] = (float)c;
+    float last = 0.f;
+    if (hi == T && lo < T)
+      for (int i = 0; i < ntile; ++i) last += part_f[(size_t)n * ntile + i];
+    auto term = [&](int t) { return log((double)(t + 1 < T ? h[t + 1] : last)); };
+    double mine = 0.0;
+    for (int t = lo; t < hi; ++t) mine += term(t);
+    double pre = mine;   // inclusive prefix over lanes
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double v = __shfl_up_sync(0xffffffffu, pre, o);
+      if (lane >= o) pre += v;
     }
-    if (loglik) loglik[n] = (float)c;
+    const double total = __shfl_sync(0xffffffffu, pre, 31);
+    if (cum_f) {
+      double c = pre - mine;
+      for (int t = lo; t < hi; ++t) { c += term(t); cum_f[(size_t)n * T + t] = (float)c; }
+    }
+    if (loglik && lane == 0) loglik[n] = (float)total;
   }
   if (hist_b && cum_b) {
     const float* h = hist_b + (size_t)n * T;
-    double c = 0.0;
-    for (int t = T - 1; t >= 0; --t) {
-      if (t + 1 < T) c += log((double)h[t]);   // h[t] = S of b_{t+1}
-      cum_b[(size_t)n * T + t] = (float)c;
+    auto term = [&](int t) { return t + 1 < T ? log((double)h[t]) : 0.0; };   // h[t] = S of b_{t+1}
+    double mine = 0.0;
+    for (int t = lo; t < hi; ++t) mine += term(t);
+    double suf = mine;   // inclusive suffix over lanes
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const double v = __shfl_down_sync(0xffffffffu, suf, o);
+      if (lane + o < 32) suf += v;
     }
+    double c = suf - mine;
+    for (int t = hi - 1; t >= lo; --t) { c += term(t); cum_b[(size_t)n * T + t] = (float)c; }
   }
 }
 
@@ -398,12 +454,18 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     if (rc) return rc;
   }
   // small q: one persistent launch for all steps of both directions (seq_kernel); g_path == 1 keeps the per-step engine
-  const size_t seq_smem = ((size_t)q * q + q + 8) * sizeof(float);
+  const size_t seq_smem = ((size_t)q * q + 200) * sizeof(float);
   const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024 && N <= 2147483647ull;
   if (seq) {
     static size_t smem_set = 0;
     if (seq_smem > smem_set) {
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
+      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
       smem_set = seq_smem;
     }
     SeqArgs a;
@@ -414,7 +476,13 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     a.k = k; a.B = B; a.T = T; a.q = q; a.ntile = ntile;
     a.dir0 = need_f ? 0 : 1;
     const int nthreads = ((q + 31) / 32) * 32;
-    seq_kernel<<<dim3((unsigned)N, (need_f && need_b) ? 2 : 1), nthreads, seq_smem, st>>>(a);
+    const dim3 sgrid((unsigned)N, (need_f && need_b) ? 2 : 1);
+    if (q <= 32) seq_kernel<32><<<sgrid, nthreads, seq_smem, st>>>(a);
+    else if (q <= 64) seq_kernel<64><<<sgrid, nthreads, seq_smem, st>>>(a);
+    else if (q <= 96) seq_kernel<96><<<sgrid, nthreads, seq_smem, st>>>(a);
+    else if (q <= 128) seq_kernel<128><<<sgrid, nthreads, seq_smem, st>>>(a);
+    else if (q <= 160) seq_kernel<160><<<sgrid, nthreads, seq_smem, st>>>(a);
+    else seq_kernel<192><<<sgrid, nthreads, seq_smem, st>>>(a);
   }
   for (int d = 0; d < 2 && !tc && !seq; ++d) {
     if ((d == 0 && !need_f) || (d == 1 && !need_b)) continue;
@@ -433,7 +501,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   }
   HMM_CUDA_OK(cudaGetLastError());
   const float* part_f = F(l.part[0][tc ? ((T - 1) & 1) : (T & 1)]);   // slot written by the last forward step
-  cum_kernel<<<cdiv((int)N, 128), 128, 0, st>>>(need_f ? F(l.hist[0]) : nullptr, part_f, need_b ? F(l.hist[1]) : nullptr,
+  cum_kernel<<<(unsigned)N, 32, 0, st>>>(need_f ? F(l.hist[0]) : nullptr, part_f, need_b ? F(l.hist[1]) : nullptr,
                                                  (out_alpha || out_post) ? F(l.cum[0]) : nullptr,
                                                  need_b ? F(l.cum[1]) : nullptr, need_f ? llbuf : nullptr, (int)N, T, ntile);
   if (out_post || out_alpha || out_beta) {

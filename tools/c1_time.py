@@ -13,7 +13,7 @@ def timeit(fn, n=50):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 
-for (k, B, T, q) in [(1, 16, 100, 67), (1, 512, 100, 67), (4, 64, 600, 131), (1, 32, 9999, 29)]:
+for (k, B, T, q) in [(1, 16, 100, 67), (1, 512, 100, 67), (4, 64, 600, 131), (2, 64, 300, 183), (1, 32, 9999, 29)]:
     g = torch.Generator().manual_seed(1)
     E = (torch.rand((k, B, T, q), generator=g) + 0.01).cuda()
     A = torch.rand((k, q, q), generator=g); A = (A / A.sum(-1, keepdim=True)).cuda()
