@@ -167,6 +167,90 @@ def tensor_peak():
     return 2250.0, "fallback (nominal dense bf16)"
 
 
+def run_config1(args, rank, world, local):
+    """Secondary line (--config 1): BASELINE config 1, the reference's own CPU-scale case — MsaHmmLayer forward
+    log-likelihood, 1 head, model length 32 (q = 67), amino-acid alphabet (24 symbols), batch 16 x len 100 — through
+    MsaHmmCell's default profile-HMM plugins.  Latency-bound on any GPU (1600 positions); single rank."""
+    if rank != 0:
+        return
+    import hmm_layer_b200 as H
+    from hmm_layer_b200 import synthetic as syn
+    from oracle import ref_port as P
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    k, B, T, L = 1, 16, 100, 32
+    q = 2 * L + 3
+    torch.manual_seed(2000)
+    cell = H.MsaHmmCell(L)
+    with torch.no_grad():
+        cell.emitter[0].emission_kernel[0].normal_(0, 1)
+    # CPU arm on the same parameters: the reference's generic HmmCell loop (port), all host threads
+    with torch.no_grad():
+        cell.recurrent_init()
+        A_c, pi_c, B_c = cell.transitioner.A.clone(), cell.init_dist.reshape(k, q).clone(), cell.emitter[0].B.clone()
+    host_in = syn.profile_inputs(k, B, T, seed=2100).pin_memory()
+
+    def cpu_step():
+        with torch.no_grad():
+            E = torch.einsum("kbts,kqs->kbtq", host_in, B_c)
+            _, ll = P.scan(E.reshape(k * B, T, q), pi_c.reshape(k, 1, q).expand(k, B, q).reshape(-1, q), A_c, k, q, False)
+        return ll
+    cpu_step()
+    t0 = time.perf_counter()
+    n_cpu = 5
+    for _ in range(n_cpu):
+        ll_cpu = cpu_step()
+    cpu_ms = (time.perf_counter() - t0) / n_cpu * 1e3
+    cell = cell.to(dev)
+    layer = H.MsaHmmLayer(cell, use_prior=False)
+    x = host_in.to(dev)
+    cells = syn.cells(k, B, T, q)
+    sampler = ClockSampler(local)
+    sampler.start()
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 10)):
+            layer(x)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(args.steps):
+            loglik, _ = layer(x)
+        e1.record(); torch.cuda.synchronize()
+        ms_step = e0.elapsed_time(e1) / args.steps
+        host_ll = torch.empty((k, B), dtype=torch.float32).pin_memory()
+        for _ in range(10):
+            host_ll.copy_(layer(host_in.to(dev, non_blocking=True))[0], non_blocking=True)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); f0.record()
+        n_e2e = max(3, min(args.steps, 50))
+        for _ in range(n_e2e):
+            host_ll.copy_(layer(host_in.to(dev, non_blocking=True))[0], non_blocking=True)
+        f1.record(); torch.cuda.synchronize()
+        ms_e2e = f0.elapsed_time(f1) / n_e2e
+    clocks = sampler.stop()
+    rel = float(((loglik.cpu() - ll_cpu.reshape(k, B)).abs() / ll_cpu.reshape(k, B).abs()).max())
+    peak, src = peaks()
+    alg = 4.0 * k * B * T * (24 + q)       # one-hot inputs read + the emission tensor the dense path consumes
+    achieved = alg / (ms_step * 1e-3) / 1e9
+    emit_json(({
+        "metric": "hmm_cells_per_s", "value": cells / (ms_step * 1e-3), "unit": "cells/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 10), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "config1: MsaHmmLayer forward log-likelihood, 1 head, model length 32 (q = 67), 24 symbols, batch 16 x 100",
+                   "num_models": k, "batch": B, "T": T, "q": q, "plugins": "ProfileHMMEmitter / ProfileHMMTransitioner defaults",
+                   "note": "latency-bound: 1600 positions, 16 chains of 100 dependent steps"},
+        "e2e": {"value": cells / (ms_e2e * 1e-3), "unit": "cells/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": int(host_in.numel() * 4), "d2h_bytes_per_step": int(host_ll.numel() * 4),
+                "api": "MsaHmmLayer.forward(pinned one-hot inputs -> device) -> loglik -> pinned host"},
+        "gpu_launches": 4 * args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": src, "scope": "whole step (emission GEMM, seq_kernel, cum_kernel); latency-bound, not a bandwidth claim"},
+        "cpu_baseline": {"value": cells / (cpu_ms * 1e-3), "unit": "cells/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": "the full config (16 x 100), reference HmmCell loop port (oracle/ref_port.py scan) on the same parameters",
+                         "ms_per_step": cpu_ms},
+        "loglik_rel_err_vs_cpu_port": rel, "clocks": clocks,
+    }))
+
+
 def run_config4(args, rank, world, local):
     """Secondary line (--config 4): BASELINE config 4, learnMSA multi-head MsaHmmLayer forward log-likelihood,
     8 heads x model length 500 (q = 1003), batch 512 x len 600 per GPU, one-hot inputs over 24 symbols.
@@ -414,8 +498,8 @@ def run_train(args, rank, world, local):
 def main():
     quiet_stdout()
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, default=2, choices=[2, 4, 5],
-                    help="BASELINE config (2 = headline; 4 = learnMSA sizes; 5 = one 1 Mbp sequence sharded over the GPUs)")
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 4, 5],
+                    help="BASELINE config (2 = headline; 1 = the reference's CPU-scale case; 4 = learnMSA sizes; 5 = one 1 Mbp sequence sharded over the GPUs)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
@@ -437,6 +521,8 @@ def main():
 
     if args.train:
         return run_train(args, rank, world, local)
+    if args.config == 1:
+        return run_config1(args, rank, world, local)
     if args.config == 4:
         return run_config4(args, rank, world, local)
     if args.config == 5:
