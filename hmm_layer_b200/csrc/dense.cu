@@ -164,96 +164,114 @@ struct SeqArgs {
 
 // QR > 0: the thread keeps its column of A in QR registers (q <= QR) and reads the state vector as float4 broadcasts;
 // QR == 0: the column is walked in shared memory (any q < 192)
+constexpr int SEQ_PF = 8;          // emission rows per prefetch block
+constexpr int SEQ_XS = 200;        // floats per state buffer: 192 state slots + 8 per-warp partial sums
+constexpr int SEQ_HDR = 2 * SEQ_XS + 2 * SEQ_PF * 192;   // two state buffers + the two-block emission ring
 template <int QR>
 __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   extern __shared__ float sm[];
-  const int q = a.q, T = a.T, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
-  float* xs = sm;                 // current un-normalised state, padded to 192 floats (16-byte aligned float4 reads)
-  float* red = sm + 192;          // per-warp partial sums
-  float* As = sm + 200;           // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
+  const int q = a.q, T = a.T, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  // sm[0..400): two state buffers (state of step s is written to buffer (s+1)&1 — one barrier per step); each holds the
+  // un-normalised state padded to 192 floats (16-byte aligned float4 reads) and the per-warp partial sums at +192
+  float* ring = sm + 2 * SEQ_XS;  // [2][SEQ_PF][192] emission ring, a thread touches only its own column
+  float* As = sm + SEQ_HDR;       // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
   const int seq = blockIdx.x, m = seq / a.B, d = a.dir0 + blockIdx.y;
   const float* Am = (d == 0 ? a.A : a.At) + (size_t)m * q * q;
   for (int i = tid; i < q * q; i += nt) As[i] = __ldg(Am + i);
+  for (int i = tid; i < 2 * SEQ_XS; i += nt) sm[i] = 0.f;
   const bool live = tid < q;
-  const float* Eseq = a.E + (size_t)seq * T * q + tid;
-  float* store = a.store[d] ? a.store[d] + (size_t)seq * T * q + tid : nullptr;
-  float* hist = a.hist[d] + (size_t)seq * T;
-  float S_in = 1.f;
-  float x = 0.f;
-  int t = d == 0 ? 0 : T - 1;
   const int dt = d == 0 ? 1 : -1;
+  const int t_first = d == 0 ? 0 : T - 1;
+  const ptrdiff_t dq = (ptrdiff_t)dt * q;
+  const float* Eseq = a.E + (size_t)seq * T * q + (size_t)t_first * q + tid;
+  float* store = (a.store[d] && live) ? a.store[d] + (size_t)seq * T * q + (size_t)t_first * q + tid : nullptr;
+  float* hist = a.hist[d] + (size_t)seq * T + t_first;
+  // emission rows arrive SEQ_PF steps ahead through cp.async into the ring (a step is shorter than a DRAM round trip);
+  // the step loop itself stays rolled so that its body is fetched from the instruction cache
+  // (running pointers made opaque to the compiler, which otherwise rebuilds them from the kernel parameters at every use)
+  unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring + tid);
+  long long dqb = (long long)dq * 4;
+  const char* esrc = reinterpret_cast<const char*>(Eseq);
+  asm volatile("" : "+r"(ring_s), "+l"(dqb), "+l"(esrc), "+l"(store), "+l"(hist));
+  int e_left = live ? T : 0;
+  auto issue = [&](int blk) {
+    const unsigned dst = ring_s + (unsigned)((blk & 1) * SEQ_PF * 192 * 4);
+#pragma unroll
+    for (int u = 0; u < SEQ_PF; ++u) {
+      if (u < e_left) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + u * 192 * 4), "l"(esrc) : "memory");
+      esrc += dqb;
+    }
+    e_left -= SEQ_PF;
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  issue(0);
   __syncthreads();
   float acol[QR > 0 ? QR : 1];
   if (QR > 0) {
 #pragma unroll
     for (int i = 0; i < QR; ++i) acol[i] = (live && i < q) ? As[(size_t)i * q + tid] : 0.f;
-    for (int i = q + tid; i < QR; i += nt) xs[i] = 0.f;   // the float4 reads run up to QR
   }
-  auto step = [&](float e, int s) {
-    float U;
-    if (s == 0) {
-      U = live ? (d == 0 ? __ldg(a.pi + (size_t)m * q + tid) : 1.f) : 0.f;
-    } else {
-      float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
-      if (QR > 0) {
-        const float4* x4 = reinterpret_cast<const float4*>(xs);
+  float S_in = 1.f;
+  const int nblk = (T + SEQ_PF - 1) / SEQ_PF;
+#pragma unroll 1
+  for (int blk = 0; blk < nblk; ++blk) {
+    issue(blk + 1);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    const float* eb = ring + (blk & 1) * SEQ_PF * 192 + tid;
+    const int s_end = min(SEQ_PF, T - blk * SEQ_PF);
+#pragma unroll 1
+    for (int u = 0; u < s_end; ++u) {
+      const int s = blk * SEQ_PF + u;
+      const float e = live ? eb[u * 192] : 0.f;
+      const float* xr = sm + (s & 1) * SEQ_XS;          // state of step s-1
+      float* xw = sm + ((s & 1) ^ 1) * SEQ_XS;
+      float U;
+      if (s == 0) {
+        U = live ? (d == 0 ? __ldg(a.pi + (size_t)m * q + tid) : 1.f) : 0.f;
+      } else {
+        float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
+        if (QR > 0) {
+          const float4* x4 = reinterpret_cast<const float4*>(xr);
 #pragma unroll
-        for (int i = 0; i < QR / 4; ++i) {
-          const float4 v = x4[i];
-          u0 = fmaf(v.x, acol[4 * i], u0); u1 = fmaf(v.y, acol[4 * i + 1], u1);
-          u2 = fmaf(v.z, acol[4 * i + 2], u2); u3 = fmaf(v.w, acol[4 * i + 3], u3);
+          for (int i = 0; i < QR / 4; ++i) {
+            const float4 v = x4[i];
+            u0 = fmaf(v.x, acol[4 * i], u0); u1 = fmaf(v.y, acol[4 * i + 1], u1);
+            u2 = fmaf(v.z, acol[4 * i + 2], u2); u3 = fmaf(v.w, acol[4 * i + 3], u3);
+          }
+        } else if (live) {
+          const float* col = As + tid;
+          int i = 0;
+          for (; i + 3 < q; i += 4) {
+            u0 = fmaf(xr[i], col[(size_t)i * q], u0);
+            u1 = fmaf(xr[i + 1], col[(size_t)(i + 1) * q], u1);
+            u2 = fmaf(xr[i + 2], col[(size_t)(i + 2) * q], u2);
+            u3 = fmaf(xr[i + 3], col[(size_t)(i + 3) * q], u3);
+          }
+          for (; i < q; ++i) u0 = fmaf(xr[i], col[(size_t)i * q], u0);
         }
-      } else if (live) {
-        const float* col = As + tid;
-        int i = 0;
-        for (; i + 3 < q; i += 4) {
-          u0 = fmaf(xs[i], col[(size_t)i * q], u0);
-          u1 = fmaf(xs[i + 1], col[(size_t)(i + 1) * q], u1);
-          u2 = fmaf(xs[i + 2], col[(size_t)(i + 2) * q], u2);
-          u3 = fmaf(xs[i + 3], col[(size_t)(i + 3) * q], u3);
-        }
-        for (; i < q; ++i) u0 = fmaf(xs[i], col[(size_t)i * q], u0);
+        // S_in: sum of the previous state over the (at most six) warps; unused slots hold zeros
+        const float4 r4 = *reinterpret_cast<const float4*>(xr + 192);
+        const float2 r2 = *reinterpret_cast<const float2*>(xr + 196);
+        S_in = ((r4.x + r4.y) + (r4.z + r4.w)) + (r2.x + r2.y);
+        U = ((u0 + u1) + (u2 + u3)) * (1.0f / S_in);
       }
-      U = ((u0 + u1) + (u2 + u3)) * (1.0f / S_in);
+      const float R = fmaxf(U, kEps);
+      const float x = live ? fmaxf(e, kEps) * R : 0.f;
+      if (store) { *store = d ? R : x; store = reinterpret_cast<float*>(reinterpret_cast<char*>(store) + dqb); }
+      if (tid == 0) *hist = S_in;
+      hist += dt;
+      float v = x;
+#pragma unroll
+      for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (live) xw[tid] = x;
+      if (lane == 0) xw[192 + warp] = v;
+      __syncthreads();
     }
-    const float R = fmaxf(U, kEps);
-    x = live ? fmaxf(e, kEps) * R : 0.f;
-    if (store && live) store[(size_t)t * q] = d ? R : x;
-    if (tid == 0) hist[t] = S_in;
-    float v = x;
-#pragma unroll
-    for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    __syncthreads();                 // everyone has read xs of the previous step
-    if (live) xs[tid] = x;
-    if (lane == 0) red[warp] = v;
-    __syncthreads();
-    float tot = 0.f;
-    for (int w = 0; w < nw; ++w) tot += red[w];
-    S_in = tot;
-    t += dt;
-  };
-  // emission rows are loaded a block of SEQ_PF steps ahead into alternating register sets (a step is shorter than a
-  // DRAM round trip)
-  constexpr int SEQ_PF = 8;
-  float ea[SEQ_PF], eb[SEQ_PF];
-  const int t_first = t;
-  auto load_block = [&](float (&dst)[SEQ_PF], int s0) {
-#pragma unroll
-    for (int u = 0; u < SEQ_PF; ++u)
-      dst[u] = (live && s0 + u < T) ? __ldg(Eseq + (size_t)(t_first + (s0 + u) * dt) * q) : 0.f;
-  };
-  auto run_block = [&](const float (&use)[SEQ_PF], float (&fill)[SEQ_PF], int s0) {
-    load_block(fill, s0 + SEQ_PF);
-#pragma unroll
-    for (int u = 0; u < SEQ_PF; ++u)
-      if (s0 + u < T) step(use[u], s0 + u);
-  };
-  load_block(ea, 0);
-  for (int s0 = 0; s0 < T; s0 += 2 * SEQ_PF) {
-    run_block(ea, eb, s0);
-    if (s0 + SEQ_PF < T) run_block(eb, ea, s0 + SEQ_PF);
   }
-  if (d == 0 && tid < a.ntile) a.part_f[(size_t)seq * a.ntile + tid] = tid == 0 ? S_in : 0.f;
+  if (d == 0 && tid < a.ntile) {
+    const float* xr = sm + (T & 1) * SEQ_XS + 192;
+    a.part_f[(size_t)seq * a.ntile + tid] = tid == 0 ? ((xr[0] + xr[1]) + (xr[2] + xr[3])) + (xr[4] + xr[5]) : 0.f;
+  }
 }
 
 // per sequence: cumulative log scales (double) and the log-likelihood.
@@ -454,7 +472,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     if (rc) return rc;
   }
   // small q: one persistent launch for all steps of both directions (seq_kernel); g_path == 1 keeps the per-step engine
-  const size_t seq_smem = ((size_t)q * q + 200) * sizeof(float);
+  const size_t seq_smem = ((size_t)q * q + SEQ_HDR) * sizeof(float);
   const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024 && N <= 2147483647ull;
   if (seq) {
     static size_t smem_set = 0;
