@@ -167,15 +167,40 @@ struct SeqArgs {
 constexpr int SEQ_PF = 8;          // emission rows per prefetch block
 constexpr int SEQ_XS = 200;        // floats per state buffer: 192 state slots + 8 per-warp partial sums
 constexpr int SEQ_HDR = 2 * SEQ_XS + 2 * SEQ_PF * 192;   // two state buffers + the two-block emission ring
+// shared-memory accesses of the step loop through 32-bit shared addresses held in registers (a generic pointer makes the
+// compiler rebuild the shared window base from SR_CgaCtaId inside the loop, on the step's dependency chain)
+__device__ __forceinline__ float4 lds4(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float2 lds2(unsigned addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds1(unsigned addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts1(unsigned addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
 template <int QR>
 __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   extern __shared__ float sm[];
-  const int q = a.q, T = a.T, tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  // thread index and direction pinned in registers: left to itself the compiler re-reads SR_TID / SR_CTAID (20+ cycles
+  // each, on the step's dependency chain) several times per step instead of keeping them
+  int tid_ = threadIdx.x, d_ = a.dir0 + blockIdx.y;
+  asm volatile("" : "+r"(tid_), "+r"(d_));
+  const int q = a.q, T = a.T, tid = tid_, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
   // sm[0..400): two state buffers (state of step s is written to buffer (s+1)&1 — one barrier per step); each holds the
   // un-normalised state padded to 192 floats (16-byte aligned float4 reads) and the per-warp partial sums at +192
   float* ring = sm + 2 * SEQ_XS;  // [2][SEQ_PF][192] emission ring, a thread touches only its own column
   float* As = sm + SEQ_HDR;       // q x q, row-major: U_j = sum_i x_i A[i][j], thread j walks a column
-  const int seq = blockIdx.x, m = seq / a.B, d = a.dir0 + blockIdx.y;
+  const int seq = blockIdx.x, m = seq / a.B, d = d_;
   const float* Am = (d == 0 ? a.A : a.At) + (size_t)m * q * q;
   for (int i = tid; i < q * q; i += nt) As[i] = __ldg(Am + i);
   for (int i = tid; i < 2 * SEQ_XS; i += nt) sm[i] = 0.f;
@@ -189,10 +214,10 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   // emission rows arrive SEQ_PF steps ahead through cp.async into the ring (a step is shorter than a DRAM round trip);
   // the step loop itself stays rolled so that its body is fetched from the instruction cache
   // (running pointers made opaque to the compiler, which otherwise rebuilds them from the kernel parameters at every use)
-  unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring + tid);
+  unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring + tid), sm_s = (unsigned)__cvta_generic_to_shared(sm);
   long long dqb = (long long)dq * 4;
   const char* esrc = reinterpret_cast<const char*>(Eseq);
-  asm volatile("" : "+r"(ring_s), "+l"(dqb), "+l"(esrc), "+l"(store), "+l"(hist));
+  asm volatile("" : "+r"(ring_s), "+r"(sm_s), "+l"(dqb), "+l"(esrc), "+l"(store), "+l"(hist));
   int e_left = live ? T : 0;
   auto issue = [&](int blk) {
     const unsigned dst = ring_s + (unsigned)((blk & 1) * SEQ_PF * 192 * 4);
@@ -217,24 +242,22 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   for (int blk = 0; blk < nblk; ++blk) {
     issue(blk + 1);
     asm volatile("cp.async.wait_group 1;" ::: "memory");
-    const float* eb = ring + (blk & 1) * SEQ_PF * 192 + tid;
     const int s_end = min(SEQ_PF, T - blk * SEQ_PF);
 #pragma unroll 1
     for (int u = 0; u < s_end; ++u) {
       const int s = blk * SEQ_PF + u;
-      const float e = live ? eb[u * 192] : 0.f;
+      const float e = live ? lds1(ring_s + (unsigned)(((blk & 1) * SEQ_PF + u) * 192 * 4)) : 0.f;
       const float* xr = sm + (s & 1) * SEQ_XS;          // state of step s-1
-      float* xw = sm + ((s & 1) ^ 1) * SEQ_XS;
+      const unsigned xr_s = sm_s + (unsigned)((s & 1) * SEQ_XS * 4), xw_s = sm_s + (unsigned)(((s & 1) ^ 1) * SEQ_XS * 4);
       float U;
       if (s == 0) {
         U = live ? (d == 0 ? __ldg(a.pi + (size_t)m * q + tid) : 1.f) : 0.f;
       } else {
         float u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
         if (QR > 0) {
-          const float4* x4 = reinterpret_cast<const float4*>(xr);
 #pragma unroll
           for (int i = 0; i < QR / 4; ++i) {
-            const float4 v = x4[i];
+            const float4 v = lds4(xr_s + 16 * i);
             u0 = fmaf(v.x, acol[4 * i], u0); u1 = fmaf(v.y, acol[4 * i + 1], u1);
             u2 = fmaf(v.z, acol[4 * i + 2], u2); u3 = fmaf(v.w, acol[4 * i + 3], u3);
           }
@@ -250,8 +273,8 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
           for (; i < q; ++i) u0 = fmaf(xr[i], col[(size_t)i * q], u0);
         }
         // S_in: sum of the previous state over the (at most six) warps; unused slots hold zeros
-        const float4 r4 = *reinterpret_cast<const float4*>(xr + 192);
-        const float2 r2 = *reinterpret_cast<const float2*>(xr + 196);
+        const float4 r4 = lds4(xr_s + 192 * 4);
+        const float2 r2 = lds2(xr_s + 196 * 4);
         S_in = ((r4.x + r4.y) + (r4.z + r4.w)) + (r2.x + r2.y);
         U = ((u0 + u1) + (u2 + u3)) * (1.0f / S_in);
       }
@@ -263,8 +286,8 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
       float v = x;
 #pragma unroll
       for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (live) xw[tid] = x;
-      if (lane == 0) xw[192 + warp] = v;
+      if (live) sts1(xw_s + 4 * tid, x);
+      if (lane == 0) sts1(xw_s + 4 * (192 + warp), v);
       __syncthreads();
     }
   }
