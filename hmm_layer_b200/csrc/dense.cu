@@ -297,6 +297,17 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   }
 }
 
+template <int QR>
+static int seq_launch(dim3 grid, int nthreads, size_t smem, cudaStream_t st, const SeqArgs& a) {
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<QR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  seq_kernel<QR><<<grid, nthreads, smem, st>>>(a);
+  return 0;
+}
+
 // per sequence: cumulative log scales (double) and the log-likelihood.
 //   forward:  hist[t] = S_{t-1} (1 at t = 0), final = partial sums of the last state  ->  cum_f[t] = sum_{tau<=t} log S_tau
 //   backward: hist[t] = S_{t+1} (1 at t = T-1)                                        ->  cum_b[t] = sum_{tau>t} log S_tau
@@ -498,17 +509,6 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   const size_t seq_smem = ((size_t)q * q + SEQ_HDR) * sizeof(float);
   const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024 && N <= 2147483647ull;
   if (seq) {
-    static size_t smem_set = 0;
-    if (seq_smem > smem_set) {
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<160>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seq_smem));
-      smem_set = seq_smem;
-    }
     SeqArgs a;
     a.E = E; a.A = A; a.At = At; a.pi = pi;
     a.store[0] = need_f ? out_alpha : nullptr; a.store[1] = need_b ? out_beta : nullptr;
@@ -518,12 +518,23 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
     a.dir0 = need_f ? 0 : 1;
     const int nthreads = ((q + 31) / 32) * 32;
     const dim3 sgrid((unsigned)N, (need_f && need_b) ? 2 : 1);
-    if (q <= 32) seq_kernel<32><<<sgrid, nthreads, seq_smem, st>>>(a);
-    else if (q <= 64) seq_kernel<64><<<sgrid, nthreads, seq_smem, st>>>(a);
-    else if (q <= 96) seq_kernel<96><<<sgrid, nthreads, seq_smem, st>>>(a);
-    else if (q <= 128) seq_kernel<128><<<sgrid, nthreads, seq_smem, st>>>(a);
-    else if (q <= 160) seq_kernel<160><<<sgrid, nthreads, seq_smem, st>>>(a);
-    else seq_kernel<192><<<sgrid, nthreads, seq_smem, st>>>(a);
+    // register column length in steps of 16 states (q = 67 runs 80 FMAs per step, not 96); the dropped terms are 0 * 0
+    int rc = 0;
+    switch ((q + 15) / 16) {
+      case 1: rc = seq_launch<16>(sgrid, nthreads, seq_smem, st, a); break;
+      case 2: rc = seq_launch<32>(sgrid, nthreads, seq_smem, st, a); break;
+      case 3: rc = seq_launch<48>(sgrid, nthreads, seq_smem, st, a); break;
+      case 4: rc = seq_launch<64>(sgrid, nthreads, seq_smem, st, a); break;
+      case 5: rc = seq_launch<80>(sgrid, nthreads, seq_smem, st, a); break;
+      case 6: rc = seq_launch<96>(sgrid, nthreads, seq_smem, st, a); break;
+      case 7: rc = seq_launch<112>(sgrid, nthreads, seq_smem, st, a); break;
+      case 8: rc = seq_launch<128>(sgrid, nthreads, seq_smem, st, a); break;
+      case 9: rc = seq_launch<144>(sgrid, nthreads, seq_smem, st, a); break;
+      case 10: rc = seq_launch<160>(sgrid, nthreads, seq_smem, st, a); break;
+      case 11: rc = seq_launch<176>(sgrid, nthreads, seq_smem, st, a); break;
+      default: rc = seq_launch<192>(sgrid, nthreads, seq_smem, st, a); break;
+    }
+    if (rc) return rc;
   }
   for (int d = 0; d < 2 && !tc && !seq; ++d) {
     if ((d == 0 && !need_f) || (d == 1 && !need_b)) continue;
