@@ -24,10 +24,29 @@ class HmmCell(nn.Module):
         self.use_fake_step_counter = use_fake_step_counter
         self.recurrent_init()
 
+    def __setattr__(self, name, value):
+        if isinstance(value, nn.Module):   # a plugin was swapped: the cached module list of _param_key is stale
+            self.__dict__.pop("_ri_modules", None)
+        super().__setattr__(name, value)
+
     # ---- parameter -> matrices, once per call (reference :41-59) ----
     def _param_key(self):
         """Identity + version of every parameter / buffer: unchanged key = unchanged derived tensors (A, B, pi)."""
-        return tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers()))
+        # walks the modules' own parameter / buffer dicts (the module list is collected once): nn.Module.parameters()
+        # re-discovers the module tree on every call, a third of the host time of a config-1 forward
+        mods = self.__dict__.get("_ri_modules")
+        if mods is None:
+            mods = tuple(self.modules())
+            object.__setattr__(self, "_ri_modules", mods)
+        key = []
+        for m in mods:
+            for t in m._parameters.values():
+                if t is not None:
+                    key.append((t.data_ptr(), t._version))
+            for t in m._buffers.values():
+                if t is not None:
+                    key.append((t.data_ptr(), t._version))
+        return tuple(key)
 
     def recurrent_init(self, fresh=False):
         """Derived tensors of this call (reference MsaHmmCell.py:41-59).  They are functions of the parameters only, so

@@ -27,15 +27,21 @@ def _req(t, name, shape=None):
     return t.contiguous()
 
 
-def _stream():
-    return torch.cuda.current_stream().cuda_stream
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
+def _stream(device=None):
+    """cudaStream_t of torch's current stream (the raw getter skips the Stream object: 2 us instead of 14 per call)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device() if device is None or device.index is None else device.index)
+    return torch.cuda.current_stream(device).cuda_stream
 
 
 _ws_cache = {}
 
 
 def _workspace(nbytes, device):
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    key = (device.index, _stream(device))
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
