@@ -75,9 +75,10 @@ class HmmCell(nn.Module):
         return self.init_dist.device
 
     def emission_probs(self, inputs, end_hints=None, training=False):
-        em_probs = self.emitter[0](inputs, end_hints=end_hints, training=training)
-        for em in self.emitter[1:]:
-            em_probs = em_probs * em(inputs, end_hints=end_hints, training=training)
+        em_probs = None   # (iterating the ModuleList: slicing it builds a new nn.ModuleList on every call)
+        for em in self.emitter:
+            e = em(inputs, end_hints=end_hints, training=training)
+            em_probs = e if em_probs is None else em_probs * e
         return em_probs
 
     # ---- one DP step (reference :73-106) ----
