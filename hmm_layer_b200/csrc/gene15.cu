@@ -51,6 +51,8 @@ constexpr int G = 32;         // chunks per tile
 constexpr int HEAP = 2 * G;   // blocks per tile in heap order: [1] tile product, [2..G) inner nodes, [G..2G) chunks
 constexpr int MAX_SCAN_TILES = 60;    // K1's last CTA of a sequence scans up to this many tile matrices itself
 constexpr int K1_THREADS = G * 16;
+constexpr int KST = 20;       // K1: floats between the coefficient rows of consecutive positions (80 B: the position-per-lane
+                              // stores and loads of a warp then fall into 32 different bank groups; 64 B would be 4-way conflicts)
 constexpr unsigned EMIT_LOG_FLOORED = 0x40000000u;   // internal flag of emission_kernel (not part of the C ABI)
 #ifndef HMM_K1_BLOCKS
 #ifndef HMM_K1_BLOCKS
@@ -83,7 +85,7 @@ struct Args {
   unsigned mL;     // (1 << DIV_SHIFT) / L + 1
   int C;           // chunks per sequence = ceil(T / L)
   int P;           // tiles per sequence  = ceil(C / G)
-  int top_scan;    // K1's last CTA per sequence scans the tile matrices (no boundary_kernel)
+  int top_scan;    // who scans the tile matrices: 0 boundary_kernel, 1 K1's last CTA of the sequence, 2 every K2 CTA itself
   // sequence sharding (multi-GPU): this rank holds positions [seq_off, seq_off + T) of sequences of total length
   // seq_total; halo nucleotides and boundary vectors come from the neighbours.
   int seq_off, seq_total;
@@ -112,6 +114,15 @@ struct Args {
 // small helpers
 // ------------------------------------------------------------------------------------------------------------
 #define HMM_MARK(base, k) do { if (a.dbg && threadIdx.x == 0) a.dbg[(size_t)(base) * 16 + (k)] = clock64(); } while (0)
+// wall-clock stamps (globaltimer, ns; comparable across SMs) and the SM id: slot 14 at CTA start, 15 at CTA end, 13 = smid
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ int smid() { int r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
+#define HMM_WALL(base, k) do { if (a.dbg && threadIdx.x == 0) { a.dbg[(size_t)(base) * 16 + (k)] = gtimer(); a.dbg[(size_t)(base) * 16 + 13] = smid(); } } while (0)
+
+// programmatic dependent launch: the next kernel of the stream may start its CTAs (their prologue) while this grid
+// drains; it touches nothing this grid wrote before griddep_wait()
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ int fexp(float x) { return ((__float_as_int(x) >> 23) & 0xff) - 127; }
 __device__ __forceinline__ int clamp_exp(int e) { return max(-126, min(126, e)); }
@@ -339,15 +350,9 @@ __device__ __forceinline__ void codon_factors(const Args& a, const EmisSmem& sp,
 // fetched from shared memory serves all of them.  FLOOR: max(e, eps) as the recursion applies it (MsaHmmCell.py:87).
 // rows[k]: the 20 input floats of position t[k] (16-byte aligned; global memory, or the tile staged in shared memory)
 template <bool FLOOR, int NP>
-__device__ __forceinline__ void emit_n(const Args& a, const EmisSmem& sp, int n, const int (&t)[NP],
-                                       const signed char* const (&cd)[NP], const float* const (&rows)[NP], float (&e)[NP][Q]) {
-  float4 x[NP][4];
+__device__ __forceinline__ void emit_x(const Args& a, const EmisSmem& sp, int n, const int (&t)[NP],
+                                       const signed char* const (&cd)[NP], const float4 (&x)[NP][4], float (&e)[NP][Q]) {
   float cod[NP][9];
-#pragma unroll
-  for (int k = 0; k < NP; ++k) {
-    const float4* row = reinterpret_cast<const float4*>(rows[k]);
-    x[k][0] = row[0]; x[k][1] = row[1]; x[k][2] = row[2]; x[k][3] = row[3];
-  }
 #pragma unroll
   for (int k = 0; k < NP; ++k) codon_factors(a, sp, n, t[k], cd[k], cod[k]);
   const float train = (a.flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
@@ -384,6 +389,19 @@ __device__ __forceinline__ void emit_n(const Args& a, const EmisSmem& sp, int n,
       for (int q = 0; q < Q; ++q) e[k][q] = fmaxf(e[k][q], kEps);
     }
   }
+}
+
+// the same with the rows read here
+template <bool FLOOR, int NP>
+__device__ __forceinline__ void emit_n(const Args& a, const EmisSmem& sp, int n, const int (&t)[NP],
+                                       const signed char* const (&cd)[NP], const float* const (&rows)[NP], float (&e)[NP][Q]) {
+  float4 x[NP][4];
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const float4* row = reinterpret_cast<const float4*>(rows[k]);
+    x[k][0] = row[0]; x[k][1] = row[1]; x[k][2] = row[2]; x[k][3] = row[3];
+  }
+  emit_x<FLOOR, NP>(a, sp, n, t, cd, x, e);
 }
 
 // two positions i0 (valid) and i1 (valid iff two) of the tile
@@ -705,12 +723,15 @@ struct K1Smem {
   float ones[QP];
 };
 
-// shared memory after K1Smem: [coefficient rows G*CS floats | staged input rows (G*L + 4) * 20 floats], reused as the
-// product tree (HEAP blocks) once the conditional rows are done, then as the staged tile matrices of the top scan
-__host__ __device__ inline size_t k1_coef_bytes(int L) { return (size_t)G * (L * QP + 4) * sizeof(float); }
+// shared memory after K1Smem: the staged input rows ((G*L + 4) * 20 floats) and the coefficient rows (G*CS floats) share
+// ONE region: an emission round reads its input rows into registers, the CTA meets at a barrier, and the round's
+// coefficient rows (16 floats at a stride of 20, like the input rows) overwrite rows that have all been read by then --
+// coefficient row i sits on the input row of position i or i - 2.  Reused as the product tree (HEAP blocks) once the conditional rows are done, then as the staged
+// tile matrices of the top scan.  At chunk length 35 this is 90 KB instead of 162 KB: two CTAs per SM.
+__host__ __device__ inline size_t k1_coef_bytes(int L) { return (size_t)G * L * 20 * sizeof(float); }
 __host__ __device__ inline size_t k1_in_bytes(int L) { return ((size_t)G * L + 4) * SIN * sizeof(float); }
 __host__ __device__ inline size_t k1_union_bytes(int L, int P) {
-  size_t b = k1_coef_bytes(L) + k1_in_bytes(L);
+  size_t b = k1_coef_bytes(L) > k1_in_bytes(L) ? k1_coef_bytes(L) : k1_in_bytes(L);
   const size_t tree = (size_t)HEAP * MAT * sizeof(float);
   if (tree > b) b = tree;
   const size_t scan = (size_t)(P <= MAX_SCAN_TILES ? P : 0) * MAT * sizeof(float);
@@ -729,7 +750,7 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
   float* U = reinterpret_cast<float*>(smem + ((sizeof(K1Smem) + 15) / 16) * 16);
   signed char* codes = reinterpret_cast<signed char*>(U) + k1_union_bytes(a.L, a.P);
   const int L = a.L, T = a.T, CS = L * QP + 4;
-  float* IN = U + (size_t)G * CS;   // staged input rows
+  float* IN = U;   // staged input rows: the same region as the coefficient rows (see k1_union_bytes)
   const int tid = threadIdx.x;
   const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
   const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
@@ -738,6 +759,8 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
   const int cta = blockIdx.y * gridDim.x + blockIdx.x;
   const size_t tile = (size_t)n * a.P + p;
   HMM_MARK(cta, 0);
+  HMM_WALL(cta, 14);
+  if (tid == 0) griddep_launch_dependents();   // every CTA of this grid is resident or done when the last one says so
 
   // ---- parameters first (their loads would otherwise queue behind this CTA's own bulk copy), then the tile's input
   // rows (with the two neighbours either side the 3-mer windows reach) by one bulk copy ----
@@ -809,17 +832,22 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
     float e0[Q];
     float* r0 = U;
     int ci0 = 0;
+    float4 xin[1][4];
+    if (one) {
+      const float4* row = reinterpret_cast<const float4*>(IN + (size_t)(t_lo + i0 - t_in0) * SIN);
+      xin[0][0] = row[0]; xin[0][1] = row[1]; xin[0][2] = row[2]; xin[0][3] = row[3];
+    }
+    __syncthreads();   // every input row of this round is in registers: its coefficient rows may land on top of them
     if (one) {
       const int t[1] = {t_lo + i0};
       const signed char* const cd[1] = {codes + 2 + i0};
-      const float* const rows[1] = {IN + (size_t)(t_lo + i0 - t_in0) * SIN};
       float e[1][Q];
-      emit_n<true, 1>(a, S.sp, n, t, cd, rows, e);
+      emit_x<true, 1>(a, S.sp, n, t, cd, xin, e);
 #pragma unroll
       for (int q = 0; q < Q; ++q) e0[q] = e[0][q];
       ci0 = divL(a, i0);
-      const int roff = ci0 * CS + (i0 - ci0 * L) * QP;
-      r0 = U + roff;
+      const int roff = ci0 * CS + (i0 - ci0 * L) * QP;   // the workspace keeps K2's layout
+      r0 = U + i0 * KST;
       reinterpret_cast<float4*>(r0)[2] = make_float4(e0[7], e0[8], e0[9], e0[10]);
       reinterpret_cast<float4*>(r0)[3] = make_float4(e0[11], e0[12], e0[13], e0[14]);
       if (Eg) store_row16(Eg + roff, e0, 0.f);
@@ -827,7 +855,7 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
     __syncthreads();
     float ep0[8];
     if (one) {
-      const float* q0 = (i0 == 0) ? r0 + 8 : (tid == 0) ? S.carry : U + tile_row_offset(a, i0 - 1, CS) + 8;
+      const float* q0 = (i0 == 0) ? r0 + 8 : (tid == 0) ? S.carry : r0 - KST + 8;
       const float4 u0 = reinterpret_cast<const float4*>(q0)[0], u1 = reinterpret_cast<const float4*>(q0)[1];
       ep0[0] = u0.x; ep0[1] = u0.y; ep0[2] = u0.z; ep0[3] = u0.w; ep0[4] = u1.x; ep0[5] = u1.y; ep0[6] = u1.z; ep0[7] = u1.w;
     }
@@ -867,7 +895,7 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
   if (c < a.C && row < Q) {
     const bool first = (c == 0 && seq_start);
     const int t0 = c * L, t1 = min(T, t0 + L) - 1, ts = t0 + (first ? 1 : 0);
-    const float* Kp = U + ci * CS;
+    const float* Kp = U + ci * L * KST;
     const float init = first ? Kp[row] : 1.f;   // E_0[row]
     float xm[7], ym[8];
 #pragma unroll
@@ -883,7 +911,7 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
       float x[7], xp[7];
       {
         float k1[QP];
-        load_row16(Kp + (ts - t0) * QP, k1);
+        load_row16(Kp + (ts - t0) * KST, k1);
 #pragma unroll
         for (int j = 0; j < 7; ++j) x[j] = k1[j] * xm[SRC1[j]];
 #pragma unroll
@@ -895,7 +923,7 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
 #pragma unroll 4
       for (int t = ts + 1; t <= t1; ++t) {
         float k[QP];
-        load_row16(Kp + (t - t0) * QP, k);
+        load_row16(Kp + (t - t0) * KST, k);
         float xn[7];
         xn[0] = fmaf(k[7 + 7], xp[5], k[0] * x[0]);
         xn[1] = fmaf(k[7 + 1], xp[4], k[1] * x[1]);
@@ -954,7 +982,8 @@ __global__ void __launch_bounds__(K1_THREADS, BLOCKS) products_kernel(const Args
     bulk_wait_all();
   }
   HMM_MARK(cta, 6);
-  if (!a.top_scan) return;
+  HMM_WALL(cta, 15);
+  if (a.top_scan != 1) return;   // 0: boundary_kernel scans the tile matrices, 2: every K2 CTA does (scan_tiles_global)
 
   // ---- top-level scan by the last CTA of the sequence to get here (TotalProbabilityCell.py:30-49 in scaled
   // probability space): boundary vectors entering / leaving every tile, log-likelihood ----
@@ -1263,6 +1292,64 @@ __device__ __forceinline__ void named_barrier_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// The top-level scan (TotalProbabilityCell.py:30-49 in scaled probability space) done by every K2 CTA for itself, by one
+// warp, from the sequence's tile matrices in global memory (L2): lanes 0-15 run pi . M_0 ... M_{P-1} (snapshot on
+// entering tile p; the end gives the log-likelihood), lanes 16-31 run M_{P-1} ... M_{p+1} . 1.  The next block's
+// entries are fetched while the current one is used.  Returns the tile's boundary vector (entering for the forward half,
+// leaving for the backward half); *ll is valid in lane 0.
+constexpr int MAX_K2_SCAN = 16;       // sequences of up to this many tiles are scanned inside K2 (no counter, no extra kernel)
+__device__ __forceinline__ HV scan_tiles_global(const float* Mt, int P, int p, const float* __restrict__ pi_m, int hl, int hi,
+                                                float* ll) {
+  const int row = min(hl, Q - 1);
+  HV h, snap;
+  h.v = (hl < Q) ? (hi == 0 ? __ldg(pi_m + hl) : 1.f) : 0.f;
+  h.e = 0;
+  snap = h;
+  const int steps = hi == 0 ? P : P - 1 - p;
+  float v[QP], sp, dcol;
+  int Eb;
+  auto fetch = [&](int it, float (&vv)[QP], float& spv, float& dv, int& ev) {
+    const float* blk = Mt + (size_t)(hi == 0 ? it : P - 1 - it) * MAT;   // it < P: always inside the sequence's list
+#pragma unroll
+    for (int k = 0; k < QP; ++k) vv[k] = __ldcg(hi == 0 ? blk + k * QP + hl : blk + row * QP + k);
+    spv = __ldcg(blk + row * QP + 15);
+    dv = __ldcg(blk + 15 * QP + hl);
+    ev = __float_as_int(__ldcg(blk + MAT - 1));
+  };
+  // both halves run P rounds (the shuffles are warp-wide); the backward half commits the first P - 1 - p of them, its
+  // remaining rounds read blocks p .. 0 for nothing
+  fetch(0, v, sp, dcol, Eb);
+  for (int it = 0; it < P; ++it) {
+    float vn[QP], spn = 0.f, dn = 0.f;
+    int En = 0;
+    const bool more = it + 1 < P;
+    if (more) fetch(it + 1, vn, spn, dn, En);
+    if (hi == 0 && it == p) snap = h;
+    const float u = (hl < Q) ? (hi ? h.v : h.v * sp) : 0.f;
+    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      const float uk = __shfl_sync(0xffffffffu, u, k, 16);
+      if (k & 1) acc1 = fmaf(uk, v[k], acc1); else acc0 = fmaf(uk, v[k], acc0);
+    }
+    const float s = half_sum(hi ? ((hl < Q) ? u * dcol : 0.f) : u);
+    const int ex = pexp(s);
+    const float out = (hi ? sp : 1.f) * (acc0 + acc1) * pow2neg(ex);
+    if (it < steps) {
+      h.v = (hl < Q) ? out : 0.f;
+      h.e += clamp_exp(ex) + Eb;
+    }
+    if (more) {
+#pragma unroll
+      for (int k = 0; k < QP; ++k) v[k] = vn[k];
+      sp = spn; dcol = dn; Eb = En;
+    }
+  }
+  const float tot = half_sum(h.v);
+  *ll = (float)((double)h.e * LN2D + (double)logf(tot));   // meaningful in the forward half only
+  return hi == 0 ? snap : h;
+}
+
 template <bool FULL>
 __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -1278,6 +1365,7 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
   const size_t tile = (size_t)n * P + p;
   const int cta = blockIdx.y * gridDim.x + blockIdx.x + gridDim.x * gridDim.y;
   HMM_MARK(cta, 0);
+  HMM_WALL(cta, 14);
 
   // ---- bulk copies: the tile's tree (heap nodes 1 .. 2G-1 land at Bh[1 ..]) and its emission rows ----
   float* Bh = U - MAT;     // heap indexing: node k at Bh + k * MAT (node 0 does not exist and is never touched)
@@ -1287,12 +1375,20 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
     float aw = 0.f, bvv = 0.f, llv = 0.f;
     int bve = 0;
     if (tid < NEDGE) aw = __ldg(a.A + (size_t)m * Q * Q + ESRC[tid] * Q + EDST[tid]);
+    griddep_wait();     // everything below reads what the kernels before this one wrote
     if (warp == 1) {
-      // boundary vectors of the tile (K1's top scan or boundary_kernel): lanes 0-15 forward, lanes 16-31 backward
-      const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
-      bvv = __ldcg(bv + hl);
-      bve = __float_as_int(__ldcg(bv + 15));
-      if (lane == 0) llv = __ldcg(a.llws + n);
+      if (a.top_scan == 2) {
+        // short sequences: this CTA scans the sequence's tile matrices itself (under the bulk copies issued by warp 0)
+        const HV b = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
+        bvv = b.v; bve = b.e;
+        if (lane == 0 && p == 0 && a.loglik) a.loglik[n] = llv;
+      } else {
+        // boundary vectors of the tile (K1's top scan or boundary_kernel): lanes 0-15 forward, lanes 16-31 backward
+        const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
+        bvv = __ldcg(bv + hl);
+        bve = __float_as_int(__ldcg(bv + 15));
+        if (lane == 0) llv = __ldcg(a.llws + n);
+      }
     }
     if (tid == 0) {
       mbar_init(&S.bar[0], 1);
@@ -1574,6 +1670,7 @@ __global__ void __launch_bounds__(512, 1) finalize_kernel(const Args a) {
     }
   }
   HMM_MARK(cta, 7);
+  HMM_WALL(cta, 15);
 }
 
 // stand-alone emission (cell.emission_probs API parity); unfloored
@@ -2293,6 +2390,24 @@ static int launch_boundary(const Args& a, const Layout& l, int NB, int mode, flo
   return 0;
 }
 
+// K2 launch.  `pdl`: programmatic dependent launch behind the kernel just queued on `st` -- K2's CTAs are placed and run
+// their prologue while that kernel drains; everything that reads its results sits behind griddepcontrol.wait.
+static int launch_finalize(const Args& a, int NB, bool full, size_t sm2, cudaStream_t st, bool pdl) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(a.P, NB);
+  cfg.blockDim = dim3(k2_threads_for(a.L));
+  cfg.dynamicSmemBytes = sm2;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  if (full) HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, finalize_kernel<true>, a));
+  else HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, finalize_kernel<false>, a));
+  return 0;
+}
+
 int run(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
         const float* codon5, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
         float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st, const unsigned short* cls16 = nullptr,
@@ -2310,7 +2425,7 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   set_L(a, choose_L(NB, T, full));
   const bool need_k2 = out_post || out_alpha || out_beta;
   // short tile lists are scanned by K1's last CTA of every sequence, long ones by the boundary kernel
-  a.top_scan = (a.P <= MAX_SCAN_TILES) ? 1 : 0;
+  a.top_scan = (need_k2 && a.P <= MAX_K2_SCAN) ? 2 : (a.P <= MAX_SCAN_TILES) ? 1 : 0;
   Layout l;
   rc = bind_workspace(a, l, NB, workspace, workspace_bytes, "genepred");
   if (rc) return rc;
@@ -2320,7 +2435,7 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   const size_t sm1 = k1_smem_bytes(a.L, a.P), sm2 = k2_smem_bytes(a.L, full);
   if (need_k2 && !full) { rc = set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc; }
   if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
-  if (a.top_scan) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
+  if (a.top_scan == 1) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
 
   if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
   rc = launch_products(a, NB, st); if (rc) return rc;
@@ -2330,9 +2445,8 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
     if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   }
   if (need_k2) {
-    const int nt = k2_threads_for(a.L);
-    if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
-    else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);
+    // directly behind products_kernel and not timed kernel by kernel: as a programmatic dependent launch
+    rc = launch_finalize(a, NB, full, sm2, st, a.top_scan != 0 && !g_prof); if (rc) return rc;
     if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
   }
   HMM_CUDA_OK(cudaGetLastError());
@@ -2533,9 +2647,7 @@ int shard_finalize(const float* inputs, int num_models, int batch, int T, int se
     const size_t sm2 = k2_smem_bytes(a.L, full);
     rc = full ? set_smem(finalize_kernel<true>, SLOT_K2F, sm2) : set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc;
     rc = launch_boundary(a, l, NB, 0, nullptr, true, workspace, st); if (rc) return rc;   // Gt: from shard_reduce
-    const int nt = k2_threads_for(a.L);
-    if (full) finalize_kernel<true><<<dim3(a.P, NB), nt, sm2, st>>>(a);
-    else finalize_kernel<false><<<dim3(a.P, NB), nt, sm2, st>>>(a);
+    rc = launch_finalize(a, NB, full, sm2, st, false); if (rc) return rc;
   }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;

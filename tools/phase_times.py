@@ -34,5 +34,9 @@ for k in range(2):
     for j, nm in enumerate(names[k]):
         print(f"   {nm:22s} median {np.median(dt[:, j]):9.0f}  max {dt[:, j].max():9.0f}")
     print(f"   per-CTA total          median {np.median(t[:, -1] - t[:, 0]):9.0f}")
-    st = np.sort(t[:, 0] - t[:, 0].min())
-    print(f"   CTA start offsets: p25 {st[len(st)//4]}  p50 {st[len(st)//2]}  p75 {st[3*len(st)//4]}  max {st[-1]}")
+    w0, w1, sm = d[k][:, 14], d[k][:, 15], d[k][:, 13]
+    base = d[0][:, 14].min()
+    st, en = np.sort(w0 - base), np.sort(w1 - base)
+    print(f"   wall clock (ns after the first CTA of kernel 0 started): starts p0 {st[0]} p25 {st[len(st)//4]} p50 {st[len(st)//2]} p75 {st[3*len(st)//4]} max {st[-1]};"
+          f" ends p0 {en[0]} p50 {en[len(en)//2]} max {en[-1]}; CTA wall median {np.median(w1 - w0):.0f} ns")
+    print(f"   SMs used {len(np.unique(sm))}, max CTAs on one SM {np.bincount(sm.astype(int)).max()}")
