@@ -21,29 +21,75 @@ def _is_fused_gene_cell(cell):
 
 def _check_inputs(inputs, cell, parallel_factor):
     """CPU inputs are accepted for the fused gene model only (host path: outputs come back as CPU tensors, like the
-    reference's); the parameters always live on the GPU."""
+    reference's).  The compute always runs on a GPU: a cell whose parameters live on the CPU (the reference's own script
+    never moves it, tests/parallel_rnn_forward.py:42-51) has its few derived parameter tensors uploaded per call."""
     if inputs.dim() != 4:
         raise ValueError(f"inputs must have shape (num_model, b, seq_len, s), got {tuple(inputs.shape)}")
     if inputs.shape[0] != cell.num_models:
         raise ValueError(f"inputs carry {inputs.shape[0]} models but the cell has {cell.num_models}")
     if parallel_factor < 1 or inputs.shape[2] % parallel_factor != 0:
         raise ValueError(f"parallel_factor={parallel_factor} must divide the sequence length {inputs.shape[2]}")
-    if not inputs.is_cuda and not (_is_fused_gene_cell(cell) and cell.init_dist.is_cuda):
-        raise ValueError("inputs must be CUDA tensors (CPU inputs only for the fused gene model with its cell on a GPU): "
-                         "this layer has no CPU compute path")
+    if not torch.cuda.is_available():
+        raise RuntimeError("hmm_layer_b200 has no CPU compute path: a CUDA device is required")
+
+
+def _compute_device(inputs, cell):
+    if inputs.is_cuda:
+        return inputs.device
+    p = next(cell.parameters(), None)
+    if p is not None and p.is_cuda:
+        return p.device
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _gene_param_tensors(cell, dev):
+    """Kernel-ready (A, pi, Bfull, codon5) of the fused gene model on `dev`, rebuilt from the parameters on every call
+    like the reference's recurrent_init (MsaHmmCell.py:41-50) -- one launch of the parameter kernel when the kernels
+    live on the GPU -- or kept across calls after cell.freeze_derived(True)."""
+    em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
+    if cell.__dict__.get("_frozen", False):
+        cell.recurrent_init()          # resets _gene_params when a parameter changed
+        gp = cell.__dict__.get("_gene_params")
+        if gp is not None and gp[0].device == dev:
+            return gp
+    elif _fused_params_ok(cell, em, tr) and em.emission_kernel.device == dev:
+        with torch.no_grad():
+            A, pi, Bfull = ops.GeneParams.apply(tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)
+        # what recurrent_init would have left on the plugins (values identical to make_A / make_initial_distribution)
+        tr.A, tr.A_transposed = A, A.transpose(1, 2)
+        cell.init_dist = pi.reshape(1, cell.num_models, -1)
+        em.B = None
+        return (A, pi, Bfull, em.codon5(dev))
+    else:
+        cell.recurrent_init()
+    with torch.no_grad():
+        gp = (tr.A.detach().to(dev).contiguous(), cell.init_dist.detach().reshape(cell.num_models, -1).to(dev).contiguous(),
+              em.make_B_full().detach().to(dev).contiguous(), em.codon5(dev))
+    object.__setattr__(cell, "_gene_params", gp)
+    return gp
 
 
 def _gene_run(inputs, cell, end_hints, training, **want):
-    em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
-    dev = cell.init_dist.device
-    gp = getattr(cell, "_gene_params", None)   # kernel-ready parameter tensors of this parameter version (recurrent_init resets)
-    if gp is None:
-        gp = (tr.A.detach().contiguous(), cell.init_dist.detach().reshape(cell.num_models, -1).contiguous(),
-              em.make_B_full().detach().contiguous(), em.codon5(dev))
-        object.__setattr__(cell, "_gene_params", gp)
+    dev = _compute_device(inputs, cell)
+    gp = _gene_param_tensors(cell, dev)
     if not inputs.is_cuda:   # host buffers: H2D / kernels / D2H pipelined inside the library, CPU tensors back
-        return ops.genepred_run_host(inputs, *gp, end_hints=None if end_hints is None else end_hints.cpu(), training=training, **want)
+        with torch.cuda.device(dev):
+            return ops.genepred_run_host(inputs, *gp, end_hints=None if end_hints is None else end_hints.cpu(), training=training, **want)
+    if end_hints is not None:
+        end_hints = end_hints.to(dev)
     return ops.genepred_run(inputs, *gp, end_hints=end_hints, training=training, **want)
+
+
+def _dense_run_cell(inputs, cell, end_hints, training, **want):
+    """Any other cell: emissions from the cell's emitters (CUDA kernels / cuBLAS), then the generic dense recurrence.
+    Host inputs and a CPU-resident cell are accepted like in the reference: the compute runs on the GPU and the results
+    come back on the inputs' device."""
+    cell.recurrent_init()
+    dev = _compute_device(inputs, cell)
+    x = inputs.to(dev)
+    E = cell.emission_probs(x, end_hints=None if end_hints is None else end_hints.to(dev), training=training)
+    r = ops.dense_run(E.detach(), cell.transitioner.A.detach().to(dev), cell.init_dist.detach().reshape(cell.num_models, -1).to(dev), **want)
+    return r if inputs.is_cuda else {k: v.to(inputs.device) for k, v in r.items()}
 
 
 def _gene_loglik_diff(inputs, cell, training):
@@ -75,14 +121,12 @@ def _priors(cell, result, return_prior):
 def _forward_recursion_impl(inputs, cell, rnn=None, total_prob_rnn=None, end_hints=None, return_prior=False,
                             training=False, parallel_factor=1):
     """log alpha (num_model, b, seq_len, q) and log-likelihoods (num_model, b)  (reference :227-282)."""
-    cell.recurrent_init()
     _check_inputs(inputs, cell, parallel_factor)
     if _is_fused_gene_cell(cell):
         r = _gene_run(inputs, cell, end_hints, training, want_post=False, want_alpha=True)
         res = (r["alpha"], r["loglik"])
     else:
-        E = cell.emission_probs(inputs, end_hints=end_hints, training=training)
-        r = ops.dense_run(E, cell.transitioner.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1), want_alpha=True)
+        r = _dense_run_cell(inputs, cell, end_hints, training, want_alpha=True)
         res = (r["alpha"], r["loglik"])
     return _priors(cell, res, return_prior)
 
@@ -90,13 +134,11 @@ def _forward_recursion_impl(inputs, cell, rnn=None, total_prob_rnn=None, end_hin
 def _backward_recursion_impl(inputs, cell, reverse_cell=None, rnn_backward=None, total_prob_rnn_rev=None,
                              end_hints=None, return_prior=False, training=False, parallel_factor=1):
     """log beta (num_model, b, seq_len, q)  (reference :322-381)."""
-    cell.recurrent_init()
     _check_inputs(inputs, cell, parallel_factor)
     if _is_fused_gene_cell(cell):
         res = _gene_run(inputs, cell, end_hints, training, want_post=False, want_beta=True)["beta"]
     else:
-        E = cell.emission_probs(inputs, end_hints=end_hints, training=training)
-        res = ops.dense_run(E, cell.transitioner.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1), want_beta=True)["beta"]
+        res = _dense_run_cell(inputs, cell, end_hints, training, want_beta=True)["beta"]
     return _priors(cell, res, return_prior)
 
 
@@ -104,14 +146,11 @@ def _state_posterior_log_probs_impl(inputs, cell, reverse_cell=None, bidirection
                                     total_prob_rnn_rev=None, end_hints=None, return_prior=False, training=False,
                                     no_loglik=False, parallel_factor=1):
     """log P(state q at position i | inputs), (num_model, b, seq_len, q)  (reference :422-521)."""
-    cell.recurrent_init()
     _check_inputs(inputs, cell, parallel_factor)
     if _is_fused_gene_cell(cell):
         res = _gene_run(inputs, cell, end_hints, training, want_post=True, no_loglik=no_loglik)["post"]
     else:
-        E = cell.emission_probs(inputs, end_hints=end_hints, training=training)
-        res = ops.dense_run(E, cell.transitioner.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1),
-                            want_post=True, no_loglik=no_loglik)["post"]
+        res = _dense_run_cell(inputs, cell, end_hints, training, want_post=True, no_loglik=no_loglik)["post"]
     return _priors(cell, res, return_prior)
 
 
@@ -163,14 +202,11 @@ class MsaHmmLayer(nn.Module):
         `log_A_dense` :46-47) but does not ship.  Fused gene model only."""
         self.build(inputs.shape)
         cell = self.cell
-        cell.recurrent_init()
         _check_inputs(inputs, cell, 1)
         if not _is_fused_gene_cell(cell) or not inputs.is_cuda:
             raise NotImplementedError("viterbi is implemented for the 15-state gene model with CUDA inputs")
-        em, tr = cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)
-        path, score = ops.genepred_viterbi(inputs, tr.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1),
-                                           em.make_B_full().detach(), em.codon5(inputs.device), end_hints=end_hints,
-                                           training=training)
+        A, pi, Bfull, codon5 = _gene_param_tensors(cell, inputs.device)
+        path, score = ops.genepred_viterbi(inputs, A, pi, Bfull, codon5, end_hints=end_hints, training=training)
         return (path.long(), score) if return_score else path.long()
 
     def apply_sequence_weights(self, loglik, indices, aggregate=False):
@@ -201,22 +237,31 @@ class MsaHmmLayer(nn.Module):
         inputs = inputs.to(torch.float32)
         self.build(inputs.shape)
         cell = self.cell
-        diff = torch.is_grad_enabled() and inputs.is_cuda and (
-            inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
+        diff = torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
         fused_gene = _is_fused_gene_cell(cell)
-        cell.recurrent_init(fresh=diff and not (fused_gene and _fused_params_ok(
-            cell, cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner))))
         _check_inputs(inputs, cell, self.parallel_factor)
+        home = inputs.device
+        if diff and not inputs.is_cuda:
+            # the reference traces its loop wherever the tensors live; here the differentiable route is the CUDA one, so
+            # host inputs follow the parameters to their device (a differentiable copy) instead of silently losing grad_fn
+            p0 = next(cell.parameters(), None)
+            if p0 is None or not p0.is_cuda:
+                raise ValueError("a differentiable call needs the cell's parameters on a CUDA device (cell.to('cuda')): "
+                                 "this layer has no CPU compute path")
+            inputs = inputs.to(p0.device)
         if diff and fused_gene:
+            if not _fused_params_ok(cell, cell.emitter[0], getattr(cell.transitioner, "base", cell.transitioner)):
+                cell.recurrent_init(fresh=True)     # a fresh autograd graph from the parameters, like the reference
             loglik = _gene_loglik_diff(inputs, cell, training)
         elif diff:   # any other cell: emissions, A and pi stay attached to the parameters' graph
+            cell.recurrent_init(fresh=True)
             E = cell.emission_probs(inputs, training=training)
             loglik = ops.DenseLoglik.apply(E, cell.transitioner.A, cell.init_dist.reshape(cell.num_models, -1))
-        elif _is_fused_gene_cell(cell):
+        elif fused_gene:
             loglik = _gene_run(inputs, cell, None, training, want_post=False)["loglik"]
         else:
-            E = cell.emission_probs(inputs, training=training)
-            loglik = ops.dense_run(E, cell.transitioner.A.detach(), cell.init_dist.detach().reshape(cell.num_models, -1))["loglik"]
+            loglik = _dense_run_cell(inputs, cell, None, training)["loglik"]
+        loglik = loglik.to(home)      # results live where the inputs live, like the reference's (a differentiable copy)
         if self.sequence_weights is not None:
             loglik = loglik.to(self.sequence_weights.device)
         loglik_mean = torch.squeeze(self.apply_sequence_weights(loglik, indices, aggregate=True))

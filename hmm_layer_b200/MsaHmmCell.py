@@ -25,21 +25,28 @@ class HmmCell(nn.Module):
         self.recurrent_init()
 
     def __setattr__(self, name, value):
-        if isinstance(value, nn.Module):   # a plugin was swapped: the cached module list of _param_key is stale
+        if isinstance(value, nn.Module):   # a plugin was swapped: derived tensors and the cached module list are stale
             self.__dict__.pop("_ri_modules", None)
+            self.__dict__["_ri_key"] = None
         super().__setattr__(name, value)
 
     # ---- parameter -> matrices, once per call (reference :41-59) ----
     def _param_key(self):
-        """Identity + version of every parameter / buffer: unchanged key = unchanged derived tensors (A, B, pi)."""
-        # walks the modules' own parameter / buffer dicts (the module list is collected once): nn.Module.parameters()
-        # re-discovers the module tree on every call, a third of the host time of a config-1 forward
-        mods = self.__dict__.get("_ri_modules")
-        if mods is None:
-            mods = tuple(self.modules())
-            object.__setattr__(self, "_ri_modules", mods)
-        key = []
-        for m in mods:
+        """Identity + version of every parameter / buffer the derived tensors depend on, including those of the base
+        transitioner behind a reverse cell's view (it is deliberately not a registered sub-module) and the identity of
+        every plugin (an emitter swapped inside the ModuleList changes the key).  Only consulted after
+        `freeze_derived(True)`."""
+        ids = (id(self.transitioner), *(id(e) for e in self.emitter))
+        cached = self.__dict__.get("_ri_modules")
+        if cached is None or cached[0] != ids:
+            mods = list(self.modules())
+            base = getattr(self.transitioner, "base", None)
+            if isinstance(base, nn.Module):
+                mods += [m for m in base.modules() if all(m is not x for x in mods)]
+            cached = (ids, tuple(mods))
+            object.__setattr__(self, "_ri_modules", cached)
+        key = [ids]
+        for m in cached[1]:
             for t in m._parameters.values():
                 if t is not None:
                     key.append((t.data_ptr(), t._version))
@@ -48,15 +55,34 @@ class HmmCell(nn.Module):
                     key.append((t.data_ptr(), t._version))
         return tuple(key)
 
+    def freeze_derived(self, on=True):
+        """Opt-in for inference loops: after freeze_derived(True), `recurrent_init` rebuilds A / B / pi only when the
+        identity or the autograd version of a parameter changed (optimizer steps, load_state_dict, in-place ops and
+        plugin swaps are all seen).  NOT seen: writes through `.data` (`p.data.copy_(...)`), which do not bump the
+        version -- call `invalidate()` after those.  Default (off) = the reference's behaviour: rebuild on every call
+        (MsaHmmCell.py:41-50)."""
+        object.__setattr__(self, "_frozen", bool(on))
+        object.__setattr__(self, "_ri_key", None)
+        return self
+
+    def invalidate(self):
+        """Forget the derived tensors kept by `freeze_derived(True)`; the next call rebuilds them."""
+        object.__setattr__(self, "_ri_key", None)
+
+    def derived_fresh(self):
+        """True when frozen derived tensors exist and still match the parameters (always False when not frozen)."""
+        return bool(self.__dict__.get("_frozen", False)) and self.__dict__.get("_ri_key") is not None \
+            and self.__dict__.get("_ri_key") == self._param_key()
+
     def recurrent_init(self, fresh=False):
-        """Derived tensors of this call (reference MsaHmmCell.py:41-59).  They are functions of the parameters only, so
-        they are rebuilt only when a parameter changed (in-place updates bump the version, .to()/.data swaps change the
-        pointer): at inference the ~20 small parameter-construction launches drop out of every call.
-        fresh=True rebuilds them regardless (a differentiable call needs its own autograd graph from the parameters)."""
+        """Derived tensors of this call (reference MsaHmmCell.py:41-59): rebuilt on every call like the reference,
+        unless `freeze_derived(True)` was requested and no parameter changed.  fresh=True rebuilds regardless (a
+        differentiable call needs its own autograd graph from the parameters)."""
         if not self.reverse and self.use_step_counter:
             self.step_counter = torch.tensor(-1, dtype=torch.int32)
-        key = self._param_key()
-        if getattr(self, "_ri_key", None) == key and not fresh:
+        frozen = self.__dict__.get("_frozen", False)
+        key = self._param_key() if frozen else None
+        if frozen and not fresh and self.__dict__.get("_ri_key") == key:
             return
         self.transitioner.recurrent_init()
         for em in self.emitter:

@@ -16,7 +16,7 @@ EXPORTS = [
     "hmm_b200_genepred_grad_workspace_size", "hmm_b200_genepred_grad",
     "hmm_b200_genepred_viterbi_workspace_size", "hmm_b200_genepred_viterbi",
     "hmm_b200_genepred_params", "hmm_b200_genepred_params_grad",
-    "hmm_b200_genepred_emission", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
+    "hmm_b200_genepred_emission", "hmm_b200_emission_general", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
     "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_cell_step",
 ]
 
@@ -56,6 +56,7 @@ def load():
     lib.hmm_b200_genepred_emission.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp,
                                                ctypes.c_uint, c_fp, c_fp]
     ci = ctypes.c_int
+    lib.hmm_b200_emission_general.argtypes = [c_fp, ci, ci, ci, ci, ci, ci, ci, c_fp, c_fp, c_fp, ctypes.c_uint, c_fp, c_fp]
     lib.hmm_b200_genepred_params.argtypes = [c_fp, c_fp, c_fp, ci, c_fp, c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_params_grad.argtypes = [c_fp, c_fp, c_fp, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_viterbi_workspace_size.restype = ctypes.c_size_t

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <mutex>
 #include "../../include/hmm_b200.h"
 
 namespace hmm {
@@ -51,6 +52,39 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
+}
+
+// ---- per-device library state (one process may drive several GPUs, from several threads) -----------------------
+constexpr int kMaxDevices = 64;
+inline std::mutex& state_mutex() { static std::mutex m; return m; }
+inline int current_device() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess) { (void)cudaGetLastError(); d = 0; }
+  return (d < 0 || d >= kMaxDevices) ? 0 : d;
+}
+inline int device_sm_count() {
+  static int sms[kMaxDevices] = {0};
+  const int d = current_device();
+  std::lock_guard<std::mutex> lk(state_mutex());
+  if (sms[d] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, d) != cudaSuccess || n <= 0) { (void)cudaGetLastError(); n = 148; }
+    sms[d] = n;
+  }
+  return sms[d];
+}
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT device only: remembered per (device, slot);
+// slots are library-wide kernel ids (see SMEM_SLOT_* in the callers)
+constexpr int kSmemSlots = 24;
+template <typename K>
+inline int ensure_dynamic_smem(K kernel, int slot, size_t bytes) {
+  static size_t done[kMaxDevices][kSmemSlots] = {};
+  const int d = current_device();
+  std::lock_guard<std::mutex> lk(state_mutex());
+  if (bytes <= done[d][slot]) return 0;
+  HMM_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  done[d][slot] = bytes;
+  return 0;
 }
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }

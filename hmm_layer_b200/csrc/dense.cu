@@ -299,11 +299,7 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
 
 template <int QR>
 static int seq_launch(dim3 grid, int nthreads, size_t smem, cudaStream_t st, const SeqArgs& a) {
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(seq_kernel<QR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-  }
+  { int rcs = ensure_dynamic_smem(seq_kernel<QR>, 10 + QR / 16, smem); if (rcs) return rcs; }   // slots 11..22: one per build
   seq_kernel<QR><<<grid, nthreads, smem, st>>>(a);
   return 0;
 }
@@ -312,8 +308,9 @@ static int seq_launch(dim3 grid, int nthreads, size_t smem, cudaStream_t st, con
 //   forward:  hist[t] = S_{t-1} (1 at t = 0), final = partial sums of the last state  ->  cum_f[t] = sum_{tau<=t} log S_tau
 //   backward: hist[t] = S_{t+1} (1 at t = T-1)                                        ->  cum_b[t] = sum_{tau>t} log S_tau
 __global__ void __launch_bounds__(32) cum_kernel(const float* __restrict__ hist_f, const float* __restrict__ part_f,
-                                                 const float* __restrict__ hist_b, float* __restrict__ cum_f,
-                                                 float* __restrict__ cum_b, float* __restrict__ loglik, int N, int T, int ntile) {
+                                                 const float* __restrict__ hist_b, double* __restrict__ cum_f,
+                                                 double* __restrict__ cum_b, float* __restrict__ loglik,
+                                                 double* __restrict__ loglik_d, int N, int T, int ntile) {
   // one warp per sequence: lane l owns the contiguous steps [l * seg, (l + 1) * seg); segment sums in double, a warp
   // prefix / suffix scan over the 32 sums, then the running sums inside each segment (same order of additions for every
   // launch: deterministic)
@@ -337,9 +334,10 @@ __global__ void __launch_bounds__(32) cum_kernel(const float* __restrict__ hist_
     const double total = __shfl_sync(0xffffffffu, pre, 31);
     if (cum_f) {
       double c = pre - mine;
-      for (int t = lo; t < hi; ++t) { c += term(t); cum_f[(size_t)n * T + t] = (float)c; }
+      for (int t = lo; t < hi; ++t) { c += term(t); cum_f[(size_t)n * T + t] = c; }
     }
     if (loglik && lane == 0) loglik[n] = (float)total;
+    if (loglik_d && lane == 0) loglik_d[n] = total;
   }
   if (hist_b && cum_b) {
     const float* h = hist_b + (size_t)n * T;
@@ -353,35 +351,40 @@ __global__ void __launch_bounds__(32) cum_kernel(const float* __restrict__ hist_
       if (lane + o < 32) suf += v;
     }
     double c = suf - mine;
-    for (int t = hi - 1; t >= lo; --t) { c += term(t); cum_b[(size_t)n * T + t] = (float)c; }
+    for (int t = hi - 1; t >= lo; --t) { c += term(t); cum_b[(size_t)n * T + t] = c; }
   }
 }
 
 // in place: stored a_t -> log alpha_t,  stored R_t -> log beta_t,  and the posterior
-// keep_a / keep_b = 0: the buffer was only lent as scratch (HMM_B200_*_SCRATCH), nothing is written back to it
+// keep_a / keep_b = 0: the buffer was only lent as scratch (HMM_B200_*_SCRATCH), nothing is written back to it.
+// The cumulative log scales and the log-likelihood are doubles: the posterior's shift cum_f + cum_b - loglik is a small
+// difference of sums that reach 1e3 .. 1e5, formed here in double and only then rounded (in fp32 the rows of exp(post)
+// summed to 1 +- 1e-3 at |loglik| = 5000).
 __global__ void finish_kernel(float* __restrict__ alpha, float* __restrict__ beta, float* __restrict__ post,
-                              const float* __restrict__ hist_f, const float* __restrict__ part_f, const float* __restrict__ cum_f,
-                              const float* __restrict__ cum_b, const float* __restrict__ loglik, int N, int T, int q, int ntile,
+                              const float* __restrict__ hist_f, const float* __restrict__ part_f, const double* __restrict__ cum_f,
+                              const double* __restrict__ cum_b, const double* __restrict__ loglik_d, int N, int T, int q, int ntile,
                               int no_loglik, int keep_a, int keep_b, int norm_a) {
   const size_t row = blockIdx.x;           // (n, t)
   const int n = (int)(row / T), t = (int)(row - (size_t)n * T);
-  float S = 1.f, cf = 0.f, cb = 0.f;
+  float S = 1.f;
+  double cf = 0.0, cb = 0.0;
   if (alpha) {
     if (t + 1 < T) S = hist_f[(size_t)n * T + t + 1];
     else { S = 0.f; for (int i = 0; i < ntile; ++i) S += part_f[(size_t)n * ntile + i]; }
     cf = cum_f[(size_t)n * T + t];
   }
   if (beta) cb = cum_b[(size_t)n * T + t];
-  const float ll = (post && !no_loglik) ? loglik[n] : 0.f;
+  const float shift = post ? (float)((cf + cb) - (no_loglik ? 0.0 : loglik_d[n])) : 0.f;
+  const float cff = (float)cf, cbf = (float)cb;
   const float invS = 1.0f / S;
   for (int j = threadIdx.x; j < q; j += blockDim.x) {
     const size_t i = row * q + j;
     float la = 0.f, lb = 0.f;
-    if (alpha) { la = logf(alpha[i] * invS) + cf; }
-    if (beta) { lb = logf(beta[i]) + cb; }
-    if (post) post[i] = la + lb - ll;
-    if (alpha && keep_a) alpha[i] = norm_a ? la - cf : la;   // norm_a: log of the normalised forward vector (HMM_B200_ALPHA_NORMALIZED)
-    if (beta && keep_b) beta[i] = lb;
+    if (alpha) { la = logf(alpha[i] * invS); }
+    if (beta) { lb = logf(beta[i]); }
+    if (post) post[i] = (la + lb) + shift;
+    if (alpha && keep_a) alpha[i] = norm_a ? la : la + cff;   // norm_a: log of the normalised forward vector (HMM_B200_ALPHA_NORMALIZED)
+    if (beta && keep_b) beta[i] = lb + cbf;
   }
 }
 
@@ -447,7 +450,7 @@ __global__ void init_state_kernel(float* __restrict__ st, const float* __restric
 }
 
 struct Layout {
-  size_t st[2][2], part[2][2], hist[2], cum[2], ll, extra, total;
+  size_t st[2][2], part[2][2], hist[2], cum[2], ll, lld, extra, total;
 };
 static Layout layout(int k, int B, int T, int q) {
   Layout l;
@@ -459,8 +462,9 @@ static Layout layout(int k, int B, int T, int q) {
   for (int d = 0; d < 2; ++d)
     for (int p = 0; p < 2; ++p) { l.part[d][p] = off; off = align_up(off + N * ntile * sizeof(float), 256); }
   for (int d = 0; d < 2; ++d) { l.hist[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
-  for (int d = 0; d < 2; ++d) { l.cum[d] = off; off = align_up(off + N * T * sizeof(float), 256); }
+  for (int d = 0; d < 2; ++d) { l.cum[d] = off; off = align_up(off + N * T * sizeof(double), 256); }
   l.ll = off; off = align_up(off + N * sizeof(float), 256);
+  l.lld = off; off = align_up(off + N * sizeof(double), 256);
   l.extra = off;
   if (g_path != 1 && dense_tc::supported(k, B, q)) off += dense_tc::extra_workspace(k, B, q);
   l.total = off;
@@ -492,6 +496,7 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   }
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   auto F = [&](size_t o) { return reinterpret_cast<float*>(ws + o); };
+  auto D = [&](size_t o) { return reinterpret_cast<double*>(ws + o); };
   const bool tc = use_tc(k, B, q);
   const int ntile = tc ? dense_tc::slots(q) : cdiv(q, BN);
   const size_t N = (size_t)k * B;
@@ -554,12 +559,13 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   HMM_CUDA_OK(cudaGetLastError());
   const float* part_f = F(l.part[0][tc ? ((T - 1) & 1) : (T & 1)]);   // slot written by the last forward step
   cum_kernel<<<(unsigned)N, 32, 0, st>>>(need_f ? F(l.hist[0]) : nullptr, part_f, need_b ? F(l.hist[1]) : nullptr,
-                                                 (out_alpha || out_post) ? F(l.cum[0]) : nullptr,
-                                                 need_b ? F(l.cum[1]) : nullptr, need_f ? llbuf : nullptr, (int)N, T, ntile);
+                                                 (out_alpha || out_post) ? D(l.cum[0]) : nullptr,
+                                                 need_b ? D(l.cum[1]) : nullptr, need_f ? llbuf : nullptr,
+                                                 need_f ? D(l.lld) : nullptr, (int)N, T, ntile);
   if (out_post || out_alpha || out_beta) {
     HMM_REQUIRE(N * (size_t)T < 2147483647ull, "dense: k*B*T too large for one launch");
     finish_kernel<<<(unsigned)(N * T), 128, 0, st>>>(need_f ? out_alpha : nullptr, need_b ? out_beta : nullptr, out_post,
-                                                     F(l.hist[0]), part_f, F(l.cum[0]), F(l.cum[1]), llbuf, (int)N, T, q, ntile,
+                                                     F(l.hist[0]), part_f, D(l.cum[0]), D(l.cum[1]), D(l.lld), (int)N, T, q, ntile,
                                                      (flags & HMM_B200_NO_LOGLIK) ? 1 : 0,
                                                      (flags & HMM_B200_ALPHA_SCRATCH) ? 0 : 1, (flags & HMM_B200_BETA_SCRATCH) ? 0 : 1,
                                                      (flags & HMM_B200_ALPHA_NORMALIZED) ? 1 : 0);

@@ -485,14 +485,7 @@ static Dims dims(int k, int B, int q) {
   return d;
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 0;
-  }
-  return n;
-}
+static int sm_count() { return device_sm_count(); }
 
 bool supported(int k, int B, int q) {
   const Dims d = dims(k, B, q);
@@ -512,11 +505,7 @@ size_t extra_workspace(int k, int B, int q) {
 int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
               float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st) {
   const Dims d = dims(k, B, q);
-  static bool attr_done = false;
-  if (!attr_done) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_done = true;
-  }
+  { int rcs = ensure_dynamic_smem(chain_kernel, 9, SMEM_BYTES); if (rcs) return rcs; }   // slot 9: dense_tc chain
   const int sms = sm_count();
   HMM_REQUIRE(sms >= d.ntile_n, "dense_tc: %d column tiles need as many SMs (device has %d)", d.ntile_n, sms);
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(extra) + 1023) & ~(uintptr_t)1023);

@@ -2165,40 +2165,38 @@ __global__ void __launch_bounds__(64) params_grad_kernel(const float* __restrict
 // ------------------------------------------------------------------------------------------------------------
 static int g_L = 0;          // 0: choose per call
 static int g_k2_threads = 0; // 0: choose per call
-static int g_num_sms = 0;
 static long long* g_dbg = nullptr;  // device buffer for phase timestamps (debug)
 
-// optional per-kernel timing (bench.py's roofline leg): events around each launch of the last profiled call
+// optional per-kernel timing (bench.py's roofline leg): events around each launch of the last profiled call, kept per
+// device (an event belongs to the device it was created on)
 static bool g_prof = false;
-static cudaEvent_t g_ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-static int g_ev_n = 0;
+struct ProfEvents { cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; int n = 0; };
+static ProfEvents g_pe[kMaxDevices];
+static int g_prof_dev = 0;   // device of the last profiled call
 
+static int prof_events(ProfEvents** out) {
+  ProfEvents& p = g_pe[current_device()];
+  std::lock_guard<std::mutex> lk(state_mutex());
+  if (!p.ev[0])
+    for (int i = 0; i < 5; ++i) HMM_CUDA_OK(cudaEventCreate(&p.ev[i]));
+  *out = &p;
+  return 0;
+}
 int profile_enable(int on) {
-  if (on && !g_ev[0])
-    for (int i = 0; i < 5; ++i) HMM_CUDA_OK(cudaEventCreate(&g_ev[i]));
   g_prof = on != 0;
-  g_ev_n = 0;
+  for (int d = 0; d < kMaxDevices; ++d) g_pe[d].n = 0;
   return 0;
 }
 int profile_read(float* ms, int n) {
-  if (g_ev_n < 2) return 0;
-  HMM_CUDA_OK(cudaEventSynchronize(g_ev[g_ev_n - 1]));
+  ProfEvents& p = g_pe[g_prof_dev];
+  if (p.n < 2) return 0;
+  HMM_CUDA_OK(cudaEventSynchronize(p.ev[p.n - 1]));
   int k = 0;
-  for (; k < g_ev_n - 1 && k < n; ++k) HMM_CUDA_OK(cudaEventElapsedTime(&ms[k], g_ev[k], g_ev[k + 1]));
+  for (; k < p.n - 1 && k < n; ++k) HMM_CUDA_OK(cudaEventElapsedTime(&ms[k], p.ev[k], p.ev[k + 1]));
   return k;
 }
 
-static int num_sms() {
-  if (g_num_sms == 0) {
-    int dev = 0, sms = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
-      (void)cudaGetLastError();
-      sms = 148;
-    }
-    g_num_sms = sms;
-  }
-  return g_num_sms;
-}
+static int num_sms() { return device_sm_count(); }
 
 static int max_L(bool full) {
   int L = MAX_L;
@@ -2308,16 +2306,10 @@ static void set_L(Args& a, int L) {
   a.P = cdiv(a.C, G);
 }
 
-// raises a kernel's dynamic shared memory limit when this call needs more than any earlier one (slot = kernel id)
-static size_t g_smem_set[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+// raises a kernel's dynamic shared memory limit when this call needs more than any earlier one on this device
 template <typename K>
-static int set_smem(K kernel, int slot, size_t bytes) {
-  if (bytes <= g_smem_set[slot]) return 0;
-  HMM_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-  g_smem_set[slot] = bytes;
-  return 0;
-}
-enum { SLOT_K1 = 0, SLOT_K2P = 1, SLOT_K2F = 2, SLOT_KB = 3, SLOT_EM = 4 };
+static int set_smem(K kernel, int slot, size_t bytes) { return ensure_dynamic_smem(kernel, slot, bytes); }
+enum { SLOT_K1 = 0, SLOT_K2P = 1, SLOT_K2F = 2, SLOT_KB = 3, SLOT_EM = 4, SLOT_GRAD = 8 };
 
 static int k2_threads_for(int L) {
   if (g_k2_threads > 0) return g_k2_threads;
@@ -2437,17 +2429,18 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   if (need_k2 && full) { rc = set_smem(finalize_kernel<true>, SLOT_K2F, sm2); if (rc) return rc; }
   if (a.top_scan == 1) HMM_CUDA_OK(cudaMemsetAsync(a.cnt, 0, (size_t)NB * sizeof(unsigned), st));
 
-  if (g_prof) { g_ev_n = 0; cudaEventRecord(g_ev[g_ev_n++], st); }
+  ProfEvents* pe = nullptr;
+  if (g_prof) { rc = prof_events(&pe); if (rc) return rc; g_prof_dev = current_device(); pe->n = 0; cudaEventRecord(pe->ev[pe->n++], st); }
   rc = launch_products(a, NB, st); if (rc) return rc;
-  if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
+  if (pe) cudaEventRecord(pe->ev[pe->n++], st);
   if (!a.top_scan) {
     rc = launch_boundary(a, l, NB, 0, nullptr, false, workspace, st); if (rc) return rc;
-    if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
+    if (pe) cudaEventRecord(pe->ev[pe->n++], st);
   }
   if (need_k2) {
     // directly behind products_kernel and not timed kernel by kernel: as a programmatic dependent launch
-    rc = launch_finalize(a, NB, full, sm2, st, a.top_scan != 0 && !g_prof); if (rc) return rc;
-    if (g_prof) cudaEventRecord(g_ev[g_ev_n++], st);
+    rc = launch_finalize(a, NB, full, sm2, st, a.top_scan != 0 && !pe); if (rc) return rc;
+    if (pe) cudaEventRecord(pe->ev[pe->n++], st);
   }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
@@ -2694,11 +2687,7 @@ int grad(const float* inputs, int num_models, int batch, int T, const float* A, 
   }
   g.part = static_cast<float*>(workspace);
   set_L(a, 32);   // codes_stage / emission helpers only need a valid chunk length
-  static bool smem_set = false;
-  if (!smem_set) {
-    HMM_CUDA_OK(cudaFuncSetAttribute(grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GradSmem)));
-    smem_set = true;
-  }
+  rc = set_smem(grad_kernel, SLOT_GRAD, sizeof(GradSmem)); if (rc) return rc;
   if (grad_A) HMM_CUDA_OK(cudaMemsetAsync(grad_A, 0, (size_t)num_models * Q * Q * sizeof(float), st));
   grad_kernel<<<dim3(g.PT, NB), GR_POS, sizeof(GradSmem), st>>>(a, g);
   grad_reduce_kernel<<<dim3(GR_PART / 32, num_models), 1024, 0, st>>>(g.part, batch * g.PT, grad_A, grad_pi, grad_Bfull);

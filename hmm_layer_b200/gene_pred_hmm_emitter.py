@@ -24,6 +24,25 @@ def make_codon_probs(codons, pivot_left):
     return probs.reshape(64).unsqueeze(0).unsqueeze(0)
 
 
+def _differentiable_emission(inputs, Bfull, codon5, num_copies, end_hints, training):
+    """Emissions that stay attached to the autograd graph of B and of the class probabilities (training a model the fused
+    15-state kernels do not cover).  The class contraction is the only differentiable factor; everything else (codon
+    factors, end hints, the training epsilon) is a constant of the graph and comes from the CUDA emission kernel run with
+    a unit class factor (class row = e_0, B = ones)."""
+    from . import ops
+    k, B, T, w = inputs.shape
+    s = w - 5 if codon5 is not None else w
+    q = Bfull.shape[1]
+    with torch.no_grad():
+        unit = torch.zeros_like(inputs)
+        unit[..., 0] = 1.0
+        if codon5 is not None:
+            unit[..., s:] = inputs[..., s:]
+        const = ops.emission_general(unit, torch.ones((k, q, s), dtype=torch.float32, device=inputs.device), codon5,
+                                     num_copies, end_hints=end_hints, training=training)
+    return torch.einsum("kbts,kqs->kbtq", inputs[..., :s], Bfull) * const
+
+
 class SimpleGenePredHMMEmitter(nn.Module):
     """Class-probability emissions: emit = x_t · softmax(kernel)^T (reference :8-146)."""
 
@@ -73,7 +92,16 @@ class SimpleGenePredHMMEmitter(nn.Module):
         return B
 
     def forward(self, inputs, end_hints=None, training=False):
-        raise NotImplementedError("the 7-state simple emitter has no stand-alone CUDA kernel yet; use GenePredHMMEmitter")
+        """(num_models, batch, T, s) -> (num_models, batch, T, num_states) on the GPU (reference :93-121): x . B^T with the
+        intron rows repeated, end hints on the first / last position.  Model i reads inputs[i] (the shipped reference
+        reads inputs[0] for every model, D13)."""
+        from . import ops
+        dev = inputs.device
+        Bfull = self.make_B_full().to(dev)
+        end_hints = None if end_hints is None else end_hints.to(dev)
+        if torch.is_grad_enabled() and (Bfull.requires_grad or inputs.requires_grad):
+            return _differentiable_emission(inputs, Bfull, None, self.num_copies, end_hints, training)
+        return ops.emission_general(inputs, Bfull.detach(), None, self.num_copies, end_hints=end_hints, training=training)
 
     def get_prior_log_density(self):
         return torch.tensor([[0.]])
@@ -131,10 +159,15 @@ class GenePredHMMEmitter(SimpleGenePredHMMEmitter):
     def forward(self, inputs, end_hints=None, training=False):
         """(num_models, batch, T, 15+5) -> (num_models, batch, T, num_states) emission probabilities on the GPU."""
         from . import ops
-        if self.num_copies != 1 or inputs.shape[-1] != 20:
-            raise NotImplementedError("stand-alone CUDA emission supports num_copies=1 with 15 classes + 5 nucleotide flags")
-        return ops.genepred_emission(inputs, self.make_B_full().detach(), self.codon5(inputs.device),
-                                     end_hints=end_hints, training=training)
+        dev = inputs.device
+        Bfull = self.make_B_full().to(dev)
+        end_hints = None if end_hints is None else end_hints.to(dev)
+        if torch.is_grad_enabled() and (Bfull.requires_grad or inputs.requires_grad):
+            return _differentiable_emission(inputs, Bfull, self.codon5(dev), self.num_copies, end_hints, training)
+        Bfull = Bfull.detach()
+        if self.num_copies != 1 or inputs.shape[-1] != 20:   # any class count / number of gene-model copies
+            return ops.emission_general(inputs, Bfull, self.codon5(dev), self.num_copies, end_hints=end_hints, training=training)
+        return ops.genepred_emission(inputs, Bfull, self.codon5(dev), end_hints=end_hints, training=training)
 
     def get_config(self):
         cfg = super().get_config()

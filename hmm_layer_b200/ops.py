@@ -406,6 +406,33 @@ def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
     return E
 
 
+def emission_general(inputs, Bfull, codon=None, num_copies=1, end_hints=None, training=False):
+    """Emissions of SimpleGenePredHMMEmitter (codon=None: inputs (k,B,T,s)) or GenePredHMMEmitter with any number of
+    copies (codon = (2,9,64) codon_probs or the prepared tables: inputs (k,B,T,s+5)); Bfull (k,q,s).  -> (k,B,T,q)."""
+    lib = _lib.load()
+    if inputs.dim() != 4:
+        raise ValueError(f"inputs must have shape (num_models, batch, T, s), got {tuple(inputs.shape)}")
+    inputs = _req(inputs, "inputs")
+    k, B, T, w = inputs.shape
+    has_codon = codon is not None
+    s = w - 5 if has_codon else w
+    Bfull = _req(Bfull, "Bfull")
+    if Bfull.dim() != 3 or Bfull.shape[0] != k or Bfull.shape[2] != s:
+        raise ValueError(f"Bfull must have shape ({k}, q, {s}), got {tuple(Bfull.shape)}")
+    q = Bfull.shape[1]
+    if has_codon:
+        codon = _codon5(codon)
+        if q != 1 + 14 * num_copies:
+            raise ValueError(f"a codon emitter with {num_copies} copies has {1 + 14 * num_copies} states, Bfull has {q}")
+    if end_hints is not None:
+        end_hints = _req(end_hints, "end_hints", (k, B, 2, q))
+    with torch.cuda.device(inputs.device):
+        E = torch.empty((k, B, T, q), dtype=torch.float32, device=inputs.device)
+        _lib.check(lib.hmm_b200_emission_general(_ptr(inputs), k, B, T, s, q, num_copies, 1 if has_codon else 0, _ptr(Bfull),
+                                                 _ptr(codon), _ptr(end_hints), TRAINING if training else 0, _ptr(E), _stream()))
+    return E
+
+
 def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_loglik=False, alpha_normalized=False):
     """Generic dense HMM evaluation from materialised emissions E (k,B,T,q), A (k,q,q), pi (k,q).
     Returns dict with the requested tensors ('post','alpha','beta' each (k,B,T,q)) and 'loglik' (k,B)."""

@@ -2,8 +2,11 @@
  *
  * Conventions (all entry points):
  *   - every pointer is a DEVICE pointer unless stated otherwise; tensors are contiguous float32, row-major;
- *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are stream-ordered,
- *     stateless and re-entrant; inputs are never written (the reference's emitter mutates its input, defect D5);
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls are stream-ordered and work on
+ *     the CURRENT device (cudaSetDevice before the call); one process may drive several devices from several threads:
+ *     the only library state is per device (raised shared-memory limits, SM count, profiling events) and mutex-guarded;
+ *     the tuning / profiling switches are process-wide; inputs are never written (the reference's emitter mutates
+ *     its input, defect D5);
  *   - nothing is allocated inside: the caller owns inputs, outputs and the workspace whose size the matching
  *     *_workspace_size call reports;
  *   - return value 0 = success, negative = HMM_B200_E*; hmm_b200_last_error() gives a thread-local message.
@@ -37,7 +40,7 @@ int hmm_b200_abi_version(void);
 const char* hmm_b200_last_error(void);
 
 /* Optional tuning of the chunked scan: chunk length in positions (0 = chosen per call from the problem size and
- * the SM count; at most 48), threads per CTA of the finalize kernel (0 = derived; a multiple of 32 in [128,512]).
+ * the SM count; at most 40), threads per CTA of the finalize kernel (0 = derived; a multiple of 64 in [128,512]).
  * dense_path selects the step kernel of the generic dense path: 0 = by size (tcgen05 tensor-core step from 192 states),
  * 1 = CUDA-core step always, 2 = tensor-core step always.  Process-wide; meant for benchmarking and tests. */
 int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int dense_path);
@@ -130,6 +133,19 @@ int hmm_b200_genepred_run_host_compact(const unsigned short* host_class_probs_bf
 int hmm_b200_genepred_emission(const float* inputs, int num_models, int batch, int T,
                                const float* Bfull, const float* codon5, const float* end_hints,
                                unsigned flags, float* out_E, void* stream);
+
+/* Stand-alone emission of the gene-structure emitters for any number of classes / states / gene-model copies:
+ *   has_codon = 0: reference SimpleGenePredHMMEmitter.forward (gene_pred_hmm_emitter.py:93-121), inputs
+ *                  (num_models, batch, T, num_classes), E = x . Bfull^T, end hints on the first / last position;
+ *   has_codon = 1: reference GenePredHMMEmitter.forward (:231-263) with num_copies >= 1, inputs
+ *                  (num_models, batch, T, num_classes + 5), num_states == 1 + 14 * num_copies, codon columns repeated per
+ *                  copy (:254-257), 1/4096 for the 1 + 5 * num_copies unconstrained states, +1e-7 with HMM_B200_TRAINING.
+ * Bfull (num_models, num_states, num_classes): one softmax row per state (intron rows repeated, :115-116).  codon5: the
+ * (2,125,12) tables of hmm_b200_genepred_prepare_codon (NULL when has_codon = 0).  out_E (num_models, batch, T, num_states).
+ * Model i reads inputs[i] (the shipped reference reads inputs[0] for every model, defect D13). */
+int hmm_b200_emission_general(const float* inputs, int num_models, int batch, int T, int num_classes, int num_states,
+                              int num_copies, int has_codon, const float* Bfull, const float* codon5,
+                              const float* end_hints, unsigned flags, float* out_E, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Gradient of the gene-HMM log-likelihood (training through the layer).  The reference has no backward code of its

@@ -153,6 +153,54 @@ def genepred_golden():
     print("ref_genepred.npz", {k: np.asarray(v).shape for k, v in out.items()})
 
 
+def multicopy_golden():
+    """4. ref_multicopy.npz – the reference's emitters outside the 15-state single-copy case:
+    GenePredHMMEmitter(num_copies = 2, 3) (gene_pred_hmm_emitter.py:231-263 with the per-copy repeat :254-257) and
+    SimpleGenePredHMMEmitter (:93-121), with end hints and the training flag; plus the 7-state transition matrix.
+    (The reference's A for k > 1 has all-zero rows as shipped -- exact-zero kernel entries are dropped, D6/D11 -- so
+    the multi-copy transitioner is pinned by the oracle's edge list, not by reference output.)"""
+    import torch
+    from hmm_layer.gene_pred_hmm_emitter import GenePredHMMEmitter, SimpleGenePredHMMEmitter
+    from hmm_layer.gene_pred_hmm_transitioner import SimpleGenePredHMMTransitioner
+
+    B, T = 2, 40
+    g = torch.Generator().manual_seed(77)
+    cls = torch.softmax(2 * torch.randn(1, B, T, 15, generator=g), -1)
+    nuc_idx = torch.randint(0, 4, (1, B, T), generator=g)
+    for s_, pos in {"ATG": 3, "GTA": 9, "TAG": 20, "AGC": 14, "TAA": 30}.items():
+        for i, ch in enumerate(s_):
+            nuc_idx[0, 0, pos + i] = "ACGT".index(ch)
+    x = torch.cat([cls, torch.nn.functional.one_hot(nuc_idx, 5).float()], -1)
+    out = dict(inputs=x.numpy())
+    with torch.no_grad():
+        for nc in (2, 3):
+            em = GenePredHMMEmitter(num_copies=nc, **CODONS)
+            em.build((1, B, T, 15))
+            ker = torch.randn(em.emission_kernel.shape, generator=g)
+            em.emission_kernel.copy_(ker)
+            em.recurrent_init()
+            hints = torch.rand(1, B, 2, 1 + 14 * nc, generator=g)
+            out[f"kernel{nc}"] = ker.numpy()
+            out[f"hints{nc}"] = hints.numpy()
+            out[f"E{nc}"] = em(x.clone()).numpy().copy()
+            out[f"E{nc}_hints_training"] = em(x.clone(), end_hints=hints, training=True).numpy().copy()
+        x7 = torch.softmax(torch.randn(1, B, T, 7, generator=g), -1)
+        sem = SimpleGenePredHMMEmitter()
+        sem.build((1, B, T, 7))
+        ker7 = torch.randn(sem.emission_kernel.shape, generator=g)
+        sem.emission_kernel.copy_(ker7)
+        sem.recurrent_init()
+        hints7 = torch.rand(1, B, 2, 7, generator=g)
+        st = SimpleGenePredHMMTransitioner()
+        st.transition_kernel += 1e-3
+        st.recurrent_init()
+        out.update(inputs7=x7.numpy(), kernel7=ker7.numpy(), hints7=hints7.numpy(), E7=sem(x7.clone()).numpy().copy(),
+                   E7_hints=sem(x7.clone(), end_hints=hints7).numpy().copy(), A7=st.A.numpy().copy(),
+                   transition_kernel7=st.transition_kernel.numpy().copy(), pi7=st.make_initial_distribution().numpy()[0].copy())
+    np.savez_compressed(os.path.join(HERE, "ref_multicopy.npz"), **out)
+    print("ref_multicopy.npz", {k: np.asarray(v).shape for k, v in out.items()})
+
+
 def dense_golden():
     import torch
     from hmm_layer.MsaHmmCell import HmmCell
@@ -197,6 +245,10 @@ def dense_golden():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "multicopy":     # only the fixture added in round 2
+        import_reference()
+        multicopy_golden()
+        sys.exit(0)
     kmer_golden()
     import_reference()
     genepred_golden()

@@ -79,7 +79,13 @@ def test_base_rnn_and_bidirectional_wiring():
     assert torch.equal(H.Bidirectional(f, b, merge_mode="sum")(x, initial_state=(*st(), *st()))[0], o[..., :3] + o[..., 3:])
     with pytest.raises(ValueError):
         H.Bidirectional(f, b, merge_mode="mul")
+    # the reference script's wiring (tests/parallel_rnn_forward.py:57-63): a backward layer built with reverse=True is
+    # accepted with a warning and scans right-to-left once (the reference flips twice, defect D3)
+    with pytest.warns(UserWarning):
+        bi_r = H.Bidirectional(f, backward_layer=r, merge_mode="concat")
+    o_r = bi_r(x, initial_state=(*st(), *st()))[0]
+    assert torch.equal(o_r, o)
     with pytest.raises(ValueError):
-        H.Bidirectional(f, r)            # a reverse=True backward layer would be flipped twice (reference defect D3)
+        H.Bidirectional(f, H.BaseRNN(_SumCell(), batch_first=False, return_sequences=True, return_state=True))
     with pytest.raises(ValueError):
         H.Bidirectional("not a module", b)

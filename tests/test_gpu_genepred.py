@@ -158,15 +158,17 @@ def test_degenerate_inputs_stay_finite():
 
 
 def test_config2_full_size_properties():
-    """BASELINE config 2 shape (B=32, T=9999): size-independent properties + oracle on a slice of the batch."""
+    """BASELINE config 2 shape (B=32, T=9999): the fp64 oracle on ALL 32 sequences (every position: argmax, |dp|,
+    loglik) + size-independent properties."""
     x = syn.gene_inputs(1, 32, 9999, seed=1234)
     A, pi, Bfull, tab = gene_params()
     got = run_gpu(x, A, pi, Bfull, tab, want_post=True)
     assert np.isfinite(got["post"]).all()
     np.testing.assert_allclose(np.exp(got["post"].astype(np.float64)).sum(-1), 1.0, atol=1e-4)
-    sl = slice(0, 3)
-    ref = oracle_gene(x.numpy()[:, sl], A, pi, Bfull, tab)
-    check_post({k: v[:, sl] for k, v in got.items()}, ref)
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    check_post(got, ref)
+    rep = O.parity_report(got["post"], got["loglik"], ref["log_post"], ref["loglik"])
+    assert rep["argmax_mismatch"] == 0 and rep["max_abs_dp"] < 1e-4 and rep["loglik_rel"] < 1e-4, rep
     # batch independence: with the same chunk length, a sequence evaluated alone gives the same bits
     try:
         ops.set_tuning(35, 0)
@@ -233,14 +235,19 @@ def test_layer_accepts_cpu_inputs_and_returns_cpu_outputs():
     p_dev = layer.state_posterior_log_probs(x.cuda())
     assert not p_host.is_cuda and p_dev.is_cuda
     np.testing.assert_allclose(np.exp(p_host.numpy()), np.exp(p_dev.cpu().numpy()), atol=2e-5)
-    ll_h, _ = layer(x)
+    ll_h, mean_h = layer(x)              # trainable parameters: the differentiable route, results back on the host
+    assert not ll_h.is_cuda and ll_h.grad_fn is not None
+    mean_h.backward()
+    assert tr.transition_kernel.grad is not None and float(tr.transition_kernel.grad.abs().sum()) > 0
     ll_d = layer(x.cuda())[0].detach()   # differentiable call: the output carries a graph
-    np.testing.assert_allclose(ll_h.numpy(), ll_d.cpu().numpy(), rtol=1e-6)
+    np.testing.assert_allclose(ll_h.detach().numpy(), ll_d.cpu().numpy(), rtol=1e-6)
+    with torch.no_grad():                # inference with host buffers: the pipelined host path
+        np.testing.assert_allclose(layer(x)[0].numpy(), ll_d.cpu().numpy(), rtol=1e-6)
 
 
 def test_config3_full_size_through_the_layer():
     """BASELINE config 3 shape: k-mer emitter (k = 3), bidirectional posterior, batch 64 x 9999 bp, through
-    MsaHmmLayer.state_posterior_log_probs; size-independent properties + the oracle on two sequences."""
+    MsaHmmLayer.state_posterior_log_probs; size-independent properties + the fp64 oracle on ALL 64 sequences."""
     import hmm_layer_b200 as H
     B, T = 64, 9999
     em = H.GenePredHMMEmitter(**syn.GENE_CODONS)
@@ -261,9 +268,11 @@ def test_config3_full_size_through_the_layer():
     A = tr.A.detach().cpu().numpy().astype(np.float64)
     pi = cell.init_dist.detach().cpu().numpy().reshape(1, 15).astype(np.float64)
     Bfull = em.make_B_full().detach().cpu().numpy().astype(np.float64)
-    sl = [7, 63]
-    E = O.genepred_emission(x.numpy()[:, sl], Bfull, em.codon_probs.cpu().numpy())
+    E = O.genepred_emission(x.numpy(), Bfull, em.codon_probs.cpu().numpy())
     ref = O.posterior(E, A, pi)
-    check_post({"post": post.cpu().numpy()[:, sl], "loglik": loglik.cpu().numpy()[:, sl]}, ref)
+    check_post({"post": post.cpu().numpy(), "loglik": loglik.cpu().numpy()}, ref)
+    rep = O.parity_report(post.cpu().numpy(), loglik.cpu().numpy(), ref["log_post"], ref["loglik"])
+    assert rep["argmax_mismatch"] == 0 and rep["max_abs_dp"] < 1e-4 and rep["loglik_rel"] < 1e-4, rep
+    sl = [7, 63]
     no = layer.state_posterior_log_probs(x.cuda(), no_loglik=True)
     np.testing.assert_allclose((no - loglik[..., None, None]).cpu().numpy()[:, sl], post.cpu().numpy()[:, sl], rtol=0, atol=0.05)

@@ -59,9 +59,8 @@ def test_sharded_hints_flags_and_n_at_shard_edges():
 
 
 def test_config5_shape_properties():
-    """One ~1 Mbp sequence over 8 shards: normalisation everywhere, loglik equal to the unsharded evaluation, and the
-    oracle on the first shard's prefix (the forward direction of a prefix does not depend on what follows; the
-    posterior does, so only log alpha is compared there)."""
+    """One ~1 Mbp sequence over 8 shards: the fp64 oracle on the WHOLE sequence (posterior at every position, argmax,
+    log-likelihood; log alpha on a prefix), normalisation everywhere, loglik equal to the unsharded evaluation."""
     T, world = 999_900, 8
     x = syn.gene_inputs(1, 1, T, seed=1234)
     A, pi, Bfull, tab = gene_params()
@@ -71,8 +70,11 @@ def test_config5_shape_properties():
     one = run_gpu(x, A, pi, Bfull, tab, want_post=True)
     np.testing.assert_allclose(got["loglik"], one["loglik"], rtol=1e-6)
     assert (np.argmax(got["post"], -1) != np.argmax(one["post"], -1)).mean() < 1e-5
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    for res in (got, one):
+        rep = O.parity_report(res["post"], res["loglik"], ref["log_post"], ref["loglik"])
+        assert rep["argmax_mismatch"] == 0 and rep["max_abs_dp"] < 1e-4 and rep["loglik_rel"] < 1e-4, rep
     n = 3000
-    ref = oracle_gene(x.numpy()[:, :, :n + 2], A, pi, Bfull, tab)   # +2: the 3-mer windows of the last two positions
     r, g = ref["log_alpha"][:, :, :n], got["alpha"][:, :, :n]
     big = r - r.max(-1, keepdims=True) > -14
     assert (np.abs(g - r) / np.maximum(1.0, np.abs(r)))[big].max() < 1e-4
