@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("HMM_B200_LIB", os.path.join(_HERE, "libhmm_b200.so"))   # override: build-variant experiments
 
 EXPORTS = [
-    "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_profile_enable", "hmm_b200_profile_read", "hmm_b200_debug_phases",
+    "hmm_b200_abi_version", "hmm_b200_last_error", "hmm_b200_set_tuning", "hmm_b200_set_fused_mode", "hmm_b200_profile_enable", "hmm_b200_profile_read", "hmm_b200_debug_phases",
     "hmm_b200_genepred_workspace_size", "hmm_b200_genepred_prepare_codon", "hmm_b200_genepred_run",
     "hmm_b200_genepred_host_scratch_size", "hmm_b200_genepred_run_host",
     "hmm_b200_genepred_run_compact", "hmm_b200_genepred_run_host_compact",
@@ -40,6 +40,7 @@ def load():
     lib.hmm_b200_abi_version.restype = ctypes.c_int
     lib.hmm_b200_last_error.restype = ctypes.c_char_p
     lib.hmm_b200_set_tuning.argtypes = [ctypes.c_int] * 3
+    lib.hmm_b200_set_fused_mode.argtypes = [ctypes.c_int]
     lib.hmm_b200_profile_enable.argtypes = [ctypes.c_int]
     lib.hmm_b200_debug_phases.argtypes = [ctypes.c_void_p]
     lib.hmm_b200_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_int]

@@ -1,0 +1,721 @@
+// 15-state gene-structure HMM: forward + posterior in ONE launch (the config-2 headline path).
+//
+// One 256-thread CTA per tile (G = 32 chunks x L positions of one sequence), two CTAs per SM, all tiles of the call
+// co-resident, so a tile can wait for the other tiles of its sequence inside the kernel:
+//
+//   1 emission      thread = a run of <= 5 consecutive positions, inputs read straight from HBM.  The class-probability
+//                   contraction runs on packed FFMA2 (two states per instruction; B sits in shared memory as state pairs,
+//                   the class probability is the scalar operand), the 3-mer factors are two table rows.  The floored
+//                   emission row goes to the L2-resident workspace (phase 5 streams it back), the coefficient row of the
+//                   two-step recurrence (gene15.cu, K1) to shared memory; a run carries the previous position's pass-state
+//                   emissions in registers, so the whole phase needs ONE barrier (run boundaries are patched behind it).
+//   2 rows          thread = two conditional rows of one chunk's transfer matrix, packed (FFMA2 with the coefficient as
+//                   the scalar operand): 15 FFMA2 per position for two rows.
+//   3 tree          the 5-level product tree of gene15.cu (mma.sync TF32 x 3), kept in shared memory.
+//   4 exchange      the tile matrix goes to the workspace with a per-call tag; one warp polls the tags of the sequence's
+//                   tiles (ld.acquire), scans the tile matrices (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49)
+//                   and the tree is swept down to the chunk boundary vectors.
+//   5 recursion     the exact recursions of MsaHmmCell.py:73-106 inside every chunk, both directions meeting in the middle
+//                   (gene15.cu, K2); emission rows arrive through a 4-deep cp.async ring per thread, so that only the
+//                   own rows / posterior products (Y) need shared memory: 103 KB per CTA instead of 153.
+//   6 output        log posterior through a per-warp staging buffer, coalesced.
+//
+// Against the two-kernel path: no product tree / emission rows re-read through bulk copies, no second launch, no second
+// wave (finalize_kernel fits one CTA per SM), half the FMA issue slots in phases 1 and 2.
+// The same arithmetic as gene15.cu in the same order (floors, scales as exact powers of two): see the comments there.
+#include <atomic>
+#include <chrono>
+#include "gene15_dev.cuh"
+
+namespace hmm {
+namespace gene15 {
+
+typedef unsigned long long u64;
+constexpr int FT = 256;        // threads per CTA
+constexpr int FRUN = 5;        // longest run of positions per emission thread (L <= 40)
+constexpr int FRING = 4;       // emission rows in flight per recursion thread
+constexpr int FRST = 20;       // floats between the ring rows of neighbouring lanes (80 B: conflict-free 128-bit reads)
+
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ u64 bc2(float x) { u64 r; asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(x)); return r; }
+__device__ __forceinline__ void upk2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+__device__ __forceinline__ void cp_async16m(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_m() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_m() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+
+// state held by slot s of a B row in pair order: pairs (0,1) (4,5) (6,7) (8,9) (10,11) (12,13) (14,-); I1, I2 share I0's row
+__device__ constexpr int PSTATE[QP] = {0, 1, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, -1, -1, -1};
+
+struct FSmem {
+  float Aw[24];          // [0..6] A[src1(j)][j], [7..14] A[pred p][p], [15..22] A[p][succ p]
+  float W[24];           // the 23 edge weights in the reference's kernel order
+  float EF[G][QP];       // emission at every chunk's first transition step
+  float EL[G][QP];       // emission at every chunk's last position
+  int hef[HEAP], her[HEAP];
+  float ll;
+  float pad_[3];
+  union {                // phase 1: last pass-state emissions of every run; phases 4-5: boundary vectors of the tree nodes
+    float carry[FT][8];
+    struct { float hvf[HEAP][QP]; float hvr[HEAP][QP]; } v;
+  };
+  union {                // phase 1: B (as state pairs per class, in sp.B) and the codon tables; 5: emission ring; 6: staging
+    EmisSmem sp;
+    float ring[2][FRING][32][FRST];
+    float stage[FT / 32][32 * Q];
+  };
+};
+
+__host__ __device__ inline size_t fused_u_floats(int L) {
+  size_t y = (size_t)G * (L * QP + 4), h = (size_t)HEAP * MAT, c = (size_t)G * L * QP;
+  size_t m = y > h ? y : h;
+  return m > c ? m : c;
+}
+__host__ __device__ inline size_t fused_smem_bytes(int L) { return ((sizeof(FSmem) + 127) / 128) * 128 + fused_u_floats(L) * sizeof(float); }
+
+// coefficient rows: row i at 16 i floats, its 16-byte piece c at piece c ^ ((i >> 1) & 3): the run-per-thread stores of
+// phase 1 (lane stride 5 rows) and the row-per-half-warp loads of phase 2 are both conflict-free
+__device__ __forceinline__ void coef_store(float* U, int i, const float (&k)[QP]) {
+  float4* b = reinterpret_cast<float4*>(U + (size_t)i * QP);
+  const int f = (i >> 1) & 3;
+  b[0 ^ f] = make_float4(k[0], k[1], k[2], k[3]);
+  b[1 ^ f] = make_float4(k[4], k[5], k[6], k[7]);
+  b[2 ^ f] = make_float4(k[8], k[9], k[10], k[11]);
+  b[3 ^ f] = make_float4(k[12], k[13], k[14], k[15]);
+}
+__device__ __forceinline__ void coef_load(const float* U, int i, float (&k)[QP]) {
+  const float4* b = reinterpret_cast<const float4*>(U + (size_t)i * QP);
+  const int f = (i >> 1) & 3;
+  const float4 a0 = b[0 ^ f], a1 = b[1 ^ f], a2 = b[2 ^ f], a3 = b[3 ^ f];
+  k[0] = a0.x; k[1] = a0.y; k[2] = a0.z; k[3] = a0.w; k[4] = a1.x; k[5] = a1.y; k[6] = a1.z; k[7] = a1.w;
+  k[8] = a2.x; k[9] = a2.y; k[10] = a2.z; k[11] = a2.w; k[12] = a3.x; k[13] = a3.y; k[14] = a3.z; k[15] = a3.w;
+}
+__device__ __forceinline__ float coef_at(const float* U, int i, int j) {
+  return U[(size_t)i * QP + ((((j >> 2) ^ (i >> 1)) & 3) << 2) + (j & 3)];
+}
+
+__device__ __forceinline__ u64 sum7p(const u64 (&v)[7]) { return add2(add2(add2(v[0], v[1]), add2(v[2], v[3])), add2(add2(v[4], v[5]), v[6])); }
+__device__ __forceinline__ u64 sum15p2(const u64 (&v)[Q]) {
+  return add2(add2(add2(add2(v[0], v[1]), add2(v[2], v[3])), add2(add2(v[4], v[5]), add2(v[6], v[7]))),
+              add2(add2(add2(v[8], v[9]), add2(v[10], v[11])), add2(add2(v[12], v[13]), v[14])));
+}
+
+// codon factors of the 9 constrained states at position t from the nucleotide codes of t-2 .. t+2 (gene_pred_hmm_emitter.py:231-263)
+__device__ __forceinline__ void codon_factors_reg(const Args& a, const EmisSmem& sp, int n, int t, int r2, int r1, int c0, int l1, int l2,
+                                                  float (&cod)[9]) {
+  float fl[9], fr[9];
+  if ((c0 | l1 | l2) >= 0) {
+    const float* tp = sp.T5[0][(l1 * 5 + l2) * 5 + c0];
+    const float4 u0 = reinterpret_cast<const float4*>(tp)[0], u1 = reinterpret_cast<const float4*>(tp)[1];
+    fl[0] = u0.x; fl[1] = u0.y; fl[2] = u0.z; fl[3] = u0.w; fl[4] = u1.x; fl[5] = u1.y; fl[6] = u1.z; fl[7] = u1.w; fl[8] = tp[8];
+  } else {
+    float tmp[12];
+    codon_side_soft(sp, 0, nuc_dist(a, n, t), nuc_dist(a, n, t + 1), nuc_dist(a, n, t + 2), tmp);
+#pragma unroll
+    for (int s = 0; s < 9; ++s) fl[s] = tmp[s];
+  }
+  if ((c0 | r1 | r2) >= 0) {
+    const float* tp = sp.T5[1][(r1 * 5 + r2) * 5 + c0];
+    const float4 u0 = reinterpret_cast<const float4*>(tp)[0], u1 = reinterpret_cast<const float4*>(tp)[1];
+    fr[0] = u0.x; fr[1] = u0.y; fr[2] = u0.z; fr[3] = u0.w; fr[4] = u1.x; fr[5] = u1.y; fr[6] = u1.z; fr[7] = u1.w; fr[8] = tp[8];
+  } else {
+    float tmp[12];
+    codon_side_soft(sp, 1, nuc_dist(a, n, t), nuc_dist(a, n, t - 1), nuc_dist(a, n, t - 2), tmp);
+#pragma unroll
+    for (int s = 0; s < 9; ++s) fr[s] = tmp[s];
+  }
+#pragma unroll
+  for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
+}
+
+__global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  FSmem& S = *reinterpret_cast<FSmem*>(smem);
+  float* U = reinterpret_cast<float*>(smem + ((sizeof(FSmem) + 127) / 128) * 128);
+  const int L = a.L, T = a.T, CS = L * QP + 4, P = a.P;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
+  const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
+  const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
+  const int nch = min(G, a.C - c0);
+  const size_t tile = (size_t)n * P + p;
+  const float* Am = a.A + (size_t)m * Q * Q;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  HMM_MARK(cta, 0);
+  HMM_WALL(cta, 14);
+
+  // ---- parameters ----
+  {
+    if (tid < 23) {
+      float aw;
+      if (tid < 7) aw = __ldg(Am + SRC1[tid] * Q + tid);
+      else if (tid < 15) aw = __ldg(Am + PRED[tid - 7] * Q + tid);
+      else aw = __ldg(Am + (tid - 8) * Q + SUCC[tid - 15]);
+      S.Aw[tid] = aw;
+      S.W[tid] = __ldg(Am + ESRC[tid] * Q + EDST[tid]);
+    }
+    {
+      const int c = tid >> 4, slot = tid & 15;   // FT == Q * QP + 16: threads 0..239 fill B as pairs
+      if (c < Q) {
+        const int st = PSTATE[slot];
+        S.sp.B[c][slot] = st >= 0 ? __ldg(a.Bfull + (size_t)m * Q * Q + st * Q + c) : 0.f;
+      }
+    }
+    const float4* tsrc = reinterpret_cast<const float4*>(a.codon5);
+    float4* tdst = reinterpret_cast<float4*>(&S.sp.T5[0][0][0]);
+    for (int i = tid; i < T5_FLOATS / 4; i += FT) tdst[i] = __ldg(tsrc + i);
+  }
+  __syncthreads();
+  HMM_MARK(cta, 1);
+
+  // ---- phase 1: emission + coefficient rows, thread = a run of consecutive positions ----
+  float* Eg = a.Ews + tile * (size_t)G * CS;
+  const int i0 = tid * a.run, i1 = min(npos, i0 + a.run);
+  float keep[QP];
+#pragma unroll
+  for (int j = 0; j < QP; ++j) keep[j] = 0.f;
+  {
+    float eprev[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) eprev[q] = 0.f;
+    if (i0 < i1) {
+      const float* seq = a.inputs + (size_t)n * T * SIN;
+      int code[FRUN + 4];
+#pragma unroll
+      for (int k = 0; k < FRUN + 4; ++k) {
+        const int t = t_lo + i0 - 2 + k;
+        int cv = 4;   // outside the sequence: 1/4 each (kmer.py:27-33)
+        if (k < (i1 - i0) + 4 && t >= 0 && t < T) {
+          const float* pp = seq + (size_t)t * SIN + 12;
+          const float4 u = ldg4(pp), v = ldg4(pp + 4);   // u.w = A flag, v = C,G,T,N flags
+          cv = code_of(u.w, v.x, v.y, v.z, v.w);
+        }
+        code[k] = cv;
+      }
+      const float train = (a.flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
+      const float free_cod = (1.0f / 4096.0f) + train;
+#pragma unroll
+      for (int k = 0; k < FRUN; ++k) {
+        const int i = i0 + k;
+        if (i < i1) {
+          const int t = t_lo + i;
+          float x[QP];
+          {
+            const float4* row = reinterpret_cast<const float4*>(seq + (size_t)t * SIN);
+            const float4 x0 = __ldg(row), x1 = __ldg(row + 1), x2 = __ldg(row + 2), x3 = __ldg(row + 3);
+            x[0] = x0.x; x[1] = x0.y; x[2] = x0.z; x[3] = x0.w; x[4] = x1.x; x[5] = x1.y; x[6] = x1.z; x[7] = x1.w;
+            x[8] = x2.x; x[9] = x2.y; x[10] = x2.z; x[11] = x2.w; x[12] = x3.x; x[13] = x3.y; x[14] = x3.z; x[15] = 0.f;
+          }
+          // class-probability contraction: two states per FFMA2, the class probability as the scalar operand
+          u64 acc[7];
+#pragma unroll
+          for (int q = 0; q < 7; ++q) acc[q] = 0ull;
+#pragma unroll
+          for (int c = 0; c < Q; ++c) {
+            const float4* bp = reinterpret_cast<const float4*>(S.sp.B[c]);
+            const float4 b0 = bp[0], b1 = bp[1], b2 = bp[2], b3 = bp[3];
+            const u64 xb = bc2(x[c]);
+            acc[0] = fma2(xb, pk2(b0.x, b0.y), acc[0]);
+            acc[1] = fma2(xb, pk2(b0.z, b0.w), acc[1]);
+            acc[2] = fma2(xb, pk2(b1.x, b1.y), acc[2]);
+            acc[3] = fma2(xb, pk2(b1.z, b1.w), acc[3]);
+            acc[4] = fma2(xb, pk2(b2.x, b2.y), acc[4]);
+            acc[5] = fma2(xb, pk2(b2.z, b2.w), acc[5]);
+            acc[6] = fma2(xb, pk2(b3.x, b3.y), acc[6]);
+          }
+          float d[QP];
+          upk2(acc[0], d[0], d[1]); d[2] = d[1]; d[3] = d[1];
+          upk2(acc[1], d[4], d[5]); upk2(acc[2], d[6], d[7]); upk2(acc[3], d[8], d[9]);
+          upk2(acc[4], d[10], d[11]); upk2(acc[5], d[12], d[13]); upk2(acc[6], d[14], d[15]);
+          float cod[9];
+          codon_factors_reg(a, S.sp, n, t, code[k], code[k + 1], code[k + 2], code[k + 3], code[k + 4], cod);
+          float e[Q];
+#pragma unroll
+          for (int q = 0; q < Q; ++q) e[q] = d[q] * ((q < 6) ? free_cod : cod[q < 6 ? 0 : q - 6] + train);
+          if (a.hints != nullptr) {
+            const float* h = a.hints + (size_t)n * 2 * Q;
+            if (t == 0) {
+#pragma unroll
+              for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + q);
+            }
+            if (t == T - 1) {
+#pragma unroll
+              for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + Q + q);
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < Q; ++q) e[q] = fmaxf(e[q], kEps);   // max(E, eps), MsaHmmCell.py:87
+          const int ci = divL(a, i), c = c0 + ci;
+          store_row16(Eg + (size_t)ci * CS + (i - ci * L) * QP, e, 0.f);
+          {
+            const int ts = c * L + (c == 0 ? 1 : 0), t1 = min(T, (c + 1) * L) - 1;
+            if (t == ts) store_row16(S.EF[ci], e, 0.f);
+            if (t == t1) store_row16(S.EL[ci], e, 0.f);
+          }
+          float kc[QP];
+          kc[15] = 0.f;
+          if (t == 0) {
+#pragma unroll
+            for (int q = 0; q < Q; ++q) kc[q] = e[q];   // position 0 keeps its emission row (no transition into it)
+          } else {
+#pragma unroll
+            for (int j = 0; j < 7; ++j) kc[j] = e[j] * S.Aw[j];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) kc[7 + q] = e[SUCC[q]] * S.Aw[15 + q];
+            if (k > 0 || i == 0) {
+              // (the tile's first position takes its own pass-state emissions: k2 is never read at a chunk's first position)
+#pragma unroll
+              for (int q = 0; q < 8; ++q) kc[7 + q] *= ((k > 0 ? eprev[q] : e[7 + q]) * S.Aw[7 + q]);
+            }
+          }
+          if (k == 0 && i > 0) {
+#pragma unroll
+            for (int j = 0; j < QP; ++j) keep[j] = kc[j];   // completed behind the barrier with the neighbour's last emissions
+          } else {
+            coef_store(U, i, kc);
+          }
+#pragma unroll
+          for (int q = 0; q < 8; ++q) eprev[q] = e[7 + q];
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 8; q += 4) *reinterpret_cast<float4*>(&S.carry[tid][q]) = make_float4(eprev[q], eprev[q + 1], eprev[q + 2], eprev[q + 3]);
+  }
+  __syncthreads();
+  if (i0 < i1 && i0 > 0) {
+    const float4 u0 = *reinterpret_cast<const float4*>(&S.carry[tid - 1][0]), u1 = *reinterpret_cast<const float4*>(&S.carry[tid - 1][4]);
+    const float ep[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+#pragma unroll
+    for (int q = 0; q < 8; ++q) keep[7 + q] *= (ep[q] * S.Aw[7 + q]);
+    coef_store(U, i0, keep);
+  }
+  __syncthreads();
+  HMM_MARK(cta, 2);
+
+  // ---- phase 2: conditional rows, thread = (chunk, row pair), packed halves = rows ra | rb ----
+  {
+    const int ci = tid >> 3, rp = tid & 7, c = c0 + ci;
+    const int ra = 2 * rp, rb = 2 * rp + 1;   // rb == 15: not a matrix row (stays zero)
+    u64 vec[Q];
+    float smA = 1.f, smB = 1.f;
+    int esA = 0, esB = 0;
+#pragma unroll
+    for (int j = 0; j < Q; ++j) vec[j] = pk2(j == ra ? 1.f : 0.f, j == rb ? 1.f : 0.f);   // chunks beyond the sequence: identity
+    if (c < a.C) {
+      const bool first = (c == 0);
+      const int t0 = c * L, t1 = min(T, t0 + L) - 1, ts = t0 + (first ? 1 : 0);
+      const int ib = ci * L;
+      float initA = 1.f, initB = 1.f;
+      if (first) { initA = coef_at(U, ib, ra); initB = coef_at(U, ib, min(rb, Q - 1)); }   // E_0[row]
+      if (rb >= Q) initB = 0.f;
+      u64 xm[7], ym[8];
+#pragma unroll
+      for (int j = 0; j < 7; ++j) xm[j] = pk2(ra == j ? initA : 0.f, rb == j ? initB : 0.f);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) ym[q] = pk2(ra == 7 + q ? initA : 0.f, rb == 7 + q ? initB : 0.f);
+      if (ts > t1) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j) vec[j] = xm[j];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) vec[7 + q] = ym[q];
+      } else {
+        u64 x[7], xp[7];
+        {
+          float k1[QP];
+          coef_load(U, ib + (ts - t0), k1);
+#pragma unroll
+          for (int j = 0; j < 7; ++j) x[j] = mul2(bc2(k1[j]), xm[SRC1[j]]);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) x[SUCC[q]] = fma2(bc2(S.EF[ci][SUCC[q]] * S.Aw[15 + q]), ym[q], x[SUCC[q]]);
+#pragma unroll
+          for (int j = 0; j < 7; ++j) xp[j] = xm[j];
+        }
+        int cnt = 0;
+#pragma unroll 4
+        for (int t = ts + 1; t <= t1; ++t) {
+          float k[QP];
+          coef_load(U, ib + (t - t0), k);
+          u64 xn[7];
+          xn[0] = fma2(bc2(k[7 + 7]), xp[5], mul2(bc2(k[0]), x[0]));
+          xn[1] = fma2(bc2(k[7 + 1]), xp[4], mul2(bc2(k[1]), x[1]));
+          xn[2] = fma2(bc2(k[7 + 2]), xp[5], mul2(bc2(k[2]), x[2]));
+          xn[3] = fma2(bc2(k[7 + 3]), xp[6], mul2(bc2(k[3]), x[3]));
+          xn[4] = fma2(bc2(k[7 + 4]), xp[1], mul2(bc2(k[4]), x[6]));
+          xn[5] = fma2(bc2(k[7 + 5]), xp[2], fma2(bc2(k[7 + 0]), xp[0], mul2(bc2(k[5]), x[4])));
+          xn[6] = fma2(bc2(k[7 + 6]), xp[3], mul2(bc2(k[6]), x[5]));
+#pragma unroll
+          for (int j = 0; j < 7; ++j) { xp[j] = x[j]; x[j] = xn[j]; }
+          if ((++cnt & 3) == 0) {
+            float sA, sB;
+            upk2(add2(sum7p(x), sum7p(xp)), sA, sB);
+            const int exA = pexp(sA), exB = pexp(sB);
+            const u64 sc = pk2(pow2neg(exA), pow2neg(exB));
+#pragma unroll
+            for (int j = 0; j < 7; ++j) { x[j] = mul2(x[j], sc); xp[j] = mul2(xp[j], sc); }
+            esA += clamp_exp(exA);
+            esB += clamp_exp(exB);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 7; ++j) vec[j] = x[j];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) vec[7 + q] = mul2(bc2(S.EL[ci][7 + q] * S.Aw[7 + q]), xp[PRED[q]]);
+      }
+      float sA, sB;
+      upk2(sum15p2(vec), sA, sB);
+      smA = fmaxf(sA, 1e-37f);
+      smB = fmaxf(sB, 1e-37f);
+      const u64 inv = pk2(__frcp_rn(smA), __frcp_rn(smB));
+#pragma unroll
+      for (int j = 0; j < Q; ++j) vec[j] = mul2(vec[j], inv);
+    }
+    // relative row scales: common power of two = the largest row exponent of the chunk (8 lanes hold its 15 rows)
+    int emax = max(esA + fexp(smA), rb < Q ? esB + fexp(smB) : -100000);
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) emax = max(emax, __shfl_xor_sync(0xffffffffu, emax, o));
+    const float spA = smA * pow2neg(emax - esA);
+    const float spB = rb < Q ? smB * pow2neg(emax - esB) : 0.f;
+    __syncthreads();   // every row is done with the coefficient rows: U becomes the product tree
+    HMM_MARK(cta, 3);
+    float* b = U + (size_t)(G + ci) * MAT;
+    {
+      float va[Q], vb[Q];
+#pragma unroll
+      for (int j = 0; j < Q; ++j) upk2(vec[j], va[j], vb[j]);
+      store_row16(b + ra * QP, va, spA);
+      if (rb < Q) store_row16(b + rb * QP, vb, spB);
+    }
+    __syncwarp();
+    {
+      // row 15: column sums of diag(s') M-hat (columns ra, rb of this thread), exponent in slot 15
+      float cs0 = 0.f, cs1 = 0.f;
+      const int colb = min(rb, Q - 1);
+#pragma unroll
+      for (int i = 0; i < Q; ++i) {
+        const float si = b[i * QP + 15];
+        cs0 = fmaf(si, b[i * QP + ra], cs0);
+        cs1 = fmaf(si, b[i * QP + colb], cs1);
+      }
+      __syncwarp();
+      b[15 * QP + ra] = cs0;
+      b[15 * QP + rb] = rb < Q ? cs1 : __int_as_float(emax);
+    }
+  }
+  __syncthreads();
+  HMM_MARK(cta, 4);
+
+  // ---- phase 3: product tree in heap order (node k = node 2k . node 2k+1, root at 1) ----
+  float* H = U;
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  HMM_MARK(cta, 5);
+
+  // ---- phase 4: publish the tile matrix, wait for the sequence's other tiles, top-level scan, down-sweep ----
+  if (tid < MAT / 4) reinterpret_cast<float4*>(a.Mt + tile * MAT)[tid] = reinterpret_cast<const float4*>(H + MAT)[tid];
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    st_release_u32(a.flg + tile, a.tag);
+  }
+  const bool add_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
+  if (warp == 1) {
+    for (int q = lane; q < P; q += 32) {
+      const unsigned* f = a.flg + (size_t)n * P + q;
+      while (ld_acquire_u32(f) != a.tag) __nanosleep(64);
+    }
+    __syncwarp();
+    float llv = 0.f;
+    const HV bnd = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
+    if (lane == 0 && p == 0 && a.loglik) a.loglik[n] = llv;
+    if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.hef[1] = bnd.e; }
+    else         { S.v.hvr[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.her[1] = bnd.e; }
+    if (lane == 0) S.ll = llv;
+  }
+  __syncthreads();
+  HMM_MARK(cta, 6);
+  {
+    // down-sweep (gene15.cu, finalize_kernel): first half of the warps forward, second half backward
+    const int wpd = FT >> 6;
+    const int dir = warp >= wpd ? 1 : 0;
+    const int wd = warp - dir * wpd;
+    const int row = min(hl, Q - 1);
+    for (int lo = 1; lo < G; lo <<= 1) {
+      for (int k0 = lo + 2 * wd; k0 < 2 * lo; k0 += 2 * wpd) {
+        const int k = k0 + hi;
+        const bool act = k < 2 * lo;
+        const int kc = act ? k : k0;
+        if (dir == 0) {
+          const float v = S.v.hvf[kc][hl];
+          const int e = S.hef[kc];
+          const float* blk = H + (size_t)(2 * kc) * MAT;
+          const float u = (hl < Q) ? v * blk[row * QP + 15] : 0.f;
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float s = half_sum(u);
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) {
+            const float uj = __shfl_sync(0xffffffffu, u, j, 16);
+            const float cc = blk[j * QP + hl];
+            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.v.hvf[2 * k][hl] = v;
+            S.v.hvf[2 * k + 1][hl] = (hl < Q) ? (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.hef[2 * k] = e; S.hef[2 * k + 1] = e + clamp_exp(ex) + Eb; }
+          }
+        } else {
+          const float v = S.v.hvr[kc][hl];
+          const int e = S.her[kc];
+          const float* blk = H + (size_t)(2 * kc + 1) * MAT;
+          const float sp = blk[15 + row * QP];
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float u = (hl < Q) ? v : 0.f;
+          const float s = half_sum((hl < Q) ? blk[15 * QP + hl] * v : 0.f);
+          const float* rp = blk + row * QP;
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < QP; ++j) {
+            const int kk = (hl + j) & 15;
+            const float uj = __shfl_sync(0xffffffffu, u, kk, 16);
+            const float cc = rp[kk];
+            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.v.hvr[2 * k + 1][hl] = v;
+            S.v.hvr[2 * k][hl] = (hl < Q) ? sp * (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.her[2 * k + 1] = e; S.her[2 * k] = e + clamp_exp(ex) + Eb; }
+          }
+        }
+      }
+      if (dir == 0) named_barrier_sync(2, wpd * 32); else named_barrier_sync(3, wpd * 32);
+    }
+  }
+  __syncthreads();   // boundary vectors complete, tree dead: U becomes Y
+  HMM_MARK(cta, 7);
+
+  // ---- phase 5: exact recursions, warp 0 forward, warp 1 backward, lane = chunk; emission rows through the ring ----
+  float* Y = U;
+  if (warp < 2) {
+    const int ci = lane, c = c0 + ci;
+    const bool act = ci < nch;
+    const int t0 = c * L, len = act ? min(L, T - t0) : 0, h = (len + 1) >> 1;
+    const float* Ec = Eg + (size_t)ci * CS;
+    float* ring = &S.ring[warp][0][lane][0];
+    constexpr int RSL = 32 * FRST;   // floats between ring slots
+    float w[NEDGE];
+    load_edges(S.W, w);
+    float* Yc = Y + (size_t)ci * CS;
+    if (warp == 0) {
+      float av[Q];
+      {
+        float tv[QP];
+        load_row16(S.v.hvf[G + ci], tv);
+#pragma unroll
+        for (int j = 0; j < Q; ++j) av[j] = tv[j];
+      }
+      float kap = sum15(av);
+      int nsum = 0;
+      const bool first = (c == 0);
+#pragma unroll
+      for (int k = 0; k < FRING; ++k) {
+        if (k < len) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) cp_async16m(ring + k * RSL + 4 * q, Ec + (size_t)k * QP + 4 * q);
+        }
+        cp_async_commit_m();
+      }
+      for (int ph = 0; ph < 2; ++ph) {
+        const int u_lo = ph == 0 ? 0 : h, u_hi = ph == 0 ? h : len;
+        for (int u = u_lo; u < u_hi; ++u) {
+          float e[QP], R[Q];
+          cp_async_wait_m<FRING - 1>();
+          load_row16(ring + (u & (FRING - 1)) * RSL, e);
+          if (u + FRING < len) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cp_async16m(ring + (u & (FRING - 1)) * RSL + 4 * q, Ec + (size_t)(u + FRING) * QP + 4 * q);
+          }
+          cp_async_commit_m();
+          if (first && u == 0) {
+#pragma unroll
+            for (int j = 0; j < Q; ++j) R[j] = av[j];
+          } else {
+            vec_A(av, w, R);
+          }
+          const float fl = kEps * kap;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) av[j] = e[j] * fmaxf(R[j], fl);
+          const float g = sum15(av);
+          int ex;
+          const float sc = recip_pow2(g, ex);
+          nsum += ex;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) av[j] *= sc;
+          kap = g * sc;
+          if (ph == 0) {
+            store_row16(Yc + u * QP, av, __int_as_float(nsum));
+          } else {
+            float o[QP];
+            load_row16(Yc + u * QP, o);
+            float gm[Q];
+#pragma unroll
+            for (int j = 0; j < Q; ++j) gm[j] = av[j] * o[j];
+            store_row16(Yc + u * QP, gm, 0.f);
+          }
+        }
+        if (ph == 0) named_barrier_sync(1, 64);
+      }
+    } else {
+      float R[Q];
+      {
+        float tv[QP];
+        load_row16(S.v.hvr[G + ci], tv);
+#pragma unroll
+        for (int j = 0; j < Q; ++j) R[j] = tv[j];
+      }
+      float kap = 1.f;
+      int nsum = 0;
+#pragma unroll
+      for (int k = 0; k < FRING; ++k) {
+        if (k < len) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) cp_async16m(ring + k * RSL + 4 * q, Ec + (size_t)(len - 1 - k) * QP + 4 * q);
+        }
+        cp_async_commit_m();
+      }
+      int step = 0;
+      for (int ph = 0; ph < 2; ++ph) {
+        const int u_hi = ph == 0 ? len : h, u_lo = ph == 0 ? h : 0;
+        for (int u = u_hi - 1; u >= u_lo; --u, ++step) {
+          float e[QP], Rf[Q], bq[Q];
+          cp_async_wait_m<FRING - 1>();
+          load_row16(ring + (step & (FRING - 1)) * RSL, e);
+          if (u - FRING >= 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cp_async16m(ring + (step & (FRING - 1)) * RSL + 4 * q, Ec + (size_t)(u - FRING) * QP + 4 * q);
+          }
+          cp_async_commit_m();
+          const float fl = kEps * kap;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) Rf[j] = fmaxf(R[j], fl);
+#pragma unroll
+          for (int j = 0; j < Q; ++j) bq[j] = e[j] * Rf[j];
+          if (ph == 0) {
+            store_row16(Yc + u * QP, Rf, __int_as_float(nsum));
+          } else {
+            float o[QP];
+            load_row16(Yc + u * QP, o);
+            float gm[Q];
+#pragma unroll
+            for (int j = 0; j < Q; ++j) gm[j] = Rf[j] * o[j];
+            store_row16(Yc + u * QP, gm, 0.f);
+          }
+          const float g = sum15(bq);
+          int ex;
+          const float sc = recip_pow2(g, ex);
+          nsum += ex;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) bq[j] *= sc;
+          kap = g * sc;
+          A_vec(bq, w, R);
+        }
+        if (ph == 0) named_barrier_sync(1, 64);
+      }
+    }
+    cp_async_wait_m<0>();
+  }
+  __syncthreads();
+  HMM_MARK(cta, 8);
+
+  // ---- phase 6: log posterior = log g - log sum(g) (+ log-likelihood), warp = 32 consecutive positions, staged ----
+  {
+    const size_t obase = ((size_t)n * T + t_lo) * Q;
+    const float ll_shift = add_ll ? S.ll : 0.f;
+    float* stg = S.stage[warp];
+    constexpr float LN2F = 0.69314718055994531f;
+    for (int ib = warp * 32; ib < npos; ib += FT) {
+      const int i = ib + lane;
+      if (i < npos) {
+        float g[QP];
+        load_row16(Y + tile_row_offset(a, i, CS), g);
+        float z = 0.f;
+#pragma unroll
+        for (int j = 0; j < Q; ++j) { g[j] = fmaxf(g[j], 1e-37f); z += g[j]; }
+        const float lz = __log2f(z);
+#pragma unroll
+        for (int j = 0; j < Q; ++j) stg[lane * Q + j] = fmaf(__log2f(g[j]) - lz, LN2F, ll_shift);
+      }
+      __syncwarp();
+      const int cnt = min(32, npos - ib) * Q;
+      float* dst = a.out_post + obase + (size_t)ib * Q;
+      for (int j = lane; j < cnt; j += 32) dst[j] = stg[j];
+      __syncwarp();
+    }
+  }
+  HMM_MARK(cta, 9);
+  HMM_WALL(cta, 15);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------------------
+enum { SLOT_FUSED = 23 };
+
+// CTAs of the fused kernel that can be resident at once on the current device for chunk length L (0: does not fit)
+int fused_capacity(int L) {
+  static int cache[kMaxDevices][MAX_L + 1] = {};
+  if (L < 1 || L > MAX_L) return 0;
+  const int dev = current_device();
+  {
+    std::lock_guard<std::mutex> lk(state_mutex());
+    if (cache[dev][L] != 0) return cache[dev][L] < 0 ? 0 : cache[dev][L];
+  }
+  const size_t smem = fused_smem_bytes(L);
+  int cap = -1;
+  if (smem <= (size_t)227 * 1024 && ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem) == 0) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_kernel, FT, smem) == cudaSuccess && per_sm > 0)
+      cap = per_sm * device_sm_count();
+    else
+      (void)cudaGetLastError();
+  }
+  std::lock_guard<std::mutex> lk(state_mutex());
+  cache[dev][L] = cap;
+  return cap < 0 ? 0 : cap;
+}
+
+int fused_run_len(int L) { return cdiv(G * L, FT); }
+
+static unsigned next_tag() {
+  static std::atomic<unsigned> tag{(unsigned)std::chrono::steady_clock::now().time_since_epoch().count() | 1u};
+  unsigned t = tag.fetch_add(2654435761u) + 2654435761u;
+  return t ? t : 1u;
+}
+
+int launch_fused(Args a, int NB, cudaStream_t st) {
+  const size_t smem = fused_smem_bytes(a.L);
+  int rc = ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem);
+  if (rc) return rc;
+  a.run = fused_run_len(a.L);
+  a.tag = next_tag();
+  fused_kernel<<<dim3(a.P, NB), FT, smem, st>>>(a);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gene15
+}  // namespace hmm

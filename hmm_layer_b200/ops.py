@@ -56,6 +56,11 @@ def set_tuning(chunk_len=0, finalize_threads=0, dense_path=0):
     _lib.check(_lib.load().hmm_b200_set_tuning(chunk_len, finalize_threads, dense_path))
 
 
+def set_fused(on=True):
+    """Single-launch forward+posterior kernel for posterior-only gene-HMM calls (default on); off = two-kernel path."""
+    _lib.check(_lib.load().hmm_b200_set_fused_mode(0 if on else 1))
+
+
 def profile_enable(on=True):
     _lib.check(_lib.load().hmm_b200_profile_enable(1 if on else 0))
 

@@ -45,6 +45,11 @@ const char* hmm_b200_last_error(void);
  * 1 = CUDA-core step always, 2 = tensor-core step always.  Process-wide; meant for benchmarking and tests. */
 int hmm_b200_set_tuning(int chunk_len, int finalize_threads, int dense_path);
 
+/* Posterior-only calls of hmm_b200_genepred_run take a single-launch kernel whenever every tile of the call can be
+ * resident on the device at once (gene15_fused.cu); mode 1 switches that off (two-kernel path: products + finalize),
+ * mode 0 (default) switches it back on.  Process-wide; meant for benchmarking and tests. */
+int hmm_b200_set_fused_mode(int mode);
+
 /* Per-kernel timing for benchmarks: when enabled, hmm_b200_genepred_run records CUDA events around each of its
  * launches (products, [boundary], finalize); hmm_b200_profile_read waits for the last profiled call and writes up to n
  * durations in milliseconds to the HOST array ms_host, returning how many it wrote. */

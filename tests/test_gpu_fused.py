@@ -1,0 +1,84 @@
+"""The single-launch forward+posterior kernel (csrc/gene15_fused.cu) against the fp64 oracle and against the two-kernel
+path (products_kernel + finalize_kernel) on the same inputs: posterior-only calls take it whenever every tile of the
+call fits the device at once."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import hmm_oracle as O
+from hmm_layer_b200 import ops, synthetic as syn
+from tests.helpers import gene_params, oracle_gene
+from tests.test_gpu_genepred import check_post, dev, run_gpu
+
+pytestmark = pytest.mark.gpu
+
+
+def both_paths(x, A, pi, Bfull, tab, **kw):
+    fused = run_gpu(x, A, pi, Bfull, tab, want_post=True, **kw)
+    ops.set_fused(False)
+    try:
+        two = run_gpu(x, A, pi, Bfull, tab, want_post=True, **kw)
+    finally:
+        ops.set_fused(True)
+    return fused, two
+
+
+@pytest.mark.parametrize("B,T", [(2, 1000), (3, 999), (1, 64), (2, 65), (4, 7), (1, 1), (2, 2), (5, 333), (1, 16), (1, 17), (3, 513),
+                                 (7, 4099), (32, 2000)])
+def test_fused_posterior_matches_oracle_and_two_kernel_path(B, T):
+    x = syn.gene_inputs(1, B, T, seed=170 + T, p_n=0.01)
+    A, pi, Bfull, tab = gene_params(pi_random=True)
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    fused, two = both_paths(x, A, pi, Bfull, tab)
+    check_post(fused, ref)
+    check_post(two, ref)
+    np.testing.assert_allclose(fused["loglik"], two["loglik"], rtol=1e-6)
+    np.testing.assert_allclose(np.exp(fused["post"]), np.exp(two["post"]), atol=2e-5)
+
+
+def test_fused_flags_hints_soft_nucleotides_and_models():
+    B, T = 3, 1203
+    x = syn.gene_inputs(2, B, T, seed=91, p_n=0.02)
+    x[0, 0, 0, 15:] = torch.tensor([0., 0, 0, 0, 1])                 # N at the very first position
+    x[0, 1, T - 1, 15:] = torch.tensor([0., 0, 0, 0, 1])             # and at the last
+    x[1, 2, 600, 15:] = torch.tensor([.1, .2, .3, .4, 0.])           # soft nucleotide rows (neither one-hot nor N)
+    x[1, 0, 4, 15:] = torch.tensor([.25, .25, .5, 0., 0.])
+    x[0, 2, 5 * 37, 15:] = torch.tensor([.5, .5, 0., 0., 0.])        # on a run boundary of the emission phase
+    A, pi, Bfull, tab = gene_params(num_models=2, pi_random=True)
+    hints = np.random.RandomState(3).rand(2, B, 2, 15) + 0.01
+    for kw in (dict(), dict(end_hints=hints), dict(training=True), dict(end_hints=hints, training=True, no_loglik=True)):
+        ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, **kw)
+        fused, two = both_paths(x, A, pi, Bfull, tab, **kw)
+        # no_loglik: the output is log gamma + loglik ~ -1.3e4, one fp32 ulp there is 1e-3 (the reference's fp32 output has
+        # the same resolution), so probabilities recovered from it are only good to ~5e-4
+        nl = bool(kw.get("no_loglik"))
+        check_post(fused, ref, tol_dp=1e-3 if nl else 1e-4)
+        check_post(two, ref, tol_dp=1e-3 if nl else 1e-4)
+        if not nl:
+            np.testing.assert_allclose(np.exp(fused["post"]), np.exp(two["post"]), atol=2e-5)
+
+
+@pytest.mark.parametrize("L", [16, 23, 32, 35, 38])
+def test_fused_chunk_lengths(L):
+    """Every emission-run length (1 .. 5 positions per thread) and partial last tiles / chunks."""
+    x = syn.gene_inputs(1, 3, 2 * 32 * L + 11, seed=7 + L, p_n=0.01)
+    A, pi, Bfull, tab = gene_params()
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    ops.set_tuning(L, 0)
+    try:
+        got = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    finally:
+        ops.set_tuning(0, 0)
+    check_post(got, ref)
+
+
+def test_fused_repeated_calls_are_bit_identical_and_config2_full_size():
+    x = syn.gene_inputs(1, 32, 9999, seed=1234)
+    A, pi, Bfull, tab = gene_params()
+    got = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+    for _ in range(3):
+        again = run_gpu(x, A, pi, Bfull, tab, want_post=True)
+        assert np.array_equal(again["post"], got["post"]) and np.array_equal(again["loglik"], got["loglik"])
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
+    rep = check_post(got, ref)
+    assert rep["argmax_mismatch"] == 0
