@@ -1518,19 +1518,26 @@ static Layout layout_for(int NB, int T, int L) { return layout(NB, cdiv(cdiv(T, 
 // Chunk length of the single-launch path: every tile of the call must be resident at once (a tile waits inside the
 // kernel for the other tiles of its sequence), so the smallest chunk length whose tile count fits the device; 0 = the
 // call does not qualify.  A tuning override (set_tuning) is honoured when it fits.
-constexpr int FUSED_MIN_L = 16, FUSED_MAX_TILES_PER_SEQ = 64;
+constexpr int FUSED_MIN_L = 12, FUSED_MAX_TILES_PER_SEQ = 64;
 static int choose_fused_L(int NB, int T) {
   if (g_fused_mode == 1) return 0;
   static const bool env_off = getenv("HMM_B200_FUSED") && atoi(getenv("HMM_B200_FUSED")) == 0;
   if (env_off) return 0;
-  for (int L = (g_L > 0 ? g_L : FUSED_MIN_L); L <= MAX_L; ++L) {
+  const int sms = num_sms();
+  // cost model (kilo-cycles per tile, fused_phases.py on B200): a tile's phases are latency chains of about 44 + 0.85 L
+  // when its CTA has the SM to itself, 1.36 x that when two tiles share an SM; more tiles than resident CTAs do not fit
+  double best = 1e300;
+  int bestL = 0;
+  for (int L = (g_L > 0 ? g_L : FUSED_MIN_L); L <= (g_L > 0 ? g_L : MAX_L); ++L) {
     const int cap = fused_capacity(L);
-    if (cap <= 0) return 0;          // shared memory: longer chunks do not fit either
+    if (cap <= 0) break;             // shared memory: longer chunks do not fit either
     const int P = cdiv(cdiv(T, L), G);
-    if (P <= FUSED_MAX_TILES_PER_SEQ && (long long)NB * P <= cap) return L;
-    if (g_L > 0) return 0;
+    const long long tiles = (long long)NB * P;
+    if (P > FUSED_MAX_TILES_PER_SEQ || tiles > cap) continue;
+    const double cost = (44.0 + 0.85 * L) * (tiles <= sms ? 1.0 : 1.36);
+    if (cost < best) { best = cost; bestL = L; }
   }
-  return 0;
+  return bestL;
 }
 
 size_t workspace_size(int num_models, int batch, int T) {
@@ -1540,7 +1547,7 @@ size_t workspace_size(int num_models, int batch, int T) {
   size_t best = layout_for(NB, T, choose_L(NB, T, false)).total;
   const size_t b = layout_for(NB, T, choose_L(NB, T, true)).total;
   if (b > best) best = b;
-  for (int L = FUSED_MIN_L; L <= MAX_L; ++L) {   // whichever chunk length the single-launch path may take (mode / tuning may change)
+  for (int L = 4; L <= MAX_L; ++L) {   // whichever chunk length the single-launch path may take (mode / tuning may change)
     const size_t f = layout_for(NB, T, L).total;
     if (f > best) best = f;
   }
@@ -1698,19 +1705,35 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
   HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred: no output requested");
   const int NB = num_models * batch;
   const bool full = out_alpha || out_beta;
-  // posterior (+ log-likelihood) from fp32 inputs: one launch when every tile of the call fits the device at once
+  // posterior (+ log-likelihood) from fp32 inputs: the single-launch kernel when every tile of a launch fits the device
+  // at once; larger batches go as a few back-to-back launches over slices of the sequences (they are independent)
   if (out_post && !full && inputs) {
-    const int Lf = choose_fused_L(NB, T);
-    if (Lf > 0) {
-      set_L(a, Lf);
-      a.top_scan = 2;
-      Layout lf;
-      rc = bind_workspace(a, lf, NB, workspace, workspace_bytes, "genepred");
-      if (rc) return rc;
-      a.out_post = out_post; a.out_alpha = nullptr; a.out_beta = nullptr; a.loglik = loglik;
+    int nb = NB, Lf = choose_fused_L(nb, T);
+    for (int parts = 2; Lf == 0 && parts <= 8 && NB / parts >= 8; ++parts) {
+      nb = cdiv(NB, parts);
+      Lf = choose_fused_L(nb, T);
+    }
+    if (Lf > 0 && (nb == NB || num_models == 1 || batch % nb == 0)) {   // a slice must not straddle two models
       ProfEvents* pe = nullptr;
       if (g_prof) { rc = prof_events(&pe); if (rc) return rc; g_prof_dev = current_device(); pe->n = 0; cudaEventRecord(pe->ev[pe->n++], st); }
-      rc = launch_fused(a, NB, st); if (rc) return rc;
+      for (int n0 = 0; n0 < NB; n0 += nb) {
+        const int cnt = NB - n0 < nb ? NB - n0 : nb;
+        Args s = a;
+        const int m0 = n0 / batch;                 // model of this slice (slices never straddle models, see above)
+        s.inputs = inputs + (size_t)n0 * T * SIN;
+        s.hints = hints ? hints + (size_t)n0 * 2 * Q : nullptr;
+        s.A = A + (size_t)m0 * Q * Q; s.pi = pi + (size_t)m0 * Q; s.Bfull = Bfull + (size_t)m0 * Q * Q;
+        s.num_models = 1; s.batch = cnt;
+        if (nb == NB) { s.A = A; s.pi = pi; s.Bfull = Bfull; s.num_models = num_models; s.batch = batch; }
+        set_L(s, Lf);
+        s.top_scan = 2;
+        Layout lf;
+        rc = bind_workspace(s, lf, cnt, workspace, workspace_bytes, "genepred");
+        if (rc) return rc;
+        s.out_post = out_post + (size_t)n0 * T * Q; s.out_alpha = nullptr; s.out_beta = nullptr;
+        s.loglik = loglik ? loglik + n0 : nullptr;
+        rc = launch_fused(s, cnt, st); if (rc) return rc;
+      }
       if (pe) cudaEventRecord(pe->ev[pe->n++], st);
       return 0;
     }

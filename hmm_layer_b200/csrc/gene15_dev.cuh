@@ -85,9 +85,10 @@ struct Args {
 // ------------------------------------------------------------------------------------------------------------
 // small helpers
 // ------------------------------------------------------------------------------------------------------------
-#define HMM_MARK(base, k) do { if (a.dbg && threadIdx.x == 0) a.dbg[(size_t)(base) * 16 + (k)] = clock64(); } while (0)
+__device__ __forceinline__ long long clock_fenced() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
+#define HMM_MARK(base, k) do { if (a.dbg && threadIdx.x == 0) a.dbg[(size_t)(base) * 16 + (k)] = clock_fenced(); } while (0)
 // wall-clock stamps (globaltimer, ns; comparable across SMs) and the SM id: slot 14 at CTA start, 15 at CTA end, 13 = smid
-__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory"); return t; }
 __device__ __forceinline__ int smid() { int r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
 #define HMM_WALL(base, k) do { if (a.dbg && threadIdx.x == 0) { a.dbg[(size_t)(base) * 16 + (k)] = gtimer(); a.dbg[(size_t)(base) * 16 + 13] = smid(); } } while (0)
 

@@ -3,12 +3,14 @@
 // One 256-thread CTA per tile (G = 32 chunks x L positions of one sequence), two CTAs per SM, all tiles of the call
 // co-resident, so a tile can wait for the other tiles of its sequence inside the kernel:
 //
-//   1 emission      thread = a run of <= 5 consecutive positions, inputs read straight from HBM.  The class-probability
-//                   contraction runs on packed FFMA2 (two states per instruction; B sits in shared memory as state pairs,
-//                   the class probability is the scalar operand), the 3-mer factors are two table rows.  The floored
-//                   emission row goes to the L2-resident workspace (phase 5 streams it back), the coefficient row of the
-//                   two-step recurrence (gene15.cu, K1) to shared memory; a run carries the previous position's pass-state
-//                   emissions in registers, so the whole phase needs ONE barrier (run boundaries are patched behind it).
+//   1 emission      a warp walks its block of positions in steps of 32 consecutive positions (lane = position), inputs
+//                   read straight from HBM / L2 (the tile is prefetched towards L2 at kernel start, the next step's rows
+//                   are in flight during the current one).  The class-probability contraction runs on packed FFMA2 (two
+//                   states per instruction; B sits in shared memory as state pairs, the class probability is the scalar
+//                   operand), the 3-mer factors are two table rows.  The floored emission row goes to the L2-resident
+//                   workspace (phase 5 streams it back), the coefficient row of the two-step recurrence (gene15.cu, K1) to
+//                   shared memory; neighbouring positions' nucleotide codes and pass-state emissions come by shuffles, so
+//                   the whole phase needs ONE barrier (block boundaries are patched behind it).
 //   2 rows          thread = two conditional rows of one chunk's transfer matrix, packed (FFMA2 with the coefficient as
 //                   the scalar operand): 15 FFMA2 per position for two rows.
 //   3 tree          the 5-level product tree of gene15.cu (mma.sync TF32 x 3), kept in shared memory.
@@ -33,8 +35,8 @@ namespace gene15 {
 typedef unsigned long long u64;
 constexpr int FT = 256;        // threads per CTA
 constexpr int FRUN = 5;        // longest run of positions per emission thread (L <= 40)
-constexpr int FRING = 4;       // emission rows in flight per recursion thread
-constexpr int FRST = 20;       // floats between the ring rows of neighbouring lanes (80 B: conflict-free 128-bit reads)
+constexpr int FRING = 6;       // emission rows in flight per recursion thread (an L2 round trip is ~4 recursion steps)
+constexpr int FSCAN = 24;      // tile matrices of one sequence staged in shared memory for the top-level scan
 
 __device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 __device__ __forceinline__ u64 bc2(float x) { u64 r; asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(x)); return r; }
@@ -67,15 +69,17 @@ struct FSmem {
   float EF[G][QP];       // emission at every chunk's first transition step
   float EL[G][QP];       // emission at every chunk's last position
   int hef[HEAP], her[HEAP];
+  unsigned long long bar;   // mbarrier: the codon tables have landed
   float ll;
-  float pad_[3];
+  float pad_[1];
   union {                // phase 1: last pass-state emissions of every run; phases 4-5: boundary vectors of the tree nodes
-    float carry[FT][8];
+    float carry[FT / 32][8];
     struct { float hvf[HEAP][QP]; float hvr[HEAP][QP]; } v;
   };
-  union {                // phase 1: B (as state pairs per class, in sp.B) and the codon tables; 5: emission ring; 6: staging
-    EmisSmem sp;
-    float ring[2][FRING][32][FRST];
+  union {                // phase 1: B (as state pairs per class, in sp.B) and the codon tables; 4: the sequence's tile matrices;
+    EmisSmem sp;         // 5: emission ring (16-byte piece c of lane l's row at piece c ^ ((l >> 1) & 3)); 6: output staging
+    float tiles[FSCAN][MAT];
+    float ring[2][FRING][32][QP];
     float stage[FT / 32][32 * Q];
   };
 };
@@ -87,8 +91,8 @@ __host__ __device__ inline size_t fused_u_floats(int L) {
 }
 __host__ __device__ inline size_t fused_smem_bytes(int L) { return ((sizeof(FSmem) + 127) / 128) * 128 + fused_u_floats(L) * sizeof(float); }
 
-// coefficient rows: row i at 16 i floats, its 16-byte piece c at piece c ^ ((i >> 1) & 3): the run-per-thread stores of
-// phase 1 (lane stride 5 rows) and the row-per-half-warp loads of phase 2 are both conflict-free
+// coefficient rows: row i at 16 i floats, its 16-byte piece c at piece c ^ ((i >> 1) & 3): the row-per-lane stores of
+// phase 1 are conflict-free at the 64-byte row stride (phase 2 reads a row as a broadcast)
 __device__ __forceinline__ void coef_store(float* U, int i, const float (&k)[QP]) {
   float4* b = reinterpret_cast<float4*>(U + (size_t)i * QP);
   const int f = (i >> 1) & 3;
@@ -97,15 +101,34 @@ __device__ __forceinline__ void coef_store(float* U, int i, const float (&k)[QP]
   b[2 ^ f] = make_float4(k[8], k[9], k[10], k[11]);
   b[3 ^ f] = make_float4(k[12], k[13], k[14], k[15]);
 }
-__device__ __forceinline__ void coef_load(const float* U, int i, float (&k)[QP]) {
-  const float4* b = reinterpret_cast<const float4*>(U + (size_t)i * QP);
-  const int f = (i >> 1) & 3;
-  const float4 a0 = b[0 ^ f], a1 = b[1 ^ f], a2 = b[2 ^ f], a3 = b[3 ^ f];
+__device__ __forceinline__ float4 lds4f(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+// ub: address of the coefficient rows in the shared window (128-byte aligned): one shift, one AND and four LOP3 per row
+__device__ __forceinline__ void coef_load(unsigned ub, int i, float (&k)[QP]) {
+  const unsigned rp = ub + ((unsigned)i << 6), f4 = ((unsigned)i << 3) & 0x30u;
+  const float4 a0 = lds4f(rp | (0x00u ^ f4)), a1 = lds4f(rp | (0x10u ^ f4)), a2 = lds4f(rp | (0x20u ^ f4)), a3 = lds4f(rp | (0x30u ^ f4));
   k[0] = a0.x; k[1] = a0.y; k[2] = a0.z; k[3] = a0.w; k[4] = a1.x; k[5] = a1.y; k[6] = a1.z; k[7] = a1.w;
   k[8] = a2.x; k[9] = a2.y; k[10] = a2.z; k[11] = a2.w; k[12] = a3.x; k[13] = a3.y; k[14] = a3.z; k[15] = a3.w;
 }
 __device__ __forceinline__ float coef_at(const float* U, int i, int j) {
   return U[(size_t)i * QP + ((((j >> 2) ^ (i >> 1)) & 3) << 2) + (j & 3)];
+}
+
+// emission ring of one recursion thread: slot s at s * 32 * QP floats from the thread's base, 16-byte piece q at po[q]
+constexpr int FRSL = 32 * QP;
+__device__ __forceinline__ void ring_issue(float* ring, int slot, const int (&po)[4], const float* src) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) cp_async16m(ring + slot * FRSL + po[q], src + 4 * q);
+}
+__device__ __forceinline__ void ring_read(const float* ring, int slot, const int (&po)[4], float (&e)[QP]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4 v = *reinterpret_cast<const float4*>(ring + slot * FRSL + po[q]);
+    e[4 * q] = v.x; e[4 * q + 1] = v.y; e[4 * q + 2] = v.z; e[4 * q + 3] = v.w;
+  }
 }
 
 __device__ __forceinline__ u64 sum7p(const u64 (&v)[7]) { return add2(add2(add2(v[0], v[1]), add2(v[2], v[3])), add2(add2(v[4], v[5]), v[6])); }
@@ -157,8 +180,48 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   HMM_MARK(cta, 0);
   HMM_WALL(cta, 14);
 
-  // ---- parameters ----
+  // ---- the first rows of every warp's block are requested before anything else (HBM latency runs under the parameter
+  // loads).  A warp owns a block of 32 * run consecutive positions and walks it in `run` steps of 32 consecutive positions
+  // (lane = position); a row = 4 pieces of class probabilities (the last holds the A flag) + 1 piece of C,G,T,N flags.
+  // Lanes behind the tile's end recompute its last position (no divergence); their stores are switched off. ----
+  const float* seq = a.inputs + (size_t)n * T * SIN;
+  const int run = a.run, wb = warp * 32 * run;
+  const bool wact = wb < npos;
+  float4 xc[4], xn[4], f3 = make_float4(0.f, 0.f, 0.f, 0.f), f4 = f3;   // f3 / f4: pieces 3 / 4 of the row two steps ahead
+  int code_prev = 4, code_cur = 4, code_next = 4;   // 4: outside the sequence, 1/4 each (kmer.py:27-33)
+  // whether tile position i is a row of this sequence whose code a step of this warp needs
+  auto row_of = [&](int i) { return reinterpret_cast<const float4*>(seq + (size_t)(t_lo + i) * SIN); };
+  if (wact) {
+    {
+      const float4* row = row_of(min(wb + lane, npos - 1));
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xc[q] = __ldg(row + q);
+      f4 = __ldg(row + 4);
+    }
+    if (t_lo + wb + lane < T) code_cur = -2;                  // marks: compute from xc / f4 once they have landed
+    if (t_lo + wb + 32 + lane < T) {                          // step 1 (or, behind the block, the two positions the 3-mer windows reach)
+      const float4* row = row_of(wb + 32 + lane);
+      xn[3] = __ldg(row + 3);
+      f3 = __ldg(row + 4);
+      code_next = -2;
+    }
+    {
+      const int t = t_lo + wb - 32 + lane;   // lanes 30, 31: the two positions in front of the block
+      if (lane >= 30 && t >= 0) {
+        const float* pp = seq + (size_t)t * SIN + 12;
+        const float4 u = ldg4(pp), v = ldg4(pp + 4);
+        code_prev = code_of(u.w, v.x, v.y, v.z, v.w);
+      }
+    }
+  }
+  // ---- parameters: the codon tables by one bulk copy (lands during the first class contraction), the rest gathered ----
   {
+    if (tid == 0) {
+      mbar_init(&S.bar, 1);
+      mbar_init_fence();
+      mbar_expect_tx(&S.bar, (unsigned)(T5_FLOATS * sizeof(float)));
+      bulk_g2s(&S.sp.T5[0][0][0], a.codon5, (unsigned)(T5_FLOATS * sizeof(float)), &S.bar);
+    }
     if (tid < 23) {
       float aw;
       if (tid < 7) aw = __ldg(Am + SRC1[tid] * Q + tid);
@@ -174,52 +237,61 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         S.sp.B[c][slot] = st >= 0 ? __ldg(a.Bfull + (size_t)m * Q * Q + st * Q + c) : 0.f;
       }
     }
-    const float4* tsrc = reinterpret_cast<const float4*>(a.codon5);
-    float4* tdst = reinterpret_cast<float4*>(&S.sp.T5[0][0][0]);
-    for (int i = tid; i < T5_FLOATS / 4; i += FT) tdst[i] = __ldg(tsrc + i);
   }
   __syncthreads();
   HMM_MARK(cta, 1);
 
-  // ---- phase 1: emission + coefficient rows, thread = a run of consecutive positions ----
+  // ---- phase 1: emission + coefficient rows.  Every global and shared access of a step is contiguous across the warp,
+  // the neighbours' nucleotide codes and the previous position's pass-state emissions come by shuffles; the class
+  // probabilities of the next step and the flags of the step after it are in flight while the current step is computed ----
   float* Eg = a.Ews + tile * (size_t)G * CS;
-  const int i0 = tid * a.run, i1 = min(npos, i0 + a.run);
   float keep[QP];
 #pragma unroll
   for (int j = 0; j < QP; ++j) keep[j] = 0.f;
   {
-    float eprev[8];
+    float elast[8];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) eprev[q] = 0.f;
-    if (i0 < i1) {
-      const float* seq = a.inputs + (size_t)n * T * SIN;
-      int code[FRUN + 4];
-#pragma unroll
-      for (int k = 0; k < FRUN + 4; ++k) {
-        const int t = t_lo + i0 - 2 + k;
-        int cv = 4;   // outside the sequence: 1/4 each (kmer.py:27-33)
-        if (k < (i1 - i0) + 4 && t >= 0 && t < T) {
-          const float* pp = seq + (size_t)t * SIN + 12;
-          const float4 u = ldg4(pp), v = ldg4(pp + 4);   // u.w = A flag, v = C,G,T,N flags
-          cv = code_of(u.w, v.x, v.y, v.z, v.w);
-        }
-        code[k] = cv;
-      }
+    for (int q = 0; q < 8; ++q) elast[q] = 0.f;
+    if (wact) {
       const float train = (a.flags & HMM_B200_TRAINING) ? 1e-7f : 0.f;
       const float free_cod = (1.0f / 4096.0f) + train;
+      if (code_cur == -2) code_cur = code_of(xc[3].w, f4.x, f4.y, f4.z, f4.w);
+      if (code_next == -2) code_next = code_of(xn[3].w, f3.x, f3.y, f3.z, f3.w);
+      mbar_wait(&S.bar, 0);   // codon tables
+      for (int k = 0; k < run; ++k) {
+        const int i = wb + 32 * k + lane, ic = min(i, npos - 1), t = t_lo + ic;
+        const bool active = i < npos;
+        // in flight during this step: class probabilities of step k + 1, flags of step k + 2
+        if (k + 1 < run) {
+          const float4* row = row_of(min(i + 32, npos - 1));
 #pragma unroll
-      for (int k = 0; k < FRUN; ++k) {
-        const int i = i0 + k;
-        if (i < i1) {
-          const int t = t_lo + i;
-          float x[QP];
-          {
-            const float4* row = reinterpret_cast<const float4*>(seq + (size_t)t * SIN);
-            const float4 x0 = __ldg(row), x1 = __ldg(row + 1), x2 = __ldg(row + 2), x3 = __ldg(row + 3);
-            x[0] = x0.x; x[1] = x0.y; x[2] = x0.z; x[3] = x0.w; x[4] = x1.x; x[5] = x1.y; x[6] = x1.z; x[7] = x1.w;
-            x[8] = x2.x; x[9] = x2.y; x[10] = x2.z; x[11] = x2.w; x[12] = x3.x; x[13] = x3.y; x[14] = x3.z; x[15] = 0.f;
-          }
-          // class-probability contraction: two states per FFMA2, the class probability as the scalar operand
+          for (int q = 0; q < 3; ++q) xn[q] = __ldg(row + q);
+        }
+        const bool v2 = t_lo + i + 64 < T && (k + 2 < run || (k + 2 == run && lane < 2));
+        if (v2) {
+          const float4* row = row_of(i + 64);
+          f3 = __ldg(row + 3);
+          f4 = __ldg(row + 4);
+        }
+        // nucleotide codes of t-2 .. t+2: lanes l-2 .. l+2 of this step, across the step edges from the previous / next step
+        int cm2, cm1, cp1, cp2;
+        {
+          const int s1 = (lane - 1) & 31, s2 = (lane - 2) & 31, s3 = (lane + 1) & 31, s4 = (lane + 2) & 31;
+          const int a1 = __shfl_sync(0xffffffffu, code_cur, s1), b1 = __shfl_sync(0xffffffffu, code_prev, s1);
+          const int a2 = __shfl_sync(0xffffffffu, code_cur, s2), b2 = __shfl_sync(0xffffffffu, code_prev, s2);
+          const int a3 = __shfl_sync(0xffffffffu, code_cur, s3), b3 = __shfl_sync(0xffffffffu, code_next, s3);
+          const int a4 = __shfl_sync(0xffffffffu, code_cur, s4), b4 = __shfl_sync(0xffffffffu, code_next, s4);
+          cm1 = lane >= 1 ? a1 : b1;
+          cm2 = lane >= 2 ? a2 : b2;
+          cp1 = lane <= 30 ? a3 : b3;
+          cp2 = lane <= 29 ? a4 : b4;
+          if (!active) cm2 = cm1 = cp1 = cp2 = 4;   // lanes behind the tile's end: nobody reads their results
+        }
+        // class-probability contraction: two states per FFMA2, the class probability as the scalar operand
+        float e[Q];
+        {
+          const float x[Q] = {xc[0].x, xc[0].y, xc[0].z, xc[0].w, xc[1].x, xc[1].y, xc[1].z, xc[1].w,
+                              xc[2].x, xc[2].y, xc[2].z, xc[2].w, xc[3].x, xc[3].y, xc[3].z};
           u64 acc[7];
 #pragma unroll
           for (int q = 0; q < 7; ++q) acc[q] = 0ull;
@@ -236,28 +308,40 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
             acc[5] = fma2(xb, pk2(b2.z, b2.w), acc[5]);
             acc[6] = fma2(xb, pk2(b3.x, b3.y), acc[6]);
           }
-          float d[QP];
-          upk2(acc[0], d[0], d[1]); d[2] = d[1]; d[3] = d[1];
-          upk2(acc[1], d[4], d[5]); upk2(acc[2], d[6], d[7]); upk2(acc[3], d[8], d[9]);
-          upk2(acc[4], d[10], d[11]); upk2(acc[5], d[12], d[13]); upk2(acc[6], d[14], d[15]);
+          float d15;
+          upk2(acc[0], e[0], e[1]); e[2] = e[1]; e[3] = e[1];
+          upk2(acc[1], e[4], e[5]); upk2(acc[2], e[6], e[7]); upk2(acc[3], e[8], e[9]);
+          upk2(acc[4], e[10], e[11]); upk2(acc[5], e[12], e[13]); upk2(acc[6], e[14], d15);
+        }
+        {
           float cod[9];
-          codon_factors_reg(a, S.sp, n, t, code[k], code[k + 1], code[k + 2], code[k + 3], code[k + 4], cod);
-          float e[Q];
+          codon_factors_reg(a, S.sp, n, t, cm2, cm1, active ? code_cur : 4, cp1, cp2, cod);
 #pragma unroll
-          for (int q = 0; q < Q; ++q) e[q] = d[q] * ((q < 6) ? free_cod : cod[q < 6 ? 0 : q - 6] + train);
-          if (a.hints != nullptr) {
-            const float* h = a.hints + (size_t)n * 2 * Q;
-            if (t == 0) {
+          for (int q = 0; q < Q; ++q) e[q] *= ((q < 6) ? free_cod : cod[q < 6 ? 0 : q - 6] + train);
+        }
+        if (a.hints != nullptr) {
+          const float* h = a.hints + (size_t)n * 2 * Q;
+          if (t == 0) {
 #pragma unroll
-              for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + q);
-            }
-            if (t == T - 1) {
-#pragma unroll
-              for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + Q + q);
-            }
+            for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + q);
           }
+          if (t == T - 1) {
 #pragma unroll
-          for (int q = 0; q < Q; ++q) e[q] = fmaxf(e[q], kEps);   // max(E, eps), MsaHmmCell.py:87
+            for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + Q + q);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < Q; ++q) e[q] = fmaxf(e[q], kEps);   // max(E, eps), MsaHmmCell.py:87
+        // pass-state emissions of position t-1: the lane below, lane 0 from the previous step's last lane
+        float ep[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float up = __shfl_up_sync(0xffffffffu, e[7 + q], 1);
+          ep[q] = lane >= 1 ? up : elast[q];
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) elast[q] = __shfl_sync(0xffffffffu, e[7 + q], 31);
+        if (active) {
           const int ci = divL(a, i), c = c0 + ci;
           store_row16(Eg + (size_t)ci * CS + (i - ci * L) * QP, e, 0.f);
           {
@@ -267,6 +351,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
           }
           float kc[QP];
           kc[15] = 0.f;
+          const bool head = (k == 0 && lane == 0);   // first position of the block: its predecessor belongs to another warp
           if (t == 0) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) kc[q] = e[q];   // position 0 keeps its emission row (no transition into it)
@@ -275,33 +360,40 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
             for (int j = 0; j < 7; ++j) kc[j] = e[j] * S.Aw[j];
 #pragma unroll
             for (int q = 0; q < 8; ++q) kc[7 + q] = e[SUCC[q]] * S.Aw[15 + q];
-            if (k > 0 || i == 0) {
+            if (!head || i == 0) {
               // (the tile's first position takes its own pass-state emissions: k2 is never read at a chunk's first position)
 #pragma unroll
-              for (int q = 0; q < 8; ++q) kc[7 + q] *= ((k > 0 ? eprev[q] : e[7 + q]) * S.Aw[7 + q]);
+              for (int q = 0; q < 8; ++q) kc[7 + q] *= ((head ? e[7 + q] : ep[q]) * S.Aw[7 + q]);
             }
           }
-          if (k == 0 && i > 0) {
+          if (head && i > 0) {
 #pragma unroll
-            for (int j = 0; j < QP; ++j) keep[j] = kc[j];   // completed behind the barrier with the neighbour's last emissions
+            for (int j = 0; j < QP; ++j) keep[j] = kc[j];   // completed behind the barrier with the previous warp's last emissions
           } else {
             coef_store(U, i, kc);
           }
-#pragma unroll
-          for (int q = 0; q < 8; ++q) eprev[q] = e[7 + q];
         }
+        // rotate: step k + 1 becomes current; its flags (requested a step ago) give the code of the step after it
+#pragma unroll
+        for (int q = 0; q < 4; ++q) xc[q] = xn[q];
+        xn[3] = f3;
+        code_prev = code_cur;
+        code_cur = code_next;
+        code_next = v2 ? code_of(f3.w, f4.x, f4.y, f4.z, f4.w) : 4;
       }
     }
+    if (lane == 0) {
+      *reinterpret_cast<float4*>(&S.carry[warp][0]) = make_float4(elast[0], elast[1], elast[2], elast[3]);
+      *reinterpret_cast<float4*>(&S.carry[warp][4]) = make_float4(elast[4], elast[5], elast[6], elast[7]);
+    }
+    __syncthreads();
+    if (lane == 0 && warp > 0 && wb < npos) {
+      const float4 u0 = *reinterpret_cast<const float4*>(&S.carry[warp - 1][0]), u1 = *reinterpret_cast<const float4*>(&S.carry[warp - 1][4]);
+      const float ep[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
-    for (int q = 0; q < 8; q += 4) *reinterpret_cast<float4*>(&S.carry[tid][q]) = make_float4(eprev[q], eprev[q + 1], eprev[q + 2], eprev[q + 3]);
-  }
-  __syncthreads();
-  if (i0 < i1 && i0 > 0) {
-    const float4 u0 = *reinterpret_cast<const float4*>(&S.carry[tid - 1][0]), u1 = *reinterpret_cast<const float4*>(&S.carry[tid - 1][4]);
-    const float ep[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
-#pragma unroll
-    for (int q = 0; q < 8; ++q) keep[7 + q] *= (ep[q] * S.Aw[7 + q]);
-    coef_store(U, i0, keep);
+      for (int q = 0; q < 8; ++q) keep[7 + q] *= (ep[q] * S.Aw[7 + q]);
+      coef_store(U, wb, keep);
+    }
   }
   __syncthreads();
   HMM_MARK(cta, 2);
@@ -310,6 +402,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   {
     const int ci = tid >> 3, rp = tid & 7, c = c0 + ci;
     const int ra = 2 * rp, rb = 2 * rp + 1;   // rb == 15: not a matrix row (stays zero)
+    const unsigned ub = smem_u32(U);
     u64 vec[Q];
     float smA = 1.f, smB = 1.f;
     int esA = 0, esB = 0;
@@ -336,7 +429,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         u64 x[7], xp[7];
         {
           float k1[QP];
-          coef_load(U, ib + (ts - t0), k1);
+          coef_load(ub, ib + (ts - t0), k1);
 #pragma unroll
           for (int j = 0; j < 7; ++j) x[j] = mul2(bc2(k1[j]), xm[SRC1[j]]);
 #pragma unroll
@@ -348,7 +441,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
 #pragma unroll 4
         for (int t = ts + 1; t <= t1; ++t) {
           float k[QP];
-          coef_load(U, ib + (t - t0), k);
+          coef_load(ub, ib + (t - t0), k);
           u64 xn[7];
           xn[0] = fma2(bc2(k[7 + 7]), xp[5], mul2(bc2(k[0]), x[0]));
           xn[1] = fma2(bc2(k[7 + 1]), xp[4], mul2(bc2(k[1]), x[1]));
@@ -429,6 +522,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   if (tid == 0) {
     __threadfence();
     st_release_u32(a.flg + tile, a.tag);
+    if (a.dbg) a.dbg[(size_t)cta * 16 + 10] = gtimer();
   }
   const bool add_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
   if (warp == 1) {
@@ -436,9 +530,39 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       const unsigned* f = a.flg + (size_t)n * P + q;
       while (ld_acquire_u32(f) != a.tag) __nanosleep(64);
     }
-    __syncwarp();
+    if (a.dbg && lane == 0) a.dbg[(size_t)cta * 16 + 11] = gtimer();
+  }
+  __syncthreads();   // every tile of the sequence has published its matrix
+  const bool staged = P <= FSCAN;
+  if (staged) {
+    // the sequence's tile matrices into shared memory with every load in flight at once: a scan step then costs a
+    // shared-memory matvec instead of an L2 round trip
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + (size_t)n * P * MAT);
+    float4* dst = reinterpret_cast<float4*>(&S.tiles[0][0]);
+    for (int i = tid; i < P * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
+    __syncthreads();
+  }
+  if (warp == 1) {
+    // top-level scan (TotalProbabilityCell.py:30-49 in scaled probability space): lanes 0-15 run pi . M_0 ... M_{P-1}
+    // (snapshot on entering tile p; the end gives the log-likelihood), lanes 16-31 run M_{P-1} ... M_{p+1} . 1
     float llv = 0.f;
-    const HV bnd = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
+    HV bnd;
+    if (staged) {
+      HV h, snap;
+      h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
+      h.e = 0;
+      snap = h;
+      const int steps = hi == 0 ? P : P - 1 - p;
+      for (int it = 0; it < P; ++it) {
+        if (hi == 0 && it == p) snap = h;
+        matvec_raw(S.tiles[hi == 0 ? it : P - 1 - it], hl, hi, it < steps, h);
+      }
+      const float tot = half_sum(h.v);
+      llv = (float)((double)h.e * LN2D + (double)logf(tot));   // meaningful in the forward half only
+      bnd = hi == 0 ? snap : h;
+    } else {
+      bnd = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
+    }
     if (lane == 0 && p == 0 && a.loglik) a.loglik[n] = llv;
     if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.hef[1] = bnd.e; }
     else         { S.v.hvr[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.her[1] = bnd.e; }
@@ -446,6 +570,26 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   }
   __syncthreads();
   HMM_MARK(cta, 6);
+  // recursion threads (warp 0 forward, warp 1 backward, lane = chunk): the first emission rows start their way back from the
+  // workspace now, under the down-sweep
+#ifdef HMM_FUSED_FINE_MARKS
+  if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 8] = clock_fenced();
+#endif
+  const int r_ci = lane, r_c = c0 + r_ci;
+  const int r_len = (warp < 2 && r_ci < nch) ? min(L, T - r_c * L) : 0;
+  const float* r_Ec = Eg + (size_t)r_ci * CS;
+  float* r_ring = &S.ring[warp & 1][0][lane][0];
+  const int r_po[4] = {(0 ^ ((lane >> 1) & 3)) << 2, (1 ^ ((lane >> 1) & 3)) << 2, (2 ^ ((lane >> 1) & 3)) << 2, (3 ^ ((lane >> 1) & 3)) << 2};
+  if (warp < 2) {
+#pragma unroll
+    for (int k = 0; k < FRING; ++k) {
+      if (k < r_len) ring_issue(r_ring, k, r_po, r_Ec + (size_t)(warp == 0 ? k : r_len - 1 - k) * QP);
+      cp_async_commit_m();
+    }
+  }
+#ifdef HMM_FUSED_FINE_MARKS
+  if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 9] = clock_fenced();
+#endif
   {
     // down-sweep (gene15.cu, finalize_kernel): first half of the warps forward, second half backward
     const int wpd = FT >> 6;
@@ -503,6 +647,9 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         }
       }
       if (dir == 0) named_barrier_sync(2, wpd * 32); else named_barrier_sync(3, wpd * 32);
+#ifdef HMM_FUSED_FINE_MARKS
+      if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 31 - __clz(lo)] = clock_fenced();
+#endif
     }
   }
   __syncthreads();   // boundary vectors complete, tree dead: U becomes Y
@@ -511,12 +658,10 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   // ---- phase 5: exact recursions, warp 0 forward, warp 1 backward, lane = chunk; emission rows through the ring ----
   float* Y = U;
   if (warp < 2) {
-    const int ci = lane, c = c0 + ci;
-    const bool act = ci < nch;
-    const int t0 = c * L, len = act ? min(L, T - t0) : 0, h = (len + 1) >> 1;
-    const float* Ec = Eg + (size_t)ci * CS;
-    float* ring = &S.ring[warp][0][lane][0];
-    constexpr int RSL = 32 * FRST;   // floats between ring slots
+    const int ci = r_ci, c = r_c;
+    const int len = r_len, h = (len + 1) >> 1;
+    const float* Ec = r_Ec;
+    float* ring = r_ring;
     float w[NEDGE];
     load_edges(S.W, w);
     float* Yc = Y + (size_t)ci * CS;
@@ -531,25 +676,16 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       float kap = sum15(av);
       int nsum = 0;
       const bool first = (c == 0);
-#pragma unroll
-      for (int k = 0; k < FRING; ++k) {
-        if (k < len) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) cp_async16m(ring + k * RSL + 4 * q, Ec + (size_t)k * QP + 4 * q);
-        }
-        cp_async_commit_m();
-      }
+      int slot = 0;
       for (int ph = 0; ph < 2; ++ph) {
         const int u_lo = ph == 0 ? 0 : h, u_hi = ph == 0 ? h : len;
         for (int u = u_lo; u < u_hi; ++u) {
           float e[QP], R[Q];
           cp_async_wait_m<FRING - 1>();
-          load_row16(ring + (u & (FRING - 1)) * RSL, e);
-          if (u + FRING < len) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) cp_async16m(ring + (u & (FRING - 1)) * RSL + 4 * q, Ec + (size_t)(u + FRING) * QP + 4 * q);
-          }
+          ring_read(ring, slot, r_po, e);
+          if (u + FRING < len) ring_issue(ring, slot, r_po, Ec + (size_t)(u + FRING) * QP);
           cp_async_commit_m();
+          slot = slot + 1 == FRING ? 0 : slot + 1;
           if (first && u == 0) {
 #pragma unroll
             for (int j = 0; j < Q; ++j) R[j] = av[j];
@@ -589,26 +725,16 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       }
       float kap = 1.f;
       int nsum = 0;
-#pragma unroll
-      for (int k = 0; k < FRING; ++k) {
-        if (k < len) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) cp_async16m(ring + k * RSL + 4 * q, Ec + (size_t)(len - 1 - k) * QP + 4 * q);
-        }
-        cp_async_commit_m();
-      }
-      int step = 0;
+      int slot = 0;
       for (int ph = 0; ph < 2; ++ph) {
         const int u_hi = ph == 0 ? len : h, u_lo = ph == 0 ? h : 0;
-        for (int u = u_hi - 1; u >= u_lo; --u, ++step) {
+        for (int u = u_hi - 1; u >= u_lo; --u) {
           float e[QP], Rf[Q], bq[Q];
           cp_async_wait_m<FRING - 1>();
-          load_row16(ring + (step & (FRING - 1)) * RSL, e);
-          if (u - FRING >= 0) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) cp_async16m(ring + (step & (FRING - 1)) * RSL + 4 * q, Ec + (size_t)(u - FRING) * QP + 4 * q);
-          }
+          ring_read(ring, slot, r_po, e);
+          if (u - FRING >= 0) ring_issue(ring, slot, r_po, Ec + (size_t)(u - FRING) * QP);
           cp_async_commit_m();
+          slot = slot + 1 == FRING ? 0 : slot + 1;
           const float fl = kEps * kap;
 #pragma unroll
           for (int j = 0; j < Q; ++j) Rf[j] = fmaxf(R[j], fl);

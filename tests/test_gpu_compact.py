@@ -30,7 +30,15 @@ def test_compact_equals_fp32_path(B, T):
     assert cls16.dtype == torch.bfloat16 and codes.dtype == torch.uint8 and int(codes.max()) <= 4
     xr = expand(cls16, codes)
     A, pi, Bfull, tab = [dev(v) for v in gene_params()]
-    ref = ops.genepred_run(xr.cuda(), A, pi, Bfull, tab, want_post=True, want_alpha=(T < 5000), want_beta=(T < 5000))
+    # bit-identity holds against the kernels the compact format shares (products + finalize); posterior-only fp32 calls
+    # normally take the single-launch kernel, whose arithmetic order differs in the last bits
+    ops.set_fused(False)
+    try:
+        ref = ops.genepred_run(xr.cuda(), A, pi, Bfull, tab, want_post=True, want_alpha=(T < 5000), want_beta=(T < 5000))
+        host_ref = ops.genepred_run_host(xr.pin_memory(), A, pi, Bfull, tab, want_post=True)
+    finally:
+        ops.set_fused(True)
+    fused = ops.genepred_run(xr.cuda(), A, pi, Bfull, tab, want_post=True)
     got = ops.genepred_run_compact(cls16.cuda(), codes.cuda(), A, pi, Bfull, tab, want_post=True, want_alpha=(T < 5000),
                                    want_beta=(T < 5000))
     host = ops.genepred_run_compact(cls16.pin_memory(), codes.pin_memory(), A, pi, Bfull, tab, want_post=True)
@@ -38,10 +46,11 @@ def test_compact_equals_fp32_path(B, T):
     for key in ref:
         assert torch.equal(ref[key], got[key]), key
     # the host path cuts the batch into slices (its own chunk length), so its twin is the fp32 HOST path
-    host_ref = ops.genepred_run_host(xr.pin_memory(), A, pi, Bfull, tab, want_post=True)
     assert not host["post"].is_cuda
     assert torch.equal(host["post"], host_ref["post"]) and torch.equal(host["loglik"], host_ref["loglik"])
     assert torch.allclose(host["post"].exp(), ref["post"].cpu().exp(), atol=2e-5)
+    assert torch.allclose(fused["post"].exp(), ref["post"].exp(), atol=2e-5)
+    assert torch.allclose(fused["loglik"], ref["loglik"], rtol=1e-6)
 
 
 def test_compact_against_oracle_and_rejects_soft_rows():
