@@ -370,6 +370,50 @@ def run_config4(args, rank, world, local):
         dist.destroy_process_group()
 
 
+def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None):
+    """Device-resident forward+posterior of ONE sequence of T positions cut into `world` contiguous shards (one per rank;
+    world == 1: the chunked scan on one GPU).  Returns (ms per step: max over ranks, log-likelihood, launches per step,
+    name of the exchange).  Must be called by every rank of the group."""
+    import torch.distributed as dist
+    from hmm_layer_b200 import ops, sharded, synthetic as syn
+    A, pi, Bfull, codon = params
+    full = syn.gene_inputs(1, 1, T, seed=1234)                       # same sequence on every rank (same seed)
+    shard, halo, off, tot = sharded.slice_with_halo(full, rank, world)
+    del full
+    if nbuf is None:                                                 # rotating shard copies so that a pass does not find its inputs in L2
+        nbuf = max(2, min(8, int(2 * 126e6 * world / (140.0 * T)) + 1))
+    xs = [shard.to(dev).clone() for _ in range(nbuf)]
+    halo_d = halo.to(dev)
+    ctx = sharded.ShardContext(xs[0], halo_d, off, tot, A, pi, Bfull, codon) if world > 1 else None
+
+    def step(i):
+        if world == 1:
+            return ops.genepred_run(xs[i % nbuf], A, pi, Bfull, codon, want_post=True)
+        return ctx.run(xs[i % nbuf], want_post=True)
+
+    for i in range(warm):
+        r = step(i)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(steps):
+        r = step(i)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ll = float(r["loglik"][0, 0])
+    launches = 1 if world == 1 else ctx.launches_per_step
+    how = "none (one GPU)" if world == 1 else ctx.exchange
+    del xs
+    return float(t.item()), ll, launches, how
+
+
 def run_config5(args, rank, world, local):
     """Secondary line (--config 5): BASELINE config 5, ONE 1 Mbp sequence, 15-state gene HMM, forward+posterior.
     N = 1: the chunked scan on one GPU.  N > 1: the sequence is cut into N contiguous shards (hmm_layer_b200/sharded.py),

@@ -575,6 +575,155 @@ __global__ void __launch_bounds__(32) shard_boundary_kernel(const float* __restr
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// K_X: sequence sharding with the exchange inside the kernels (peer memory over NVLink).  Two kernels replace
+// group_reduce + boundary(mode 1) + [NCCL all-gather] + shard_boundary + boundary + group_down:
+//   shard_product_kernel  one CTA per 32 tile matrices: group product (tensor-core tree, as group_reduce_kernel); the
+//                         last CTA of a sequence multiplies the group matrices to the shard's block and stores it --
+//                         with a step tag -- into the block table of EVERY rank (its own included).
+//   shard_scan_kernel     one CTA per 32 tiles: waits for the tagged blocks of all ranks (ld.acquire.sys on its own
+//                         flags), folds the ranks in front / behind (TotalProbabilityCell.py:30-49 across ranks), the
+//                         groups in front / behind, and replays its own tiles: boundary vectors of every tile; the
+//                         log-likelihood of the whole sequence comes out of the forward fold over all ranks.
+// ------------------------------------------------------------------------------------------------------------
+constexpr int MAX_PEERS = 16;
+struct Peers {
+  float* blocks[MAX_PEERS];      // block table of every rank: [2][world][NB][256] (two step parities)
+  unsigned* flags[MAX_PEERS];    // flag table of every rank:  [2][world][NB]
+  int rank, world;
+  unsigned tag;                  // step number (same on every rank); parity selects the table half
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(K1_THREADS) shard_product_kernel(const Args a, float* __restrict__ Gt, const Peers pr,
+                                                                   float* __restrict__ block_out) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* H = reinterpret_cast<float*>(smem);   // heap order: leaves [G, 2G), root at 1
+  __shared__ unsigned s_last;
+  const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, NB = gridDim.y, tid = threadIdx.x;
+  const int nb = min(G, P - g * G);
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+    for (int i = tid; i < nb * (MAT / 4); i += K1_THREADS) dst[i] = __ldg(src + i);
+    for (int b = nb + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+  }
+  __syncthreads();
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  if (PG > 1) {
+    float4* out = reinterpret_cast<float4*>(Gt + ((size_t)n * PG + g) * MAT);
+    for (int i = tid; i < MAT / 4; i += K1_THREADS) out[i] = reinterpret_cast<const float4*>(H + MAT)[i];
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      const unsigned done = atomicAdd(a.cnt + n, 1u);
+      s_last = (done == (unsigned)PG - 1u) ? 1u : 0u;
+      if (s_last) { a.cnt[n] = 0u; __threadfence(); }   // left at zero for the next call
+    }
+    __syncthreads();
+    if (!s_last) return;
+    const float4* src = reinterpret_cast<const float4*>(Gt + (size_t)n * PG * MAT);
+    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+    for (int i = tid; i < PG * (MAT / 4); i += K1_THREADS) dst[i] = __ldcg(src + i);
+    for (int b = PG + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+    __syncthreads();
+    for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  }
+  // the shard's block: to the caller's buffer (NCCL route) or into every rank's table (peer stores over NVLink)
+  const float4* root = reinterpret_cast<const float4*>(H + MAT);
+  if (block_out != nullptr) {
+    for (int i = tid; i < MAT / 4; i += K1_THREADS) reinterpret_cast<float4*>(block_out + (size_t)n * MAT)[i] = root[i];
+  }
+  if (pr.world > 0) {
+    const size_t half = (size_t)(pr.tag & 1u) * pr.world * NB;
+    for (int i = tid; i < pr.world * (MAT / 4); i += K1_THREADS) {
+      const int r = i / (MAT / 4), j = i - r * (MAT / 4);
+      reinterpret_cast<float4*>(pr.blocks[r] + (half + (size_t)pr.rank * NB + n) * MAT)[j] = root[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < pr.world) st_release_sys_u32(pr.flags[tid] + half + (size_t)pr.rank * NB + n, pr.tag);
+  }
+}
+
+struct XSmem {
+  float rb[MAX_PEERS][MAT];   // the ranks' blocks
+  float gm[G][MAT];           // this sequence's group matrices
+  float tm[G][MAT];           // this group's tile matrices
+};
+
+__global__ void __launch_bounds__(256) shard_scan_kernel(const Args a, const float* __restrict__ Gt, const float* __restrict__ blocks,
+                                                         const unsigned* __restrict__ flags, int rank, int world, unsigned tag,
+                                                         float* __restrict__ loglik) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  XSmem& S = *reinterpret_cast<XSmem*>(smem);
+  const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, NB = gridDim.y, m = n / a.batch;
+  const int tid = threadIdx.x, lane = tid & 31, hl = lane & 15, hi = lane >> 4;
+  const int nb = min(G, P - g * G);
+  // local data first (they do not depend on the other ranks), then the wait, then the ranks' blocks
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+    for (int i = tid; i < nb * (MAT / 4); i += 256) cp_async16(reinterpret_cast<float4*>(&S.tm[0][0]) + i, src + i);
+    if (PG > 1) {
+      const float4* gs = reinterpret_cast<const float4*>(Gt + (size_t)n * PG * MAT);
+      for (int i = tid; i < PG * (MAT / 4); i += 256) cp_async16(reinterpret_cast<float4*>(&S.gm[0][0]) + i, gs + i);
+    }
+    cp_async_commit();
+  }
+  if (flags != nullptr && tid < world) {
+    const unsigned* f = flags + (size_t)tid * NB + n;
+    while (ld_acquire_sys_u32(f) != tag) __nanosleep(100);
+  }
+  __syncthreads();
+  for (int i = tid; i < world * (MAT / 4); i += 256) {
+    const int r = i / (MAT / 4), j = i - r * (MAT / 4);
+    reinterpret_cast<float4*>(&S.rb[r][0])[j] = __ldcg(reinterpret_cast<const float4*>(blocks + ((size_t)r * NB + n) * MAT) + j);
+  }
+  cp_async_wait_all();
+  __syncthreads();
+  if (tid >= 32) return;
+  // lanes 0-15: forward fold (row vector), lanes 16-31: backward fold (column vector); the shuffles are warp-wide, so both
+  // halves run every loop to the longer trip count and commit only their own steps
+  HV h;
+  h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
+  h.e = 0;
+  HV mine = h;                       // forward: entering this rank's shard
+  for (int it = 0; it < world; ++it) {
+    if (hi == 0 && it == rank) mine = h;
+    const int s = hi == 0 ? it : world - 1 - it;
+    matvec_raw(S.rb[s], hl, hi, hi == 0 ? true : s > rank, h);
+  }
+  {
+    const float tot = half_sum(h.v);   // (warp-wide shuffle: both halves)
+    if (g == 0 && lane == 0) {
+      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+      a.llws[n] = ll;
+      if (loglik) loglik[n] = ll;
+    }
+    if (hi == 0) h = mine;
+  }
+  if (PG > 1) {
+    for (int it = 0; it < PG; ++it) {
+      const int s = hi == 0 ? it : PG - 1 - it;
+      matvec_raw(S.gm[s], hl, hi, hi == 0 ? s < g : s > g, h);
+    }
+  }
+  float* vout = (hi == 0 ? a.bvf : a.bvr) + ((size_t)n * P + (size_t)g * G) * QP;
+  for (int it = 0; it < nb; ++it) {
+    const int s = hi == 0 ? it : nb - 1 - it;
+    vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+    matvec_raw(S.tm[s], hl, hi, true, h);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // K2: boundary vectors of every chunk, exact in-chunk recursions, outputs
 // ------------------------------------------------------------------------------------------------------------
 struct K2Smem {
@@ -1970,6 +2119,72 @@ int shard_finalize(const float* inputs, int num_models, int batch, int T, int se
   return 0;
 }
 
+// ---- sequence sharding with the exchange inside the kernels (peer memory): 4 launches per step --------------------
+// peer_blocks / peer_flags: `world` device pointers each (host arrays), the block / flag tables of every rank in rank
+// order, mapped into this process (CUDA IPC or symmetric memory); NULL = no peer stores: the block goes to block_out and
+// the caller gathers (NCCL).  `tag` = step counter, the same on every rank, never 0.
+int shard_reduce_x(const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total, const float* halo,
+                   const float* A, const float* pi, const float* Bfull, const float* codon5, const float* hints, unsigned flags,
+                   float* block_out, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank,
+                   int world, unsigned tag, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  Layout l;
+  int rc = shard_args(a, l, inputs, num_models, batch, T, seq_off, seq_total, halo, A, pi, Bfull, codon5, hints, flags, workspace,
+                      workspace_bytes);
+  if (rc) return rc;
+  HMM_REQUIRE(block_out || peer_blocks, "genepred shard_reduce_x: neither an output block nor peer tables");
+  HMM_REQUIRE(!peer_blocks || (peer_flags && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world && tag != 0),
+              "genepred shard_reduce_x: bad peer tables (world %d, rank %d, tag %u)", world, rank, tag);
+  const int NB = num_models * batch, PG = cdiv(a.P, G);
+  HMM_REQUIRE(PG <= G, "genepred shard_reduce_x: shard too long (%d tiles; at most %d)", a.P, G * G);
+  Peers pr{};
+  if (peer_blocks) {
+    for (int r = 0; r < world; ++r) {
+      pr.blocks[r] = reinterpret_cast<float*>(static_cast<uintptr_t>(peer_blocks[r]));
+      pr.flags[r] = reinterpret_cast<unsigned*>(static_cast<uintptr_t>(peer_flags[r]));
+    }
+    pr.rank = rank; pr.world = world; pr.tag = tag;
+  }
+  rc = launch_products(a, NB, st); if (rc) return rc;
+  const size_t smg = (size_t)HEAP * MAT * sizeof(float);
+  rc = ensure_dynamic_smem(shard_product_kernel, 14, smg); if (rc) return rc;
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  shard_product_kernel<<<dim3(PG, NB), K1_THREADS, smg, st>>>(a, reinterpret_cast<float*>(ws + l.Gt), pr, block_out);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// all_blocks: (world, NB, 256) -- this rank's block table half for `tag` (peer route; then block_flags = the matching
+// flag table half) or the NCCL-gathered blocks (block_flags NULL: nothing to wait for)
+int shard_finalize_x(const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total, const float* halo,
+                     const float* A, const float* pi, const float* Bfull, const float* codon5, const float* hints, unsigned flags,
+                     const float* all_blocks, const unsigned* block_flags, int rank, int world, unsigned tag, float* out_post,
+                     float* out_alpha, float* out_beta, float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  Layout l;
+  int rc = shard_args(a, l, inputs, num_models, batch, T, seq_off, seq_total, halo, A, pi, Bfull, codon5, hints, flags, workspace,
+                      workspace_bytes);
+  if (rc) return rc;
+  HMM_REQUIRE(all_blocks && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world, "genepred shard_finalize_x: bad rank %d of %d", rank, world);
+  HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred shard_finalize_x: no output requested");
+  const int NB = num_models * batch, PG = cdiv(a.P, G);
+  HMM_REQUIRE(PG <= G, "genepred shard_finalize_x: shard too long (%d tiles; at most %d)", a.P, G * G);
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  rc = ensure_dynamic_smem(shard_scan_kernel, 15, sizeof(XSmem)); if (rc) return rc;
+  a.ll_external = 1;
+  shard_scan_kernel<<<dim3(PG, NB), 256, sizeof(XSmem), st>>>(a, reinterpret_cast<const float*>(ws + l.Gt), all_blocks, block_flags, rank,
+                                                              world, tag, loglik);
+  a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = nullptr;
+  if (out_post || out_alpha || out_beta) {
+    const bool full = out_alpha || out_beta;
+    const size_t sm2 = k2_smem_bytes(a.L, full);
+    rc = full ? set_smem(finalize_kernel<true>, SLOT_K2F, sm2) : set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc;
+    rc = launch_finalize(a, NB, full, sm2, st, true); if (rc) return rc;
+  }
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 int emission(const float* inputs, int num_models, int batch, int T, const float* Bfull, const float* codon5,
              const float* hints, unsigned flags, float* out_E, cudaStream_t st) {
   Args a{};
@@ -2184,6 +2399,26 @@ int hmm_b200_genepred_shard_finalize(const float* inputs, int num_models, int ba
   return hmm::gene15::shard_finalize(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
                                      flags, all_blocks, rank, world, out_post, out_alpha, out_beta, loglik, workspace,
                                      workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_shard_reduce_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                     const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                     const float* end_hints, unsigned flags, float* block_out,
+                                     const unsigned long long* peer_block_tables, const unsigned long long* peer_flag_tables,
+                                     int rank, int world, unsigned step_tag, void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::gene15::shard_reduce_x(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
+                                     flags, block_out, peer_block_tables, peer_flag_tables, rank, world, step_tag, workspace,
+                                     workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_shard_finalize_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                       const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                       const float* end_hints, unsigned flags, const float* all_blocks, const unsigned* block_flags,
+                                       int rank, int world, unsigned step_tag, float* out_post, float* out_alpha, float* out_beta,
+                                       float* loglik, void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::gene15::shard_finalize_x(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
+                                       flags, all_blocks, block_flags, rank, world, step_tag, out_post, out_alpha, out_beta, loglik,
+                                       workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -395,6 +395,42 @@ def genepred_shard_finalize(inputs, halo, seq_off, seq_total, A, pi, Bfull, codo
     return res
 
 
+def genepred_shard_reduce_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, workspace, step_tag, block_out=None,
+                            peer_blocks=None, peer_flags=None, rank=0, world=0, end_hints=None, training=False):
+    """Step 1 with the exchange inside the kernel (include/hmm_b200.h): products + shard product; the block goes into
+    every rank's table (`peer_blocks` / `peer_flags`: ctypes arrays of device pointers in rank order) and / or to
+    `block_out` (k*B,256).  `workspace`: a ZEROED uint8 tensor of hmm_b200_genepred_workspace_size bytes, kept across steps."""
+    lib = _lib.load()
+    k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints = _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints)
+    with torch.cuda.device(inputs.device):
+        _lib.check(lib.hmm_b200_genepred_shard_reduce_x(
+            _ptr(inputs), k, B, T, seq_off, seq_total, _ptr(halo), _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+            TRAINING if training else 0, _ptr(block_out), peer_blocks, peer_flags, rank, world, step_tag,
+            _ptr(workspace), workspace.numel(), _stream()))
+
+
+def genepred_shard_finalize_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, all_blocks, block_flags, rank, world,
+                              step_tag, workspace, end_hints=None, training=False, no_loglik=False, want_post=True,
+                              want_alpha=False, want_beta=False, out=None):
+    """Step 3 of the same: all_blocks (world, k*B, 256) = this rank's own table half of the step (then block_flags = the
+    matching flag half, waited for inside the kernel) or NCCL-gathered blocks (block_flags=None)."""
+    lib = _lib.load()
+    k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints = _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints)
+    dev = inputs.device
+    with torch.cuda.device(dev):
+        res, out = {}, out or {}
+        for name, want in (("post", want_post), ("alpha", want_alpha), ("beta", want_beta)):
+            if want:
+                res[name] = out.get(name) if out.get(name) is not None else torch.empty((k, B, T, 15), dtype=torch.float32, device=dev)
+        res["loglik"] = out.get("loglik") if out.get("loglik") is not None else torch.empty((k, B), dtype=torch.float32, device=dev)
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        _lib.check(lib.hmm_b200_genepred_shard_finalize_x(
+            _ptr(inputs), k, B, T, seq_off, seq_total, _ptr(halo), _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+            flags, _ptr(all_blocks), _ptr(block_flags), rank, world, step_tag, _ptr(res.get("post")), _ptr(res.get("alpha")),
+            _ptr(res.get("beta")), _ptr(res["loglik"]), _ptr(workspace), workspace.numel(), _stream()))
+    return res
+
+
 def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
     lib = _lib.load()
     if inputs.dim() != 4 or inputs.shape[-1] != 20:

@@ -73,6 +73,75 @@ def sequence_sharded_run(shard, halo, seq_off, seq_total, A, pi, Bfull, codon, g
                                        want_alpha=want_alpha, want_beta=want_beta)
 
 
+class ShardContext:
+    """Persistent state of a rank for repeated sequence-sharded evaluations of one shard shape: the zeroed workspace, the
+    step counter and -- when the ranks' devices can map each other's memory (torch symmetric memory: CUDA VMM handles
+    over NVLink) -- the block / flag tables every rank's kernels store into directly.  4 launches per step, no
+    collective call on the data path; without peer mapping the blocks travel by ONE NCCL all-gather between the two
+    halves (5 launches).  `run` must be called by every rank of the group, in lockstep."""
+
+    def __init__(self, shard, halo, seq_off, seq_total, A, pi, Bfull, codon, group=None, use_peer_memory=True):
+        import ctypes
+        from . import _lib
+        if not dist.is_initialized():
+            raise RuntimeError("ShardContext needs an initialised torch.distributed process group")
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.halo, self.seq_off, self.seq_total = halo, seq_off, seq_total
+        self.params = (A, pi, Bfull, ops._codon5(codon))
+        k, B, T, _ = shard.shape
+        self.NB, dev = k * B, shard.device
+        self.ws = torch.zeros(max(_lib.load().hmm_b200_genepred_workspace_size(k, B, T), 256), dtype=torch.uint8, device=dev)
+        self.tag = 0
+        self.peer_blocks = self.peer_flags = None
+        n_blk, n_flg = 2 * self.world * self.NB * 256, 2 * self.world * self.NB
+        self.n_blk = n_blk
+        self.exchange = "NCCL all_gather_into_tensor (1 KB per rank and sequence) between the two kernel pairs"
+        self.launches_per_step = 5
+        if use_peer_memory and self.world > 1:
+            try:
+                import torch.distributed._symmetric_memory as symm
+                gname = (group or dist.group.WORLD).group_name
+                # one allocation: [blocks: 2 x world x NB x 256 fp32][flags: 2 x world x NB u32], zero-filled
+                self.table = symm.empty(n_blk + n_flg, dtype=torch.float32, device=dev)
+                self.table.zero_()
+                hdl = symm.rendezvous(self.table, gname)
+                ptrs = [int(p) for p in hdl.buffer_ptrs]
+                arr = ctypes.c_ulonglong * self.world
+                self.peer_blocks = arr(*ptrs)
+                self.peer_flags = arr(*[p + 4 * n_blk for p in ptrs])
+                self._hdl = hdl
+                torch.cuda.synchronize(dev)
+                dist.barrier(group)            # every rank's table is zero before anybody stores into it
+                self.exchange = "peer stores over NVLink into symmetric memory, inside the kernels (no collective call)"
+                self.launches_per_step = 4
+            except Exception as e:             # no peer mapping on this system: the NCCL route
+                self.peer_blocks = self.peer_flags = None
+                self.exchange += f" [peer memory unavailable: {type(e).__name__}: {e}]"
+        if self.peer_blocks is None:
+            self.block = torch.empty((self.NB, 256), dtype=torch.float32, device=dev)
+
+    def run(self, shard, end_hints=None, training=False, no_loglik=False, want_post=True, want_alpha=False, want_beta=False, out=None):
+        A, pi, Bfull, codon = self.params
+        self.tag += 1
+        tag = self.tag
+        if self.peer_blocks is not None:
+            ops.genepred_shard_reduce_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
+                                        peer_blocks=self.peer_blocks, peer_flags=self.peer_flags, rank=self.rank, world=self.world,
+                                        end_hints=end_hints, training=training)
+            half = (tag & 1) * self.world * self.NB
+            blocks = self.table[half * 256:(half + self.world * self.NB) * 256].view(self.world, self.NB, 256)
+            flags = self.table[self.n_blk + half:self.n_blk + half + self.world * self.NB].view(torch.int32)
+        else:
+            ops.genepred_shard_reduce_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
+                                        block_out=self.block, end_hints=end_hints, training=training)
+            blocks, flags = all_gather_blocks(self.block, self.group), None
+        return ops.genepred_shard_finalize_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, blocks, flags,
+                                             self.rank, self.world, tag, self.ws, end_hints=end_hints, training=training,
+                                             no_loglik=no_loglik, want_post=want_post, want_alpha=want_alpha, want_beta=want_beta,
+                                             out=out)
+
+
 def sequence_sharded_run_local(shards, A, pi, Bfull, codon, **kw):
     """Single-process form (tests, one GPU): `shards` = [(shard, halo, seq_off, seq_total)] for every virtual rank, all
     on this device; the all-gather is a stack.  Same kernels, same order of operations as the multi-rank path."""

@@ -266,6 +266,29 @@ int hmm_b200_cell_step(const float* E_t, const float* scaled, const float* logli
                        int num_models, int n, int qc, int q, int reverse, int init,
                        float* out, float* new_scaled, float* new_loglik, void* stream);
 
+/* The same three steps with the exchange INSIDE the kernels (peer memory over NVLink) and the boundary machinery folded
+ * into two kernels: 4 launches per step (products, shard product + peer stores, wait + cross-rank / cross-group fold +
+ * tile replay, finalize) instead of 7 launches around an NCCL all-gather.
+ *   peer_block_tables / peer_flag_tables: HOST arrays of `world` device pointers, the block table (float [2][world][NB][256])
+ *     and flag table (uint32 [2][world][NB]) of every rank in rank order, all mapped into this process (CUDA IPC /
+ *     torch symmetric memory); the tables must be zero before the first step.  NULL: no peer stores -- the block goes to
+ *     block_out and the caller gathers it (e.g. NCCL), then passes the gathered blocks with block_flags = NULL.
+ *   step_tag: step counter, identical on every rank, never 0; its parity selects the table half, so a rank may run one
+ *     step ahead of its peers (it cannot run two ahead: finalize_x waits for every rank's block of the step).
+ *   finalize_x: all_blocks / block_flags = this rank's OWN tables at half (step_tag & 1).
+ * The workspace must be zero before the first step (a per-sequence counter lives there and is left at zero). */
+int hmm_b200_genepred_shard_reduce_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                     const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                     const float* end_hints, unsigned flags, float* block_out,
+                                     const unsigned long long* peer_block_tables, const unsigned long long* peer_flag_tables,
+                                     int rank, int world, unsigned step_tag, void* workspace, size_t workspace_bytes, void* stream);
+
+int hmm_b200_genepred_shard_finalize_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                       const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                       const float* end_hints, unsigned flags, const float* all_blocks, const unsigned* block_flags,
+                                       int rank, int world, unsigned step_tag, float* out_post, float* out_alpha, float* out_beta,
+                                       float* loglik, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
