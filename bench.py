@@ -29,6 +29,7 @@ NBUF = 8                              # rotating input/output sets: 8 x 44.8 MB 
 # caches before every kernel, so the L2-resident workspace K1 hands to K2 (emission rows + product trees) shows up as
 # DRAM reads there; in the back-to-back bench those reads are L2 hits.
 NCU_TRAFFIC_BYTES = 65.42e6
+NCU_TRAFFIC_NOTE = "ncu cold-cache capture"
 
 
 _STDOUT_FD = None
@@ -414,87 +415,72 @@ def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None):
     return float(t.item()), ll, launches, how
 
 
+def gene_params_on(dev):
+    from hmm_layer_b200 import ops
+    layer, cell = build_layer(dev)
+    em, tr = cell.emitter[0], cell.transitioner
+    cell.recurrent_init()
+    A, pi = tr.A.detach().contiguous(), cell.init_dist.detach().reshape(1, 15).contiguous()
+    return (A, pi, em.make_B_full().detach().contiguous(), ops.prepare_codon(em.codon_probs))
+
+
+def strong_c5(rank, world, dev, params, sizes=(1_000_000, 8_000_000), steps=50):
+    """BASELINE config 5 inside the caller's process group: ONE sequence cut into `world` contiguous shards (strong
+    scaling: total work fixed).  At N > 1 rank 0 also times the same sequence alone on its GPU, so that the line carries
+    its own speed-up; every rank must call this."""
+    import torch.distributed as dist
+    out = {}
+    for T in sizes:
+        ms, ll, launches, how = measure_c5(T, rank, world, dev, params, steps=steps)
+        ms1 = ms
+        if world > 1:
+            if rank == 0:
+                ms1, ll1, _, _ = measure_c5(T, 0, 1, dev, params, steps=max(5, steps // 2))
+            dist.barrier()
+        key = f"{T // 1_000_000}Mbp"
+        out[key] = {"T": T, "ms_per_step": ms, "ms_per_step_1gpu": ms1, "speedup_vs_1": ms1 / ms, "efficiency": ms1 / ms / world,
+                    "loglik": ll, "launches_per_step": launches, "collective": how,
+                    "cells_per_s": 225.0 * T / (ms * 1e-3)}
+    return out
+
+
 def run_config5(args, rank, world, local):
     """Secondary line (--config 5): BASELINE config 5, ONE 1 Mbp sequence, 15-state gene HMM, forward+posterior.
     N = 1: the chunked scan on one GPU.  N > 1: the sequence is cut into N contiguous shards (hmm_layer_b200/sharded.py),
-    every rank reduces its shard to one 16x16 transfer block, ONE all-gather of 1 KB per rank (NCCL over NVLink), every
-    rank finalises its own positions.  Strong scaling: total work fixed."""
+    every rank reduces its shard to one 16x16 transfer block and stores it into every rank's table over NVLink inside the
+    kernel (NCCL all-gather when peer memory cannot be mapped); every rank finalises its own positions.  Strong scaling."""
     import torch.distributed as dist
-    from hmm_layer_b200 import ops, sharded, synthetic as syn
+    from hmm_layer_b200 import synthetic as syn
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     k, B, T, q = 1, 1, 1_000_000, 15
-    layer, cell = build_layer(dev)
-    em, tr = cell.emitter[0], cell.transitioner
-    cell.recurrent_init()
-    A, pi = tr.A.detach().contiguous(), cell.init_dist.detach().reshape(1, 15).contiguous()
-    Bfull, codon = em.make_B_full().detach().contiguous(), ops.prepare_codon(em.codon_probs)
-    full = syn.gene_inputs(k, B, T, seed=1234)                       # same sequence on every rank (same seed)
-    shard, halo, off, tot = sharded.slice_with_halo(full, rank, world)
-    host_shard = shard.pin_memory()
-    nbuf = 8                                                         # 8 rotating shard copies: 8 x 140 MB / N > 126 MB L2
-    xs = [host_shard.to(dev).clone() for _ in range(nbuf)]
-    halo_d = halo.to(dev)
-    host_out = torch.empty((k, B, shard.shape[2], q), dtype=torch.float32).pin_memory()
-
-    def step(i, x=None):
-        x = xs[i % nbuf] if x is None else x
-        if world == 1:
-            return ops.genepred_run(x, A, pi, Bfull, codon, want_post=True)
-        return sharded.sequence_sharded_run(x, halo_d, off, tot, A, pi, Bfull, codon, want_post=True)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    steps, warm = min(args.steps, 50), max(3, min(args.warmup, 10))
+    params = gene_params_on(dev)
     sampler = ClockSampler(local)
     sampler.start()
-    for i in range(warm):
-        step(i)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier(); e0.record()
-    for i in range(steps):
-        step(i)
-    e1.record(); barrier()
-    ms_step = e0.elapsed_time(e1) / steps
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n_e2e = 5
-    barrier(); f0.record()
-    for i in range(n_e2e):
-        r = step(i, host_shard.to(dev, non_blocking=True))
-        host_out.copy_(r["post"], non_blocking=True)
-    f1.record(); barrier()
-    ms_e2e = f0.elapsed_time(f1) / n_e2e
-    ll = float(r["loglik"][0, 0])
+    steps = min(args.steps, 50)
+    res = strong_c5(rank, world, dev, params, steps=steps)
     clocks = sampler.stop()
-    t = torch.tensor([ms_step, ms_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step, ms_e2e = t.tolist()
-    cells = syn.cells(k, B, T, q)
     if rank == 0:
+        r = res["1Mbp"]
+        ms_step = r["ms_per_step"]
         peak, src = peaks()
         achieved = BYTES_PER_POSITION * T / (ms_step * 1e-3) / 1e9
         emit_json(({
-            "metric": "hmm_cells_per_s", "value": cells / (ms_step * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": steps,
-            "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "metric": "hmm_cells_per_s", "value": syn.cells(k, B, T, q) / (ms_step * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": steps,
+            "warmup": 5, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "config5: single 1 Mbp genomic sequence, 15-state gene HMM forward+posterior, sequence sharded over the GPUs",
                        "num_models": k, "batch": B, "T": T, "q": q,
-                       "sharding": "contiguous sequence shards, one all-gather of 1 KB per rank" if world > 1 else "one GPU, chunked scan",
-                       "l2_policy": f"{nbuf} rotating shard copies ({nbuf} x {140 * T / world / 1e6:.0f} MB) > 126 MB L2"},
-            "e2e": {"value": cells / (ms_e2e * 1e-3), "unit": "cells/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": int(host_shard.numel() * 4) * world, "d2h_bytes_per_step": int(host_out.numel() * 4) * world,
-                    "api": "sharded.sequence_sharded_run(pinned host shard -> device) + D2H of the local log-posterior"},
-            "gpu_launches": (2 if world == 1 else 5) * steps,
+                       "sharding": f"contiguous sequence shards; exchange: {r['collective']}" if world > 1 else "one GPU, chunked scan",
+                       "l2_policy": "rotating shard copies larger than the 126 MB L2"},
+            "e2e": None,
+            "gpu_launches": r["launches_per_step"] * steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),
                          "traffic": None, "peak_source": src,
-                         "scope": "whole step (all kernels + the all-gather), 140 B/position x 1e6 positions over the aggregate HBM peak of the N GPUs"},
-            "loglik": ll, "clocks": clocks,
+                         "scope": "whole step (all kernels + the exchange), 140 B/position x 1e6 positions over the aggregate HBM peak of the N GPUs"},
+            "strong_c5": res, "loglik": r["loglik"], "clocks": clocks,
         }))
     if world > 1:
         dist.destroy_process_group()
@@ -571,8 +557,10 @@ def run_train(args, rank, world, local):
 def main():
     quiet_stdout()
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 4, 5],
-                    help="BASELINE config (2 = headline; 1 = the reference's CPU-scale case; 4 = learnMSA sizes; 5 = one 1 Mbp sequence sharded over the GPUs)")
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 4, 5],
+                    help="BASELINE config (2 = headline; 1 = the reference's CPU-scale case; 3 = k-mer emitter, Bidirectional posterior, "
+                         "batch 64 x 9999; 4 = learnMSA sizes; 5 = one 1 Mbp sequence sharded over the GPUs)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the strong_c5 / config-3 objects of the default line")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
@@ -597,6 +585,12 @@ def main():
         return run_config4(args, rank, world, local)
     if args.config == 5:
         return run_config5(args, rank, world, local)
+    if args.config == 3:
+        # same model and path as config 2 (the reference's GenePredHMMEmitter IS the k = 3 k-mer emitter, and the posterior is the
+        # Bidirectional forward-backward): twice the batch
+        WORKLOAD["batch"] = 64
+        global WORKLOAD_STR
+        WORKLOAD_STR = "config3: gene_pred HMM with kmer emitter (k=3), Bidirectional posterior, batch 64 x 9999 bp"
     import torch.distributed as dist
     from hmm_layer_b200 import ops, synthetic as syn
     dev = torch.device("cuda", local)
@@ -680,14 +674,41 @@ def main():
     ms_e2e = f0.elapsed_time(f1) / max(n_e2e, 1)
     # ---- per-kernel durations, live, on the launching stream ----
     ops.profile_enable(True)
-    ker = [0.0, 0.0]
+    ker = []
     n_prof = 0 if args.no_e2e else max(3, min(args.steps, 50))
     for i in range(n_prof):
         step(i)
-        for j, v in enumerate(ops.profile_read()):
-            ker[j] += v / n_prof
+        cur = ops.profile_read()
+        ker = [a_ + b_ / n_prof for a_, b_ in zip(ker or [0.0] * len(cur), cur)]
     ops.profile_enable(False)
     clocks = sampler.stop()
+    # ---- the other GPU-scale gene-HMM workloads in the same process group (not part of the headline number) ----
+    secondary, c5 = {}, None
+    if not args.no_secondary and args.config == 2:
+        try:
+            c5 = strong_c5(rank, world, dev, (A, pi, Bfull, codon), steps=min(args.steps, 50))
+        except Exception as e:                      # the headline line must not depend on it
+            c5 = {"error": f"{type(e).__name__}: {e}"}
+        try:
+            x3 = [torch.cat([xs[j], xs[(j + 1) % NBUF]], 1) for j in range(0, 4)]     # 64 x 9999 per rank
+            o3 = [torch.empty((k, 2 * B, T, q), dtype=torch.float32, device=dev) for _ in range(4)]
+            for i in range(5):
+                ops.genepred_run(x3[i % 4], A, pi, Bfull, codon, want_post=True, out={"post": o3[i % 4]})
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); g0.record()
+            n3 = min(args.steps, 50)
+            for i in range(n3):
+                ops.genepred_run(x3[i % 4], A, pi, Bfull, codon, want_post=True, out={"post": o3[i % 4]})
+            g1.record(); barrier()
+            t3 = torch.tensor([g0.elapsed_time(g1) / n3], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+            secondary["config3"] = {"workload": "gene_pred HMM with kmer emitter (k=3), Bidirectional posterior, batch 64 x 9999 bp per GPU",
+                                    "ms_per_step": float(t3.item()), "cells_per_s": world * syn.cells(k, 2 * B, T, q) / (float(t3.item()) * 1e-3),
+                                    "frac_of_hbm_peak": BYTES_PER_POSITION * k * 2 * B * T / (float(t3.item()) * 1e-3) / 1e9 / peaks()[0]}
+            del x3, o3
+        except Exception as e:
+            secondary["config3"] = {"error": f"{type(e).__name__}: {e}"}
 
     t = torch.tensor([ms_e2e], dtype=torch.float64, device=dev)
     if world > 1:
@@ -715,15 +736,19 @@ def main():
             "e2e": {"value": e2e_value, "unit": "cells/s", "ms_per_step": ms_e2e, "warmup_calls": n_e2e_warm,
                     "h2d_bytes_per_step": int(host_in.numel() * 4), "d2h_bytes_per_step": int(host_out.numel() * 4),
                     "api": "MsaHmmLayer.state_posterior_log_probs(pinned CPU tensor) -> pinned CPU log-posterior, through hmm_b200_genepred_run_host (batch-sliced H2D / kernels / D2H pipeline)"},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": max(1, len(ker) - 0) * args.steps if ker else args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": NCU_TRAFFIC_BYTES,
-                         "traffic_note": "ncu cold-cache capture r1j (profiles/r1j_ncu_summary.txt): K1 reads 25.7 MB of inputs, K2 reads 39.4 MB (emission rows + product trees written by K1; L2-resident outside the profiler); the 19.2 MB of log posterior are still in L2 when the capture ends (0.3 MB of DRAM writes)",
+                         "traffic_note": NCU_TRAFFIC_NOTE,
                          "peak_source": peak_src,
-                         "scope": "the fused pass = 2 launches (products_kernel, finalize_kernel); algorithmic bytes = 140 B/position x 319968 positions = 44.8 MB per pass; duration = sum of the two kernels' CUDA-event times",
-                         "kernel_ms": {"products_kernel": ker[0], "finalize_kernel": ker[1]}},
+                         "scope": "the whole pass = ONE launch (fused_kernel, csrc/gene15_fused.cu); algorithmic bytes = 140 B/position x positions per pass; duration = the back-to-back timed loop itself",
+                         "kernel_ms": ({"fused_kernel": ker[0]} if len(ker) == 1 else {f"launch{j}": v for j, v in enumerate(ker)})},
             "clocks": clocks,
         }
+        if c5 is not None:
+            line["strong_c5"] = c5
+        if secondary:
+            line["secondary"] = secondary
         if not args.no_cpu_baseline and world == 1:
             # the same measurement as `--impl reference`: the full config-2 batch per pass, all host threads
             cpu_step, kind, what = cpu_arm(k, B, T)
