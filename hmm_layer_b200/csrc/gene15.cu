@@ -609,11 +609,13 @@ __global__ void __launch_bounds__(K1_THREADS) shard_product_kernel(const Args a,
   __shared__ unsigned s_last;
   const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, NB = gridDim.y, tid = threadIdx.x;
   const int nb = min(G, P - g * G);
+  if (tid == 0) griddep_launch_dependents();
+  for (int b = nb + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+  griddep_wait();   // the tile matrices come from products_kernel (programmatic dependent launch)
   {
     const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
     float4* dst = reinterpret_cast<float4*>(H + G * MAT);
-    for (int i = tid; i < nb * (MAT / 4); i += K1_THREADS) dst[i] = __ldg(src + i);
-    for (int b = nb + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+    for (int i = tid; i < nb * (MAT / 4); i += K1_THREADS) dst[i] = __ldcg(src + i);
   }
   __syncthreads();
   for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
@@ -630,11 +632,14 @@ __global__ void __launch_bounds__(K1_THREADS) shard_product_kernel(const Args a,
     __syncthreads();
     if (!s_last) return;
     const float4* src = reinterpret_cast<const float4*>(Gt + (size_t)n * PG * MAT);
-    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+    // a tree over the next power of two of PG leaves only: its leaves sit at heap slots [W, 2W), its root at 1
+    int W = 1;
+    while (W < PG) W <<= 1;
+    float4* dst = reinterpret_cast<float4*>(H + (size_t)W * MAT);
     for (int i = tid; i < PG * (MAT / 4); i += K1_THREADS) dst[i] = __ldcg(src + i);
-    for (int b = PG + (tid >> 5); b < G; b += K1_THREADS / 32) identity_block(H + (G + b) * MAT, tid & 31);
+    for (int b = PG + (tid >> 5); b < W; b += K1_THREADS / 32) identity_block(H + (W + b) * MAT, tid & 31);
     __syncthreads();
-    for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+    for (int np = W / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
   }
   // the shard's block: to the caller's buffer (NCCL route) or into every rank's table (peer stores over NVLink)
   const float4* root = reinterpret_cast<const float4*>(H + MAT);
@@ -653,6 +658,22 @@ __global__ void __launch_bounds__(K1_THREADS) shard_product_kernel(const Args a,
   }
 }
 
+// very long shards (more than G * G tiles per rank): the boundary kernels of the NCCL route do the scans, these two move
+// the block into every rank's table and wait for the tables
+__global__ void __launch_bounds__(64) shard_publish_kernel(const float* __restrict__ block, const Peers pr, int NB) {
+  const int n = blockIdx.x, tid = threadIdx.x;
+  const size_t half = (size_t)(pr.tag & 1u) * pr.world * NB;
+  const float4 v = reinterpret_cast<const float4*>(block + (size_t)n * MAT)[tid];
+  for (int r = 0; r < pr.world; ++r) reinterpret_cast<float4*>(pr.blocks[r] + (half + (size_t)pr.rank * NB + n) * MAT)[tid] = v;
+  __threadfence_system();
+  __syncthreads();
+  if (tid < pr.world) st_release_sys_u32(pr.flags[tid] + half + (size_t)pr.rank * NB + n, pr.tag);
+}
+__global__ void __launch_bounds__(256) shard_wait_kernel(const unsigned* __restrict__ flags, int count, unsigned tag) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    while (ld_acquire_sys_u32(flags + i) != tag) __nanosleep(100);
+}
+
 struct XSmem {
   float rb[MAX_PEERS][MAT];   // the ranks' blocks
   float gm[G][MAT];           // this sequence's group matrices
@@ -667,6 +688,8 @@ __global__ void __launch_bounds__(256) shard_scan_kernel(const Args a, const flo
   const int g = blockIdx.x, n = blockIdx.y, P = a.P, PG = gridDim.x, NB = gridDim.y, m = n / a.batch;
   const int tid = threadIdx.x, lane = tid & 31, hl = lane & 15, hi = lane >> 4;
   const int nb = min(G, P - g * G);
+  if (tid == 0) griddep_launch_dependents();
+  griddep_wait();   // tile / group matrices come from the kernels in front (programmatic dependent launch)
   // local data first (they do not depend on the other ranks), then the wait, then the ranks' blocks
   {
     const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
@@ -2136,7 +2159,6 @@ int shard_reduce_x(const float* inputs, int num_models, int batch, int T, int se
   HMM_REQUIRE(!peer_blocks || (peer_flags && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world && tag != 0),
               "genepred shard_reduce_x: bad peer tables (world %d, rank %d, tag %u)", world, rank, tag);
   const int NB = num_models * batch, PG = cdiv(a.P, G);
-  HMM_REQUIRE(PG <= G, "genepred shard_reduce_x: shard too long (%d tiles; at most %d)", a.P, G * G);
   Peers pr{};
   if (peer_blocks) {
     for (int r = 0; r < world; ++r) {
@@ -2146,10 +2168,26 @@ int shard_reduce_x(const float* inputs, int num_models, int batch, int T, int se
     pr.rank = rank; pr.world = world; pr.tag = tag;
   }
   rc = launch_products(a, NB, st); if (rc) return rc;
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  if (PG > G) {
+    // more than G * G tiles per rank: the general boundary kernels reduce the shard, a small kernel publishes the block
+    float* blk = block_out ? block_out : reinterpret_cast<float*>(ws + l.bvf);   // (bvf is written only by finalize_x)
+    rc = launch_boundary(a, l, NB, 1, blk, false, workspace, st); if (rc) return rc;
+    if (peer_blocks) shard_publish_kernel<<<NB, 64, 0, st>>>(blk, pr, NB);
+    HMM_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
   const size_t smg = (size_t)HEAP * MAT * sizeof(float);
   rc = ensure_dynamic_smem(shard_product_kernel, 14, smg); if (rc) return rc;
-  unsigned char* ws = static_cast<unsigned char*>(workspace);
-  shard_product_kernel<<<dim3(PG, NB), K1_THREADS, smg, st>>>(a, reinterpret_cast<float*>(ws + l.Gt), pr, block_out);
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(PG, NB); cfg.blockDim = dim3(K1_THREADS); cfg.dynamicSmemBytes = smg; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_product_kernel, a, reinterpret_cast<float*>(ws + l.Gt), pr, block_out));
+  }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -2168,12 +2206,36 @@ int shard_finalize_x(const float* inputs, int num_models, int batch, int T, int 
   HMM_REQUIRE(all_blocks && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world, "genepred shard_finalize_x: bad rank %d of %d", rank, world);
   HMM_REQUIRE(out_post || out_alpha || out_beta || loglik, "genepred shard_finalize_x: no output requested");
   const int NB = num_models * batch, PG = cdiv(a.P, G);
-  HMM_REQUIRE(PG <= G, "genepred shard_finalize_x: shard too long (%d tiles; at most %d)", a.P, G * G);
   unsigned char* ws = static_cast<unsigned char*>(workspace);
-  rc = ensure_dynamic_smem(shard_scan_kernel, 15, sizeof(XSmem)); if (rc) return rc;
   a.ll_external = 1;
-  shard_scan_kernel<<<dim3(PG, NB), 256, sizeof(XSmem), st>>>(a, reinterpret_cast<const float*>(ws + l.Gt), all_blocks, block_flags, rank,
-                                                              world, tag, loglik);
+  if (PG > G) {
+    if (block_flags) shard_wait_kernel<<<1, 256, 0, st>>>(block_flags, world * NB, tag);
+    float* in_f = reinterpret_cast<float*>(ws + l.inf);
+    float* in_r = reinterpret_cast<float*>(ws + l.inr);
+    shard_boundary_kernel<<<NB, 32, 0, st>>>(all_blocks, rank, world, NB, batch, pi, in_f, in_r, a.llws, loglik);
+    a.in_f = in_f; a.in_r = in_r;
+    a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = nullptr;
+    if (out_post || out_alpha || out_beta) {
+      const bool full = out_alpha || out_beta;
+      const size_t sm2 = k2_smem_bytes(a.L, full);
+      rc = full ? set_smem(finalize_kernel<true>, SLOT_K2F, sm2) : set_smem(finalize_kernel<false>, SLOT_K2P, sm2); if (rc) return rc;
+      rc = launch_boundary(a, l, NB, 0, nullptr, true, workspace, st); if (rc) return rc;
+      rc = launch_finalize(a, NB, full, sm2, st, false); if (rc) return rc;
+    }
+    HMM_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
+  rc = ensure_dynamic_smem(shard_scan_kernel, 15, sizeof(XSmem)); if (rc) return rc;
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(PG, NB); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = sizeof(XSmem); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_scan_kernel, a, reinterpret_cast<const float*>(ws + l.Gt), all_blocks, block_flags, rank,
+                                   world, tag, loglik));
+  }
   a.out_post = out_post; a.out_alpha = out_alpha; a.out_beta = out_beta; a.loglik = nullptr;
   if (out_post || out_alpha || out_beta) {
     const bool full = out_alpha || out_beta;

@@ -24,12 +24,14 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _rank_main(rank, world, port, B, T, seed, outdir):
+def _rank_main(rank, world, port, B, T, seed, outdir, chunk_len):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    if chunk_len:
+        ops.set_tuning(chunk_len, 0)
     x = syn.gene_inputs(1, B, T, seed=seed, p_n=0.01)
     A, pi, Bfull, tab = [torch.as_tensor(np.asarray(v, np.float32)).to(dev) for v in gene_params(pi_random=True)]
     shard, halo, off, tot = sharded.slice_with_halo(x, rank, world)
@@ -50,12 +52,14 @@ def _rank_main(rank, world, port, B, T, seed, outdir):
 
 
 @needs2
-@pytest.mark.parametrize("B,T", [(2, 40_000), (1, 300_001)])
-def test_sequence_sharded_on_real_ranks_matches_oracle(tmp_path, B, T):
+@pytest.mark.parametrize("B,T,chunk_len,max_world", [(2, 40_000, 0, 8), (1, 300_001, 0, 8), (1, 300_001, 4, 2)])
+def test_sequence_sharded_on_real_ranks_matches_oracle(tmp_path, B, T, chunk_len, max_world):
+    """chunk_len = 4 on two ranks: 1172 tiles per rank, beyond the 32 x 32 tiles the in-kernel scans cover -- the
+    general boundary kernels do the scans, the exchange stays in-kernel."""
     import torch.multiprocessing as mp
-    world = min(torch.cuda.device_count(), 8)
+    world = min(torch.cuda.device_count(), max_world)
     port = _free_port()
-    mp.spawn(_rank_main, args=(world, port, B, T, 900 + B, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_rank_main, args=(world, port, B, T, 900 + B, str(tmp_path), chunk_len), nprocs=world, join=True)
     x = syn.gene_inputs(1, B, T, seed=900 + B, p_n=0.01)
     A, pi, Bfull, tab = gene_params(pi_random=True)
     ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
