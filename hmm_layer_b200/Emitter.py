@@ -72,6 +72,11 @@ class ProfileHMMEmitter(nn.Module):
             mats.append(torch.nn.functional.pad(m, (0, 0, 0, q - m.shape[0])))
         return torch.stack(mats)
 
+    def onehot_table(self):
+        """(k, s + 1, q): column x of B for every symbol x -- what a one-hot input row picks (forward :139-157)."""
+        B = self.B if self.B is not None else self.make_B()
+        return B.transpose(1, 2)
+
     def make_B_amino(self):
         return self.make_B()
 

@@ -23,7 +23,9 @@ def _check_inputs(inputs, cell, parallel_factor):
     """CPU inputs are accepted for the fused gene model only (host path: outputs come back as CPU tensors, like the
     reference's).  The compute always runs on a GPU: a cell whose parameters live on the CPU (the reference's own script
     never moves it, tests/parallel_rnn_forward.py:42-51) has its few derived parameter tensors uploaded per call."""
-    if inputs.dim() != 4:
+    if inputs.dim() == 3 and not inputs.is_floating_point() and not _is_fused_gene_cell(cell):
+        pass   # integer symbols (num_model, b, seq_len): the fused one-hot route of the dense engines
+    elif inputs.dim() != 4:
         raise ValueError(f"inputs must have shape (num_model, b, seq_len, s), got {tuple(inputs.shape)}")
     if inputs.shape[0] != cell.num_models:
         raise ValueError(f"inputs carry {inputs.shape[0]} models but the cell has {cell.num_models}")
@@ -87,9 +89,33 @@ def _dense_run_cell(inputs, cell, end_hints, training, **want):
     cell.recurrent_init()
     dev = _compute_device(inputs, cell)
     x = inputs.to(dev)
+    table = _onehot_table(cell, x, end_hints)
+    if table is not None:
+        # one-hot inputs: E_t = B[:, x_t] is a column gather inside the recurrence kernels (reference Emitter.py:139-157
+        # contracts inputs . B^T); neither cuBLAS nor a (k,B,T,q) emission tensor on the path
+        sym = x if x.dim() == 3 else x.argmax(-1)
+        r = ops.dense_run_onehot(sym.to(torch.uint8), table.to(dev), cell.transitioner.A.detach().to(dev),
+                                 cell.init_dist.detach().reshape(cell.num_models, -1).to(dev), **want)
+        return r if inputs.is_cuda else {k: v.to(inputs.device) for k, v in r.items()}
     E = cell.emission_probs(x, end_hints=None if end_hints is None else end_hints.to(dev), training=training)
     r = ops.dense_run(E.detach(), cell.transitioner.A.detach().to(dev), cell.init_dist.detach().reshape(cell.num_models, -1).to(dev), **want)
     return r if inputs.is_cuda else {k: v.to(inputs.device) for k, v in r.items()}
+
+
+def _onehot_table(cell, x, end_hints):
+    """(k, s, q) emission table for the fused one-hot route, or None: taken when the caller declared the inputs one-hot
+    (`cell.onehot_inputs = True`, or passes integer symbols (k, B, T) directly) and the cell's single emitter exposes
+    `onehot_table()` (ProfileHMMEmitter, DenseEmitter).  Soft inputs keep the GEMM form."""
+    symbols = x.dim() == 3 and not x.is_floating_point()
+    if not (symbols or getattr(cell, "onehot_inputs", False)) or end_hints is not None or len(cell.emitter) != 1:
+        return None
+    em = cell.emitter[0]
+    if not hasattr(em, "onehot_table"):
+        return None
+    t = em.onehot_table().detach()
+    if not symbols and t.shape[1] != x.shape[-1]:
+        t = t[:, :x.shape[-1]]
+    return t.contiguous()
 
 
 def _gene_loglik_diff(inputs, cell, training):
@@ -234,10 +260,12 @@ class MsaHmmLayer(nn.Module):
 
     def forward(self, inputs, indices=None, training=False):
         """loglik (num_model, b), aggregated loglik (), [prior (num_model), aux_loss ()]  (reference :180-208)."""
-        inputs = inputs.to(torch.float32)
-        self.build(inputs.shape)
+        symbols = inputs.dim() == 3 and not inputs.is_floating_point()    # integer symbols: the fused one-hot route (inference)
+        if not symbols:
+            inputs = inputs.to(torch.float32)
+        self.build(None if symbols else inputs.shape)
         cell = self.cell
-        diff = torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
+        diff = not symbols and torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in cell.parameters()))
         fused_gene = _is_fused_gene_cell(cell)
         _check_inputs(inputs, cell, self.parallel_factor)
         home = inputs.device

@@ -18,7 +18,7 @@ EXPORTS = [
     "hmm_b200_genepred_params", "hmm_b200_genepred_params_grad",
     "hmm_b200_genepred_emission", "hmm_b200_emission_general", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
     "hmm_b200_genepred_shard_reduce_x", "hmm_b200_genepred_shard_finalize_x",
-    "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_cell_step",
+    "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_dense_workspace_size_onehot", "hmm_b200_dense_run_onehot", "hmm_b200_cell_step",
 ]
 
 _lib = None
@@ -82,6 +82,10 @@ def load():
     lib.hmm_b200_dense_workspace_size.argtypes = [ctypes.c_int] * 4
     lib.hmm_b200_dense_run.argtypes = [c_fp, c_fp, c_fp, c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                        ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
+    lib.hmm_b200_dense_workspace_size_onehot.restype = ctypes.c_size_t
+    lib.hmm_b200_dense_workspace_size_onehot.argtypes = [ctypes.c_int] * 4
+    lib.hmm_b200_dense_run_onehot.argtypes = [c_fp, c_fp, ctypes.c_int, c_fp, c_fp, c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_int, ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
     lib.hmm_b200_cell_step.argtypes = [c_fp, c_fp, c_fp, c_fp] + [ctypes.c_int] * 6 + [c_fp, c_fp, c_fp, c_fp]
     _lib = lib
     return lib

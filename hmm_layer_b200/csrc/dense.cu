@@ -20,8 +20,9 @@ namespace dense_tc {   // dense_tc.cu: tcgen05 step for profile-HMM sizes
 bool supported(int k, int B, int q);
 int slots(int q);
 size_t extra_workspace(int k, int B, int q);
-int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
-              float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st);
+int run_steps(const float* E, const unsigned char* sym, const float* Bt, int nsym, const float* A, const float* pi, int k, int B, int T,
+              int q, bool need_f, bool need_b, float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra,
+              cudaStream_t st);
 }  // namespace dense_tc
 namespace dense {
 
@@ -156,6 +157,9 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs a) {
 // partial sums), so cum_kernel / finish_kernel are shared.  thread = state.
 struct SeqArgs {
   const float* E; const float* A; const float* At; const float* pi;
+  // one-hot form (E == NULL): E_t = Bt[m][sym_t], sym (k, B, T) bytes, Bt (k, nsym, q); the sequence's symbols are staged
+  // in shared memory behind the transition matrix and the ring is filled from rows of the (L2-resident) table
+  const unsigned char* sym; const float* Bt; int nsym;
   float* store[2];   // forward: a_t, backward: R_t  (k, B, T, q) or NULL when the direction is not wanted
   float* hist[2];    // (k, B, T)
   float* part_f;     // (k, B, ntile): partial sums of the last forward state (slot 0 gets the sum, the rest zeros)
@@ -208,7 +212,16 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   const int dt = d == 0 ? 1 : -1;
   const int t_first = d == 0 ? 0 : T - 1;
   const ptrdiff_t dq = (ptrdiff_t)dt * q;
-  const float* Eseq = a.E + (size_t)seq * T * q + (size_t)t_first * q + tid;
+  const float* Eseq = a.E ? a.E + (size_t)seq * T * q + (size_t)t_first * q + tid : nullptr;
+  unsigned char* syms = reinterpret_cast<unsigned char*>(As + (size_t)q * q);
+  if (!a.E) {
+    const unsigned char* src = a.sym + (size_t)seq * T;
+    for (int i = tid; i < T; i += nt) syms[i] = min((int)__ldg(src + i), a.nsym - 1);
+    __syncthreads();
+  }
+  const char* btm = reinterpret_cast<const char*>(a.Bt + (size_t)m * a.nsym * q + tid);
+  const unsigned syms_s = (unsigned)__cvta_generic_to_shared(syms);
+  int t_issue = t_first;
   float* store = (a.store[d] && live) ? a.store[d] + (size_t)seq * T * q + (size_t)t_first * q + tid : nullptr;
   float* hist = a.hist[d] + (size_t)seq * T + t_first;
   // emission rows arrive SEQ_PF steps ahead through cp.async into the ring (a step is shorter than a DRAM round trip);
@@ -217,14 +230,25 @@ __global__ void __launch_bounds__(192) seq_kernel(const SeqArgs a) {
   unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring + tid), sm_s = (unsigned)__cvta_generic_to_shared(sm);
   long long dqb = (long long)dq * 4;
   const char* esrc = reinterpret_cast<const char*>(Eseq);
-  asm volatile("" : "+r"(ring_s), "+r"(sm_s), "+l"(dqb), "+l"(esrc), "+l"(store), "+l"(hist));
+  asm volatile("" : "+r"(ring_s), "+r"(sm_s), "+l"(dqb), "+l"(esrc), "+l"(store), "+l"(hist), "+l"(btm));
   int e_left = live ? T : 0;
+  const bool onehot = a.E == nullptr;
+  const long long qb = (long long)q * 4;
   auto issue = [&](int blk) {
     const unsigned dst = ring_s + (unsigned)((blk & 1) * SEQ_PF * 192 * 4);
 #pragma unroll
     for (int u = 0; u < SEQ_PF; ++u) {
-      if (u < e_left) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + u * 192 * 4), "l"(esrc) : "memory");
+      if (u < e_left) {
+        const char* src = esrc;
+        if (onehot) {
+          unsigned sy;
+          asm volatile("ld.shared.u8 %0, [%1];" : "=r"(sy) : "r"(syms_s + (unsigned)t_issue));
+          src = btm + (long long)sy * qb;
+        }
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + u * 192 * 4), "l"(src) : "memory");
+      }
       esrc += dqb;
+      t_issue += dt;
     }
     e_left -= SEQ_PF;
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -449,6 +473,18 @@ __global__ void init_state_kernel(float* __restrict__ st, const float* __restric
   st[i] = pi ? pi[(size_t)m * q + j] : 1.f;
 }
 
+// fallback of the one-hot form for the engines that read a materialised emission tensor (per-step CUDA-core engine,
+// sequences too long for seq_kernel's symbol staging): E[n][t][j] = Bt[m][sym[n][t]][j], coalesced over j
+__global__ void __launch_bounds__(256) onehot_expand_kernel(const unsigned char* __restrict__ sym, const float* __restrict__ Bt,
+                                                            float* __restrict__ E, size_t rows, int B, int T, int q, int nsym) {
+  for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
+    const int m = (int)(r / ((size_t)B * T));
+    const int sy = min((int)__ldg(sym + r), nsym - 1);
+    const float* src = Bt + ((size_t)m * nsym + sy) * q;
+    for (int j = threadIdx.x; j < q; j += blockDim.x) E[r * q + j] = __ldg(src + j);
+  }
+}
+
 struct Layout {
   size_t st[2][2], part[2][2], hist[2], cum[2], ll, lld, extra, total;
 };
@@ -478,10 +514,37 @@ size_t workspace_size(int k, int B, int T, int q) {
 
 // out_alpha / out_beta double as the per-step stores; out_post needs both (the caller passes scratch for the one it
 // does not want back: see hmm_b200.h)
+// symbols + table (one-hot form) need the expanded tensor only where no engine gathers: bytes of it behind the layout
+static size_t onehot_expand_bytes(int k, int B, int T, int q) {
+  const bool tc = use_tc(k, B, q);
+  const size_t seq_smem = ((size_t)q * q + SEQ_HDR) * sizeof(float) + align_up((size_t)T, 16);
+  const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024;
+  return (tc || seq) ? 0 : align_up((size_t)k * B * T * q * sizeof(float), 256);
+}
+size_t workspace_size_onehot(int k, int B, int T, int q) {
+  if (k <= 0 || B <= 0 || T <= 0 || q <= 0) return 0;
+  return layout(k, B, T, q).total + onehot_expand_bytes(k, B, T, q);
+}
+
 int run(const float* E, const float* A, const float* At, const float* pi, int k, int B, int T, int q, unsigned flags,
         float* out_post, float* out_alpha, float* out_beta, float* loglik, void* workspace, size_t workspace_bytes,
-        cudaStream_t st) {
-  HMM_REQUIRE(E && A && pi, "dense: null input pointer");
+        cudaStream_t st, const unsigned char* sym = nullptr, const float* Bt = nullptr, int nsym = 0) {
+  HMM_REQUIRE((E || (sym && Bt && nsym > 0)) && A && pi, "dense: null input pointer");
+  if (!E) {
+    const size_t xb = onehot_expand_bytes(k, B, T, q);
+    if (xb) {   // no gathering engine for this shape: materialise E behind the regular workspace
+      const size_t base = layout(k, B, T, q).total;
+      if (!workspace || workspace_bytes < base + xb) {
+        set_error("dense onehot: workspace too small (%zu < %zu bytes)", workspace_bytes, base + xb);
+        return HMM_B200_EWORKSPACE;
+      }
+      float* Ex = reinterpret_cast<float*>(static_cast<unsigned char*>(workspace) + base);
+      const size_t rows = (size_t)k * B * T;
+      onehot_expand_kernel<<<(unsigned)(rows < 65535u * 16u ? rows : 65535u * 16u), 256, 0, st>>>(sym, Bt, Ex, rows, B, T, q, nsym);
+      HMM_CUDA_OK(cudaGetLastError());
+      E = Ex; sym = nullptr;
+    }
+  }
   HMM_REQUIRE(k > 0 && B > 0 && T > 0 && q > 0, "dense: k, B, T, q must be positive (got %d,%d,%d,%d)", k, B, T, q);
   HMM_REQUIRE(cdiv(q, BN) <= MAXP, "dense: q = %d exceeds the supported %d states", q, MAXP * BN);
   HMM_REQUIRE(cdiv(B, BM) <= 65535 && k <= 65535, "dense: batch / model count too large");
@@ -507,15 +570,16 @@ int run(const float* E, const float* A, const float* At, const float* pi, int k,
   if (tc) {
     float* part[2][2] = {{F(l.part[0][0]), F(l.part[0][1])}, {F(l.part[1][0]), F(l.part[1][1])}};
     float* hist[2] = {F(l.hist[0]), F(l.hist[1])};
-    const int rc = dense_tc::run_steps(E, A, pi, k, B, T, q, need_f, need_b, out_alpha, out_beta, part, hist, ws + l.extra, st);
+    const int rc = dense_tc::run_steps(E, sym, Bt, nsym, A, pi, k, B, T, q, need_f, need_b, out_alpha, out_beta, part, hist, ws + l.extra, st);
     if (rc) return rc;
   }
   // small q: one persistent launch for all steps of both directions (seq_kernel); g_path == 1 keeps the per-step engine
-  const size_t seq_smem = ((size_t)q * q + SEQ_HDR) * sizeof(float);
+  const size_t seq_smem = ((size_t)q * q + SEQ_HDR) * sizeof(float) + (E ? 0 : align_up((size_t)T, 16));
   const bool seq = !tc && g_path == 0 && q < kTcMinStates && seq_smem <= 200 * 1024 && N <= 2147483647ull;
   if (seq) {
     SeqArgs a;
     a.E = E; a.A = A; a.At = At; a.pi = pi;
+    a.sym = sym; a.Bt = Bt; a.nsym = nsym;
     a.store[0] = need_f ? out_alpha : nullptr; a.store[1] = need_b ? out_beta : nullptr;
     a.hist[0] = F(l.hist[0]); a.hist[1] = F(l.hist[1]);
     a.part_f = F(l.part[0][T & 1]);
@@ -601,6 +665,18 @@ int hmm_b200_dense_run(const float* E, const float* A, const float* A_transposed
                        void* workspace, size_t workspace_bytes, void* stream) {
   return hmm::dense::run(E, A, A_transposed, pi, num_models, batch, T, q, flags, out_post, out_alpha, out_beta, loglik, workspace,
                          workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+size_t hmm_b200_dense_workspace_size_onehot(int num_models, int batch, int T, int q) {
+  return hmm::dense::workspace_size_onehot(num_models, batch, T, q);
+}
+
+int hmm_b200_dense_run_onehot(const unsigned char* symbols, const float* Bt, int num_symbols, const float* A,
+                              const float* A_transposed, const float* pi, int num_models, int batch, int T, int q, unsigned flags,
+                              float* out_post, float* out_alpha, float* out_beta, float* loglik, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+  return hmm::dense::run(nullptr, A, A_transposed, pi, num_models, batch, T, q, flags, out_post, out_alpha, out_beta, loglik,
+                         workspace, workspace_bytes, static_cast<cudaStream_t>(stream), symbols, Bt, num_symbols);
 }
 
 int hmm_b200_cell_step(const float* E_t, const float* scaled, const float* loglik, const float* A, int num_models, int n,

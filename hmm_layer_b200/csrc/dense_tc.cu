@@ -35,7 +35,10 @@ constexpr int MAXP = 32;
 static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 
 struct Args {
-  const float* E;        // (k, B, T, q)
+  const float* E;        // (k, B, T, q), or NULL with the one-hot form:
+  const unsigned char* sym;   // (k, B, T) symbol of every position
+  const float* Bt;            // (k, nsym, q) emission table, Bt[m][x][j] = P(symbol x | state j): E_t = Bt[m][sym_t]
+  int nsym;
   uint16_t* state;       // bf16 [dir][pp][hi|lo][k*Bpad][Npad]
   float* store[2];       // per direction (k, B, T, q) or null: a_t (forward) / R_t (backward), un-normalised
   float* part[2][2];     // per direction, ping-pong: (k, B, ntile) partial row sums
@@ -256,7 +259,12 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
     for (int it = 0; it < nitems; ++it) {
       const int s = 1 + it / a.ndir, dir = a.dir0 + it % a.ndir, pp = (s + 1) & 1, buf = it & 1;
       const int t = dir == 0 ? s : a.T - 1 - s;
-      const float* Et = a.E + (size_t)t * a.q;
+      const float* Et = a.E ? a.E + (size_t)t * a.q : nullptr;
+      // one-hot form: lane i holds the symbol of the warp's row i at this step; the row's emissions are a row of the
+      // (L2-resident) table, fetched coalesced over the columns
+      const float* Btm = a.Bt + (size_t)m * a.nsym * a.q;
+      int mysym = 0;
+      if (!Et && lane < rows_here) mysym = min((int)__ldg(a.sym + ((size_t)m * a.B + row0 + qd * 32 + lane) * a.T + t), a.nsym - 1);
       float* St = a.store[dir] ? a.store[dir] + (size_t)t * a.q : nullptr;
       const bool stamp = (ew == 0 && lane == 0);
       if (stamp) dbg_stamp(a, 2, it, 0);
@@ -264,8 +272,10 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
       {
         const int col = cbase + lane;
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          ereg[i] = (i < rows_here && col < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + col) : 0.f;
+        for (int i = 0; i < 32; ++i) {
+          const int sy = __shfl_sync(0xffffffffu, mysym, i);
+          ereg[i] = (i < rows_here && col < a.q) ? (Et ? __ldg(Et + rbase + (size_t)i * rowpitch + col) : __ldg(Btm + (size_t)sy * a.q + col)) : 0.f;
+        }
       }
       if (s >= 2) {
         if (lane == 0) wait_count(cnt_r + dir, (unsigned)(a.ntile_n * (s - 1)));
@@ -295,8 +305,10 @@ chain_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CU
         if (c + 1 < CH) {   // next chunk's emissions: in flight while this chunk is processed
           const int ncol = col + 32;
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            ereg[i] = (i < rows_here && ncol < a.q) ? __ldg(Et + rbase + (size_t)i * rowpitch + ncol) : 0.f;
+          for (int i = 0; i < 32; ++i) {
+            const int sy = __shfl_sync(0xffffffffu, mysym, i);
+            ereg[i] = (i < rows_here && ncol < a.q) ? (Et ? __ldg(Et + rbase + (size_t)i * rowpitch + ncol) : __ldg(Btm + (size_t)sy * a.q + ncol)) : 0.f;
+          }
         }
         uint32_t acc[32];
         tmem_ld32(tmem + ((uint32_t)(qd * 32) << 16) + (uint32_t)(buf * TBN + half * (CH * 32) + c * 32), acc);
@@ -373,7 +385,8 @@ __global__ void __launch_bounds__(256) init_kernel(const Args a, const float* __
   const int t = dir == 0 ? 0 : a.T - 1;
   const bool valid = r < a.B;
   const size_t seq = (size_t)m * a.B + (valid ? r : 0);
-  const float* Er = a.E + (seq * a.T + t) * a.q;
+  const float* Er = a.E ? a.E + (seq * a.T + t) * a.q
+                        : a.Bt + ((size_t)m * a.nsym + min((int)a.sym[seq * a.T + t], a.nsym - 1)) * a.q;
   float* Sr = a.store[dir] ? a.store[dir] + (seq * a.T + t) * a.q : nullptr;
   uint16_t* o_hi = a.state + state_off(a, dir, 0, 0) + ((size_t)m * a.Bpad + r) * a.Npad;
   uint16_t* o_lo = a.state + state_off(a, dir, 0, 1) + ((size_t)m * a.Bpad + r) * a.Npad;
@@ -502,8 +515,9 @@ size_t extra_workspace(int k, int B, int q) {
 }
 
 // Runs every step of the requested directions.  part[d][p], hist[d]: the slots of dense.cu's layout with slots(q) per row.
-int run_steps(const float* E, const float* A, const float* pi, int k, int B, int T, int q, bool need_f, bool need_b,
-              float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra, cudaStream_t st) {
+int run_steps(const float* E, const unsigned char* sym, const float* Bt, int nsym, const float* A, const float* pi, int k, int B, int T,
+              int q, bool need_f, bool need_b, float* store_f, float* store_b, float* part[2][2], float* hist[2], void* extra,
+              cudaStream_t st) {
   const Dims d = dims(k, B, q);
   { int rcs = ensure_dynamic_smem(chain_kernel, 9, SMEM_BYTES); if (rcs) return rcs; }   // slot 9: dense_tc chain
   const int sms = sm_count();
@@ -519,7 +533,7 @@ int run_steps(const float* E, const float* A, const float* pi, int k, int B, int
   if (rc) return rc;
 
   Args a;
-  a.E = E; a.state = state; a.cnt = cnt; a.dbg = g_dbg;
+  a.E = E; a.sym = sym; a.Bt = Bt; a.nsym = nsym; a.state = state; a.cnt = cnt; a.dbg = g_dbg;
   a.store[0] = store_f; a.store[1] = store_b;
   for (int dd = 0; dd < 2; ++dd) {
     a.part[dd][0] = part[dd][0]; a.part[dd][1] = part[dd][1];

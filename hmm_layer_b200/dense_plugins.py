@@ -63,6 +63,10 @@ class DenseEmitter(nn.Module):
     def make_B(self):
         return self.B_param
 
+    def onehot_table(self):
+        """(k, s, q): column x of B for every symbol x -- what a one-hot input row picks."""
+        return self.B_param.transpose(1, 2)
+
     def forward(self, inputs, end_hints=None, training=False):
         """(k, b, T, s) -> (k, b, T, q): inputs . B^T (one-hot inputs pick a column of B)."""
         E = torch.einsum("kbts,kqs->kbtq", inputs, self.B_param)

@@ -505,6 +505,41 @@ def dense_run(E, A, pi, want_post=False, want_alpha=False, want_beta=False, no_l
     return res
 
 
+def dense_run_onehot(symbols, Bt, A, pi, want_post=False, want_alpha=False, want_beta=False, no_loglik=False):
+    """dense_run with the one-hot emission contraction fused (include/hmm_b200.h): symbols (k,B,T) uint8, Bt (k, s, q) =
+    the emission table transposed (Bt[m][x] = the emissions of every state for symbol x).  No (k,B,T,q) emission tensor."""
+    lib = _lib.load()
+    if not isinstance(symbols, torch.Tensor) or symbols.dim() != 3 or symbols.dtype != torch.uint8 or not symbols.is_cuda:
+        raise ValueError("symbols must be a CUDA uint8 tensor of shape (num_models, batch, T)")
+    k, B, T = symbols.shape
+    symbols = symbols.contiguous()
+    Bt = _req(Bt, "Bt")
+    if Bt.dim() != 3 or Bt.shape[0] != k:
+        raise ValueError(f"Bt must have shape ({k}, num_symbols, q), got {tuple(Bt.shape)}")
+    nsym, q = int(Bt.shape[1]), int(Bt.shape[2])
+    dev = symbols.device
+    A = _req(A, "A", (k, q, q)); pi = _req(pi.reshape(k, q), "pi", (k, q))
+    need_b = want_post or want_beta
+    At = A.transpose(1, 2).contiguous() if need_b else None
+    with torch.cuda.device(dev):
+        res = {"loglik": torch.empty((k, B), dtype=torch.float32, device=dev)}
+        alpha = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if (want_alpha or want_post) else None
+        beta = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if need_b else None
+        post = torch.empty((k, B, T, q), dtype=torch.float32, device=dev) if want_post else None
+        ws = _workspace(lib.hmm_b200_dense_workspace_size_onehot(k, B, T, q), dev)
+        flags = (NO_LOGLIK if no_loglik else 0) | (0 if want_alpha else ALPHA_SCRATCH) | (0 if want_beta else BETA_SCRATCH)
+        _lib.check(lib.hmm_b200_dense_run_onehot(_ptr(symbols), _ptr(Bt), nsym, _ptr(A), _ptr(At), _ptr(pi), k, B, T, q, flags,
+                                                 _ptr(post), _ptr(alpha), _ptr(beta), _ptr(res["loglik"]), _ptr(ws), ws.numel(),
+                                                 _stream()))
+    if want_post:
+        res["post"] = post
+    if want_alpha:
+        res["alpha"] = alpha
+    if want_beta:
+        res["beta"] = beta
+    return res
+
+
 class DenseLoglik(torch.autograd.Function):
     """loglik (k,B) of the generic dense HMM, differentiable w.r.t. E (k,B,T,q), A (k,q,q) and pi (k,q) — training
     profile-HMM models through MsaHmmLayer.forward (the reference differentiates its Python loop, MsaHmmCell.py:73-106).

@@ -258,6 +258,21 @@ int hmm_b200_dense_run(const float* E, const float* A, const float* A_transposed
                        float* out_post, float* out_alpha, float* out_beta, float* loglik,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same evaluation with the emission contraction fused for one-hot inputs (reference Emitter.py:139-157: inputs . B^T
+ * picks a column of B when the input row is one-hot): E is never materialised.
+ *   symbols (num_models, batch, T) uint8     the symbol of every position (values >= num_symbols are clamped)
+ *   Bt      (num_models, num_symbols, q)     Bt[m][x][j] = P(symbol x | state j) = B[m][j][x]
+ * The persistent recurrence (q < 192) stages a sequence's symbols in shared memory and fills its emission ring from rows
+ * of the (L2-resident) table; the tcgen05 step (q >= 192) gathers the 32 rows of an epilogue warp by symbol.  Shapes
+ * no gathering engine covers expand the tensor inside the workspace (hmm_b200_dense_workspace_size_onehot accounts for it). */
+size_t hmm_b200_dense_workspace_size_onehot(int num_models, int batch, int T, int q);
+
+int hmm_b200_dense_run_onehot(const unsigned char* symbols, const float* Bt, int num_symbols,
+                              const float* A, const float* A_transposed, const float* pi,
+                              int num_models, int batch, int T, int q, unsigned flags,
+                              float* out_post, float* out_alpha, float* out_beta, float* loglik,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
 /* One HmmCell.forward call (MsaHmmCell.py:73-106), for API parity with code that drives the cell step by step.
  *   E_t (num_models*n, q); scaled (num_models*n, qc*q); loglik (num_models*n, qc), qc = 1 or q (chunked form);
  *   A (num_models, q, q) already oriented (A forward, A^T reverse); init = 1 skips the transition (:77-78)

@@ -180,3 +180,52 @@ def test_config4_full_size_properties():
     finally:
         ops.set_tuning(0, 0, dense_path=0)
     np.testing.assert_allclose(cc.cpu().numpy(), ll[:, :16].cpu().numpy(), rtol=1e-5)
+
+
+@pytest.mark.parametrize("k,L,B,T,tc", [(1, 32, 16, 100, False), (2, 20, 5, 33, False), (1, 90, 3, 300, False), (1, 500, 130, 9, True),
+                                        (2, 500, 140, 12, True), (1, 100, 130, 7, True)])
+def test_onehot_route_equals_materialised_emissions(k, L, B, T, tc):
+    """hmm_b200_dense_run_onehot (column gather inside seq_kernel's ring fill / chain_kernel's epilogue) against the same
+    engines fed with the materialised tensor: the values entering the recurrence are identical, so are the results."""
+    A, pi, Bm = syn.profile_model(k, L)
+    x = syn.profile_inputs(k, B, T)
+    E = torch.einsum("kbts,kqs->kbtq", x, Bm)
+    sym = x.argmax(-1).to(torch.uint8).cuda()
+    Bt = Bm.transpose(1, 2).contiguous().cuda()
+    ops.set_tuning(0, 0, dense_path=2 if tc else 0)
+    try:
+        ref = ops.dense_run(E.cuda(), A.cuda(), pi.cuda(), want_post=True, want_alpha=True, want_beta=True)
+        got = ops.dense_run_onehot(sym, Bt, A.cuda(), pi.cuda(), want_post=True, want_alpha=True, want_beta=True)
+        only = ops.dense_run_onehot(sym, Bt, A.cuda(), pi.cuda())
+    finally:
+        ops.set_tuning(0, 0, dense_path=0)
+    torch.cuda.synchronize()
+    for key in ("loglik", "post", "alpha", "beta"):
+        assert torch.equal(ref[key], got[key]), key
+    assert torch.equal(only["loglik"], ref["loglik"])
+    full = O.posterior(E.numpy().astype(np.float64), A.numpy().astype(np.float64), pi.numpy().astype(np.float64))
+    rep = O.parity_report(got["post"].cpu().numpy(), got["loglik"].cpu().numpy(), full["log_post"], full["loglik"])
+    assert rep["loglik_rel"] < 2e-6 and rep["max_abs_dp"] < 1e-4 and rep["argmax_mismatch"] == 0, rep
+
+
+def test_onehot_route_through_the_layer_and_fallback_engine():
+    """cell.onehot_inputs = True (float one-hot inputs) and integer symbols through MsaHmmLayer; the per-step engine has
+    no gather and expands the table inside the workspace."""
+    layer, (A, pi, Bm) = make_profile_layer(1, 32)
+    x = syn.profile_inputs(1, 16, 100)
+    ll_gemm = layer(x.cuda())[0]
+    post_gemm = layer.state_posterior_log_probs(x.cuda())
+    layer.cell.onehot_inputs = True
+    ll_1h = layer(x.cuda())[0]
+    post_1h = layer.state_posterior_log_probs(x.cuda())
+    sym = x.argmax(-1).cuda()
+    ll_sym = layer(sym)[0]
+    la_sym, _ = layer.forward_recursion(sym)
+    assert torch.equal(ll_gemm, ll_1h) and torch.equal(ll_1h, ll_sym) and torch.equal(post_gemm, post_1h)
+    assert la_sym.shape == (1, 16, 100, 67)
+    ops.set_tuning(0, 0, dense_path=1)
+    try:
+        ll_step = layer(sym)[0]
+    finally:
+        ops.set_tuning(0, 0, dense_path=0)
+    np.testing.assert_allclose(ll_step.cpu().numpy(), ll_gemm.cpu().numpy(), rtol=2e-6)
