@@ -405,20 +405,25 @@ def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None):
 
     for i in range(warm):
         r = step(i)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    e0.record()
-    for i in range(steps):
-        r = step(i)
-    e1.record()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    # the K-step loop is timed 5 times (barrier + synchronize either side); per loop the slowest rank, then the median
+    loops = []
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(steps):
+            r = step(i)
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        loops.append(e0.elapsed_time(e1) / steps)
+    t = torch.tensor(loops, dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t = t.median().reshape(1)
     ll = float(r["loglik"][0, 0])
     launches = 1 if world == 1 else ctx.launches_per_step
     how = "none (one GPU)" if world == 1 else ctx.exchange
@@ -435,14 +440,14 @@ def gene_params_on(dev):
     return (A, pi, em.make_B_full().detach().contiguous(), ops.prepare_codon(em.codon_probs))
 
 
-def strong_c5(rank, world, dev, params, sizes=(1_000_000, 8_000_000), steps=50):
+def strong_c5(rank, world, dev, params, sizes=(1_000_000, 8_000_000), steps=100):
     """BASELINE config 5 inside the caller's process group: ONE sequence cut into `world` contiguous shards (strong
     scaling: total work fixed).  At N > 1 rank 0 also times the same sequence alone on its GPU, so that the line carries
     its own speed-up; every rank must call this."""
     import torch.distributed as dist
     out = {}
     for T in sizes:
-        ms, ll, launches, how = measure_c5(T, rank, world, dev, params, steps=steps)
+        ms, ll, launches, how = measure_c5(T, rank, world, dev, params, steps=steps if T <= 2_000_000 else max(10, steps // 4))
         ms1 = ms
         if world > 1:
             if rank == 0:
@@ -470,7 +475,7 @@ def run_config5(args, rank, world, local):
     params = gene_params_on(dev)
     sampler = ClockSampler(local)
     sampler.start()
-    steps = min(args.steps, 50)
+    steps = 100
     res = strong_c5(rank, world, dev, params, steps=steps)
     clocks = sampler.stop()
     if rank == 0:
@@ -697,7 +702,7 @@ def main():
     secondary, c5 = {}, None
     if not args.no_secondary and args.config == 2:
         try:
-            c5 = strong_c5(rank, world, dev, (A, pi, Bfull, codon), steps=min(args.steps, 50))
+            c5 = strong_c5(rank, world, dev, (A, pi, Bfull, codon))
         except Exception as e:                      # the headline line must not depend on it
             c5 = {"error": f"{type(e).__name__}: {e}"}
         try:
