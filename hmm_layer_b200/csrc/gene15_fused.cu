@@ -131,6 +131,8 @@ __device__ __forceinline__ void ring_read(const float* ring, int slot, const int
   }
 }
 
+__device__ __forceinline__ float lg2_fast(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }   // x normal
+
 __device__ __forceinline__ u64 sum7p(const u64 (&v)[7]) { return add2(add2(add2(v[0], v[1]), add2(v[2], v[3])), add2(add2(v[4], v[5]), v[6])); }
 __device__ __forceinline__ u64 sum15p2(const u64 (&v)[Q]) {
   return add2(add2(add2(add2(v[0], v[1]), add2(v[2], v[3])), add2(add2(v[4], v[5]), add2(v[6], v[7]))),
@@ -245,9 +247,6 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   // the neighbours' nucleotide codes and the previous position's pass-state emissions come by shuffles; the class
   // probabilities of the next step and the flags of the step after it are in flight while the current step is computed ----
   float* Eg = a.Ews + tile * (size_t)G * CS;
-  float keep[QP];
-#pragma unroll
-  for (int j = 0; j < QP; ++j) keep[j] = 0.f;
   {
     float elast[8];
 #pragma unroll
@@ -258,6 +257,11 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       if (code_cur == -2) code_cur = code_of(xc[3].w, f4.x, f4.y, f4.z, f4.w);
       if (code_next == -2) code_next = code_of(xn[3].w, f3.x, f3.y, f3.z, f3.w);
       mbar_wait(&S.bar, 0);   // codon tables
+#ifdef HMM_EMIT_UNROLL2
+#pragma unroll 2
+#else
+#pragma unroll 1
+#endif
       for (int k = 0; k < run; ++k) {
         const int i = wb + 32 * k + lane, ic = min(i, npos - 1), t = t_lo + ic;
         const bool active = i < npos;
@@ -366,12 +370,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
               for (int q = 0; q < 8; ++q) kc[7 + q] *= ((head ? e[7 + q] : ep[q]) * S.Aw[7 + q]);
             }
           }
-          if (head && i > 0) {
-#pragma unroll
-            for (int j = 0; j < QP; ++j) keep[j] = kc[j];   // completed behind the barrier with the previous warp's last emissions
-          } else {
-            coef_store(U, i, kc);
-          }
+          coef_store(U, i, kc);   // (a block's first row is completed behind the barrier with the previous warp's last emissions)
         }
         // rotate: step k + 1 becomes current; its flags (requested a step ago) give the code of the step after it
 #pragma unroll
@@ -390,6 +389,8 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
     if (lane == 0 && warp > 0 && wb < npos) {
       const float4 u0 = *reinterpret_cast<const float4*>(&S.carry[warp - 1][0]), u1 = *reinterpret_cast<const float4*>(&S.carry[warp - 1][4]);
       const float ep[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+      float keep[QP];
+      coef_load(smem_u32(U), wb, keep);
 #pragma unroll
       for (int q = 0; q < 8; ++q) keep[7 + q] *= (ep[q] * S.Aw[7 + q]);
       coef_store(U, wb, keep);
@@ -781,9 +782,9 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         float z = 0.f;
 #pragma unroll
         for (int j = 0; j < Q; ++j) { g[j] = fmaxf(g[j], 1e-37f); z += g[j]; }
-        const float lz = __log2f(z);
+        const float lz = lg2_fast(z);   // every g >= 1e-37: normal numbers, no denormal branch needed
 #pragma unroll
-        for (int j = 0; j < Q; ++j) stg[lane * Q + j] = fmaf(__log2f(g[j]) - lz, LN2F, ll_shift);
+        for (int j = 0; j < Q; ++j) stg[lane * Q + j] = fmaf(lg2_fast(g[j]) - lz, LN2F, ll_shift);
       }
       __syncwarp();
       const int cnt = min(32, npos - ib) * Q;
