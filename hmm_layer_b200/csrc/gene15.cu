@@ -375,16 +375,6 @@ __device__ __forceinline__ void warp_block_mm(const float* __restrict__ Ab, cons
   __syncwarp();
 }
 
-__device__ __forceinline__ void identity_block(float* blk, int lane) {
-  for (int i = lane; i < MAT; i += 32) {
-    const int r = i >> 4, c = i & 15;
-    float v;
-    if (r < Q) v = (c == r || c == 15) ? 1.f : 0.f;          // e_r | s' = 1
-    else v = (c < Q) ? 1.f : __int_as_float(0);              // column sums 1 | E = 0
-    blk[i] = v;
-  }
-}
-
 // copy one stored block (global, stride QP) into a staged block (shared, stride BST) by one half warp
 __device__ __forceinline__ void hw_stage_block(float* dst, const float* __restrict__ src, int hl) {
 #pragma unroll
@@ -585,23 +575,6 @@ __global__ void __launch_bounds__(32) shard_boundary_kernel(const float* __restr
 //                         groups in front / behind, and replays its own tiles: boundary vectors of every tile; the
 //                         log-likelihood of the whole sequence comes out of the forward fold over all ranks.
 // ------------------------------------------------------------------------------------------------------------
-constexpr int MAX_PEERS = 16;
-struct Peers {
-  float* blocks[MAX_PEERS];      // block table of every rank: [2][world][NB][256] (two step parities)
-  unsigned* flags[MAX_PEERS];    // flag table of every rank:  [2][world][NB]
-  int rank, world;
-  unsigned tag;                  // step number (same on every rank); parity selects the table half
-};
-
-__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
-}
-
 __global__ void __launch_bounds__(K1_THREADS) shard_product_kernel(const Args a, float* __restrict__ Gt, const Peers pr,
                                                                    float* __restrict__ block_out) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -1586,6 +1559,8 @@ __global__ void __launch_bounds__(64) params_grad_kernel(const float* __restrict
 int fused_capacity(int L);
 int fused_run_len(int L);
 int launch_fused(Args a, int NB, cudaStream_t st);
+int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
+                       unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st);
 static int g_fused_mode = 0; // 0: whenever the call qualifies, 1: never (two-kernel path)
 
 static int g_L = 0;          // 0: choose per call
@@ -1662,7 +1637,7 @@ static int choose_L(int NB, int T, bool full) {
 }
 
 struct Layout {
-  size_t Mh, Mt, bvf, bvr, llws, inf, inr, cnt, flg, Gt, gvf, gvr, Ews, total;
+  size_t Mh, Mt, bvf, bvr, llws, inf, inr, cnt, flg, Gt, gvf, gvr, gflg, bvflg, Ews, total;
 };
 static Layout layout(int NB, int P, int L) {
   Layout l;
@@ -1681,6 +1656,8 @@ static Layout layout(int NB, int P, int L) {
   l.Gt = off;   off = align_up(off + NG * MAT * sizeof(float), 256);
   l.gvf = off;  off = align_up(off + NG * QP * sizeof(float), 256);
   l.gvr = off;  off = align_up(off + NG * QP * sizeof(float), 256);
+  l.gflg = off; off = align_up(off + NG * sizeof(unsigned), 256);     // single-launch shard mode: group matrix published
+  l.bvflg = off; off = align_up(off + NG * sizeof(unsigned), 256);    //                          boundary vectors published
   l.Ews = off;  off = align_up(off + NP * G * ((size_t)L * QP + 4) * sizeof(float), 256);
   l.total = off;
   return l;
@@ -2247,6 +2224,57 @@ int shard_finalize_x(const float* inputs, int num_models, int batch, int T, int 
   return 0;
 }
 
+// ---- sequence sharding in ONE launch per step: the single-launch kernel with reducer CTAs (gene15_fused.cu) ----------
+// Chunk length for a shard of T positions: the tile CTAs and the reducer CTAs (one per 32 tiles) of every sequence must be
+// resident at once; 0 = the shard does not qualify (the 4-launch route above takes it).
+int shard_fused_chunk(int NB, int T) {
+  if (g_fused_mode == 1 || NB <= 0 || T <= 0) return 0;
+  static const bool env_off = getenv("HMM_B200_FUSED") && atoi(getenv("HMM_B200_FUSED")) == 0;
+  if (env_off) return 0;
+  const int sms = num_sms();
+  double best = 1e300;
+  int bestL = 0;
+  for (int L = (g_L > 0 ? g_L : FUSED_MIN_L); L <= (g_L > 0 ? g_L : MAX_L); ++L) {
+    const int cap = fused_capacity(L);
+    if (cap <= 0) break;
+    const int P = cdiv(cdiv(T, L), G), PG = cdiv(P, G);
+    const long long ctas = (long long)NB * (P + PG);
+    if (PG > G || ctas > cap) continue;
+    const double cost = (44.0 + 0.85 * L) * (ctas <= sms ? 1.0 : 1.36);   // choose_fused_L's model
+    if (cost < best) { best = cost; bestL = L; }
+  }
+  return bestL;
+}
+
+int shard_run_x(const float* inputs, int num_models, int batch, int T, int seq_off, int seq_total, const float* halo,
+                const float* A, const float* pi, const float* Bfull, const float* codon5, const float* hints, unsigned flags,
+                const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world, unsigned tag,
+                float* out_post, float* loglik, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  Args a{};
+  int rc = fill_args(a, inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags);
+  if (rc) return rc;
+  HMM_REQUIRE(inputs && A && pi && out_post, "genepred shard_run_x: null inputs / A / pi / posterior output");
+  HMM_REQUIRE(seq_off >= 0 && seq_total >= seq_off + T, "genepred shard_run_x: positions [%d, %d) outside a sequence of length %d",
+              seq_off, seq_off + T, seq_total);
+  HMM_REQUIRE(halo || (seq_off == 0 && seq_total == T), "genepred shard_run_x: a proper shard needs the 2+2 halo nucleotides");
+  HMM_REQUIRE(peer_blocks && peer_flags && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world && tag != 0,
+              "genepred shard_run_x: bad peer tables (world %d, rank %d, tag %u)", world, rank, tag);
+  const int NB = num_models * batch;
+  const int L = shard_fused_chunk(NB, T);
+  HMM_REQUIRE(L > 0, "genepred shard_run_x: %d sequences x %d positions do not fit one launch on this device (use shard_reduce_x / "
+              "shard_finalize_x; hmm_b200_genepred_shard_fused_chunk tells beforehand)", NB, T);
+  a.seq_off = seq_off; a.seq_total = seq_total; a.halo = halo;
+  set_L(a, L);
+  a.top_scan = 0;
+  Layout l;
+  rc = bind_workspace(a, l, NB, workspace, workspace_bytes, "genepred shard_run_x");
+  if (rc) return rc;
+  unsigned char* ws = static_cast<unsigned char*>(workspace);
+  a.out_post = out_post; a.out_alpha = nullptr; a.out_beta = nullptr; a.loglik = loglik;
+  return launch_fused_shard(a, NB, peer_blocks, peer_flags, rank, world, tag, reinterpret_cast<float*>(ws + l.Gt),
+                            reinterpret_cast<unsigned*>(ws + l.gflg), reinterpret_cast<unsigned*>(ws + l.bvflg), st);
+}
+
 int emission(const float* inputs, int num_models, int batch, int T, const float* Bfull, const float* codon5,
              const float* hints, unsigned flags, float* out_E, cudaStream_t st) {
   Args a{};
@@ -2481,6 +2509,20 @@ int hmm_b200_genepred_shard_finalize_x(const float* inputs, int num_models, int 
   return hmm::gene15::shard_finalize_x(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
                                        flags, all_blocks, block_flags, rank, world, step_tag, out_post, out_alpha, out_beta, loglik,
                                        workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_shard_fused_chunk(int num_models, int batch, int T_local) {
+  return hmm::gene15::shard_fused_chunk(num_models * batch, T_local);
+}
+
+int hmm_b200_genepred_shard_run_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
+                                  const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,
+                                  const float* end_hints, unsigned flags, const unsigned long long* peer_block_tables,
+                                  const unsigned long long* peer_flag_tables, int rank, int world, unsigned step_tag,
+                                  float* out_post, float* loglik, void* workspace, size_t workspace_bytes, void* stream) {
+  return hmm::gene15::shard_run_x(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
+                                  flags, peer_block_tables, peer_flag_tables, rank, world, step_tag, out_post, loglik, workspace,
+                                  workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -764,5 +764,35 @@ __device__ __forceinline__ HV scan_tiles_global(const float* Mt, int P, int p, c
   return hi == 0 ? snap : h;
 }
 
+__device__ __forceinline__ void identity_block(float* blk, int lane) {
+  for (int i = lane; i < MAT; i += 32) {
+    const int r = i >> 4, c = i & 15;
+    float v;
+    if (r < Q) v = (c == r || c == 15) ? 1.f : 0.f;          // e_r | s' = 1
+    else v = (c < Q) ? 1.f : __int_as_float(0);              // column sums 1 | E = 0
+    blk[i] = v;
+  }
+}
+
+
+// ---- sequence sharding: the block / flag tables of all ranks (peer memory) ----
+constexpr int MAX_PEERS = 16;
+struct Peers {
+  float* blocks[MAX_PEERS];      // block table of every rank: [2][world][NB][256] (two step parities)
+  unsigned* flags[MAX_PEERS];    // flag table of every rank:  [2][world][NB]
+  int rank, world;
+  unsigned tag;                  // step number (same on every rank); parity selects the table half
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+
+
 }  // namespace gene15
 }  // namespace hmm

@@ -84,6 +84,21 @@ struct FSmem {
   };
 };
 
+// Sequence-shard mode (multi-GPU): the launch carries extra "reducer" CTAs (blockIdx.x >= P), one per group of G tiles,
+// that do what shard_product_kernel + shard_scan_kernel do as kernels of their own (gene15.cu) while the tile CTAs wait:
+// group product, the shard's block into every rank's table over NVLink, the cross-rank / cross-group fold, the boundary
+// vectors of the group's tiles.  world == 0: not sharded (no reducers, the top-level scan of phase 4 instead).
+struct FShard {
+  int world, rank, PG;
+  unsigned tag;                // step tag of the peer tables: the same on every rank (local flags carry Args::tag, per launch)
+  float* Gt;                   // [NB][PG][256] group matrices
+  unsigned* gflg;              // [NB][PG] group matrix published
+  unsigned* bvflg;             // [NB][PG] boundary vectors of the group's tiles published
+  const float* my_blocks;      // this rank's block table half of the step: [world][NB][256]
+  const unsigned* my_flags;    // this rank's flag table half of the step:  [world][NB]
+  Peers pr;                    // the tables of every rank (peer stores)
+};
+
 __host__ __device__ inline size_t fused_u_floats(int L) {
   size_t y = (size_t)G * (L * QP + 4), h = (size_t)HEAP * MAT, c = (size_t)G * L * QP;
   size_t m = y > h ? y : h;
@@ -167,12 +182,19 @@ __device__ __forceinline__ void codon_factors_reg(const Args& a, const EmisSmem&
   for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
 }
 
-__global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
+__device__ void shard_reducer(const Args& a, const FShard& sh, FSmem& S, float* U);
+
+__global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard sh) {
   extern __shared__ __align__(128) unsigned char smem[];
   FSmem& S = *reinterpret_cast<FSmem*>(smem);
   float* U = reinterpret_cast<float*>(smem + ((sizeof(FSmem) + 127) / 128) * 128);
   const int L = a.L, T = a.T, CS = L * QP + 4, P = a.P;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
+  if ((int)blockIdx.x >= P) {      // shard mode: a reducer CTA
+    shard_reducer(a, sh, S, U);
+    return;
+  }
+  const bool seq_start = (a.seq_off == 0);   // position 0 of this launch is the start of the whole sequence
   const int p = blockIdx.x, n = blockIdx.y, m = n / a.batch;
   const int c0 = p * G, t_lo = c0 * L, npos = min(T, t_lo + G * L) - t_lo;
   const int nch = min(G, a.C - c0);
@@ -193,6 +215,8 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
   int code_prev = 4, code_cur = 4, code_next = 4;   // 4: outside the sequence, 1/4 each (kmer.py:27-33)
   // whether tile position i is a row of this sequence whose code a step of this warp needs
   auto row_of = [&](int i) { return reinterpret_cast<const float4*>(seq + (size_t)(t_lo + i) * SIN); };
+  // code of a position outside this launch's rows: the neighbour shard's nucleotide (halo) or 4 outside the sequence
+  auto edge = [&](int t) { return (a.halo != nullptr && t >= -2 && t < T + 2) ? nuc_code(a, n, t) : 4; };
   if (wact) {
     {
       const float4* row = row_of(min(wb + lane, npos - 1));
@@ -201,6 +225,8 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       f4 = __ldg(row + 4);
     }
     if (t_lo + wb + lane < T) code_cur = -2;                  // marks: compute from xc / f4 once they have landed
+    else code_cur = edge(t_lo + wb + lane);
+    if (t_lo + wb + 32 + lane >= T) code_next = edge(t_lo + wb + 32 + lane);
     if (t_lo + wb + 32 + lane < T) {                          // step 1 (or, behind the block, the two positions the 3-mer windows reach)
       const float4* row = row_of(wb + 32 + lane);
       xn[3] = __ldg(row + 3);
@@ -213,6 +239,8 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         const float* pp = seq + (size_t)t * SIN + 12;
         const float4 u = ldg4(pp), v = ldg4(pp + 4);
         code_prev = code_of(u.w, v.x, v.y, v.z, v.w);
+      } else if (lane >= 30) {
+        code_prev = edge(t);
       }
     }
   }
@@ -325,11 +353,11 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         }
         if (a.hints != nullptr) {
           const float* h = a.hints + (size_t)n * 2 * Q;
-          if (t == 0) {
+          if (a.seq_off + t == 0) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + q);
           }
-          if (t == T - 1) {
+          if (a.seq_off + t == a.seq_total - 1) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) e[q] *= __ldg(h + Q + q);
           }
@@ -349,14 +377,14 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
           const int ci = divL(a, i), c = c0 + ci;
           store_row16(Eg + (size_t)ci * CS + (i - ci * L) * QP, e, 0.f);
           {
-            const int ts = c * L + (c == 0 ? 1 : 0), t1 = min(T, (c + 1) * L) - 1;
+            const int ts = c * L + ((c == 0 && seq_start) ? 1 : 0), t1 = min(T, (c + 1) * L) - 1;
             if (t == ts) store_row16(S.EF[ci], e, 0.f);
             if (t == t1) store_row16(S.EL[ci], e, 0.f);
           }
           float kc[QP];
           kc[15] = 0.f;
           const bool head = (k == 0 && lane == 0);   // first position of the block: its predecessor belongs to another warp
-          if (t == 0) {
+          if (t == 0 && seq_start) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) kc[q] = e[q];   // position 0 keeps its emission row (no transition into it)
           } else {
@@ -378,7 +406,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
         xn[3] = f3;
         code_prev = code_cur;
         code_cur = code_next;
-        code_next = v2 ? code_of(f3.w, f4.x, f4.y, f4.z, f4.w) : 4;
+        code_next = v2 ? code_of(f3.w, f4.x, f4.y, f4.z, f4.w) : edge(t_lo + i + 64);
       }
     }
     if (lane == 0) {
@@ -410,7 +438,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
 #pragma unroll
     for (int j = 0; j < Q; ++j) vec[j] = pk2(j == ra ? 1.f : 0.f, j == rb ? 1.f : 0.f);   // chunks beyond the sequence: identity
     if (c < a.C) {
-      const bool first = (c == 0);
+      const bool first = (c == 0 && seq_start);
       const int t0 = c * L, t1 = min(T, t0 + L) - 1, ts = t0 + (first ? 1 : 0);
       const int ib = ci * L;
       float initA = 1.f, initB = 1.f;
@@ -526,7 +554,22 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
     if (a.dbg) a.dbg[(size_t)cta * 16 + 10] = gtimer();
   }
   const bool add_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
-  if (warp == 1) {
+  const bool sharded = sh.world > 0;
+  if (sharded) {
+    // shard mode: the group's reducer CTA publishes this tile's boundary vectors (cross-rank, cross-group, in-group folds)
+    if (warp == 1) {
+      const unsigned* f = sh.bvflg + (size_t)n * sh.PG + p / G;
+      if (lane == 0) while (ld_acquire_u32(f) != a.tag) __nanosleep(64);
+      __syncwarp();
+      const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
+      const float bvv = __ldcg(bv + hl);
+      const int bve = __float_as_int(__ldcg(bv + 15));
+      if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? bvv : 0.f; if (hl == 0) S.hef[1] = bve; }
+      else         { S.v.hvr[1][hl] = (hl < Q) ? bvv : 0.f; if (hl == 0) S.her[1] = bve; }
+      if (lane == 0) S.ll = __ldcg(a.llws + n);
+    }
+  }
+  if (!sharded && warp == 1) {
     for (int q = lane; q < P; q += 32) {
       const unsigned* f = a.flg + (size_t)n * P + q;
       while (ld_acquire_u32(f) != a.tag) __nanosleep(64);
@@ -534,7 +577,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
     if (a.dbg && lane == 0) a.dbg[(size_t)cta * 16 + 11] = gtimer();
   }
   __syncthreads();   // every tile of the sequence has published its matrix
-  const bool staged = P <= FSCAN;
+  const bool staged = !sharded && P <= FSCAN;
   if (staged) {
     // the sequence's tile matrices into shared memory with every load in flight at once: a scan step then costs a
     // shared-memory matvec instead of an L2 round trip
@@ -543,7 +586,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
     for (int i = tid; i < P * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
     __syncthreads();
   }
-  if (warp == 1) {
+  if (!sharded && warp == 1) {
     // top-level scan (TotalProbabilityCell.py:30-49 in scaled probability space): lanes 0-15 run pi . M_0 ... M_{P-1}
     // (snapshot on entering tile p; the end gives the log-likelihood), lanes 16-31 run M_{P-1} ... M_{p+1} . 1
     float llv = 0.f;
@@ -676,7 +719,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
       }
       float kap = sum15(av);
       int nsum = 0;
-      const bool first = (c == 0);
+      const bool first = (c == 0 && seq_start);
       int slot = 0;
       for (int ph = 0; ph < 2; ++ph) {
         const int u_lo = ph == 0 ? 0 : h, u_hi = ph == 0 ? h : len;
@@ -798,6 +841,121 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a) {
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// shard mode: reducer CTA of group g of sequence n (the bodies of shard_product_kernel / shard_scan_kernel, gene15.cu,
+// driven by tagged flags instead of kernel boundaries)
+// ------------------------------------------------------------------------------------------------------------
+__device__ __noinline__ void shard_reducer(const Args& a, const FShard& sh, FSmem& S, float* U) {
+  const int P = a.P, PG = sh.PG, NB = gridDim.y;
+  const int g = (int)blockIdx.x - P, n = blockIdx.y, m = n / a.batch;
+  const int tid = threadIdx.x, lane = tid & 31, hl = lane & 15, hi = lane >> 4;
+  const int nb = min(G, P - g * G);
+  float* H = U;   // heap order: leaves [G, 2G), root at 1
+  // 1. the group's tile matrices, as their CTAs publish them
+  for (int b = nb + (tid >> 5); b < G; b += FT / 32) identity_block(H + (G + b) * MAT, lane);
+  if (tid < nb) {
+    const unsigned* f = a.flg + (size_t)n * P + (size_t)g * G + tid;
+    while (ld_acquire_u32(f) != a.tag) __nanosleep(200);
+  }
+  __syncthreads();
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+    for (int i = tid; i < nb * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
+  }
+  __syncthreads();
+  // 2. group product -> Gt, tagged
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  if (tid < MAT / 4) reinterpret_cast<float4*>(sh.Gt + ((size_t)n * PG + g) * MAT)[tid] = reinterpret_cast<const float4*>(H + MAT)[tid];
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    st_release_u32(sh.gflg + (size_t)n * PG + g, a.tag);
+  }
+  // every reducer needs all group matrices of its sequence (cross-group fold); the last one also multiplies them
+  if (tid < PG) {
+    const unsigned* f = sh.gflg + (size_t)n * PG + tid;
+    while (ld_acquire_u32(f) != a.tag) __nanosleep(100);
+  }
+  __syncthreads();
+  if (g == PG - 1) {
+    // 3. the shard's block = product of the group matrices (tree over the next power of two), into every rank's table
+    int W = 1;
+    while (W < PG) W <<= 1;
+    if (PG > 1) {
+      const float4* src = reinterpret_cast<const float4*>(sh.Gt + (size_t)n * PG * MAT);
+      float4* dst = reinterpret_cast<float4*>(H + (size_t)W * MAT);
+      for (int i = tid; i < PG * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
+      for (int b = PG + (tid >> 5); b < W; b += FT / 32) identity_block(H + (W + b) * MAT, lane);
+      __syncthreads();
+      for (int np = W / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+    }
+    const float4* root = reinterpret_cast<const float4*>(H + MAT);
+    const size_t half = (size_t)(sh.tag & 1u) * sh.world * NB;
+    for (int i = tid; i < sh.world * (MAT / 4); i += FT) {
+      const int r = i / (MAT / 4), j = i - r * (MAT / 4);
+      reinterpret_cast<float4*>(sh.pr.blocks[r] + (half + (size_t)sh.rank * NB + n) * MAT)[j] = root[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < sh.world) st_release_sys_u32(sh.pr.flags[tid] + half + (size_t)sh.rank * NB + n, sh.tag);
+  }
+  __syncthreads();
+  // 4. stage the group matrices and this group's tile matrices (U: [gm: G blocks][tm: G blocks]), wait for the ranks' blocks
+  float* gm = U;
+  float* tm = U + (size_t)G * MAT;
+  {
+    const float4* gs = reinterpret_cast<const float4*>(sh.Gt + (size_t)n * PG * MAT);
+    for (int i = tid; i < PG * (MAT / 4); i += FT) reinterpret_cast<float4*>(gm)[i] = __ldcg(gs + i);
+    const float4* ts = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+    for (int i = tid; i < nb * (MAT / 4); i += FT) reinterpret_cast<float4*>(tm)[i] = __ldcg(ts + i);
+  }
+  if (tid < sh.world) {
+    const unsigned* f = sh.my_flags + (size_t)tid * NB + n;
+    while (ld_acquire_sys_u32(f) != sh.tag) __nanosleep(100);
+  }
+  __syncthreads();
+  for (int i = tid; i < sh.world * (MAT / 4); i += FT) {
+    const int r = i / (MAT / 4), j = i - r * (MAT / 4);
+    reinterpret_cast<float4*>(&S.tiles[r][0])[j] = __ldcg(reinterpret_cast<const float4*>(sh.my_blocks + ((size_t)r * NB + n) * MAT) + j);
+  }
+  __syncthreads();
+  if (tid >= 32) return;
+  // 5. folds (TotalProbabilityCell.py:30-49 across ranks, then groups, then this group's tiles): lanes 0-15 forward,
+  // lanes 16-31 backward; both halves run every loop to the longer trip count and commit only their own steps
+  HV h;
+  h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
+  h.e = 0;
+  HV mine = h;
+  for (int it = 0; it < sh.world; ++it) {
+    if (hi == 0 && it == sh.rank) mine = h;
+    const int s = hi == 0 ? it : sh.world - 1 - it;
+    matvec_raw(S.tiles[s], hl, hi, hi == 0 ? true : s > sh.rank, h);
+  }
+  {
+    const float tot = half_sum(h.v);
+    if (lane == 0) {   // every reducer of the sequence stores the same value: its own tiles read it behind its own flag
+      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+      a.llws[n] = ll;
+      if (g == 0 && a.loglik) a.loglik[n] = ll;
+    }
+    if (hi == 0) h = mine;
+  }
+  for (int it = 0; it < PG; ++it) {
+    const int s = hi == 0 ? it : PG - 1 - it;
+    matvec_raw(gm + (size_t)s * MAT, hl, hi, hi == 0 ? s < g : s > g, h);
+  }
+  float* vout = (hi == 0 ? a.bvf : a.bvr) + ((size_t)n * P + (size_t)g * G) * QP;
+  for (int it = 0; it < nb; ++it) {
+    const int s = hi == 0 ? it : nb - 1 - it;
+    vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
+    matvec_raw(tm + (size_t)s * MAT, hl, hi, true, h);
+  }
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) st_release_u32(sh.bvflg + (size_t)n * PG + g, a.tag);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
 enum { SLOT_FUSED = 23 };
@@ -839,7 +997,33 @@ int launch_fused(Args a, int NB, cudaStream_t st) {
   if (rc) return rc;
   a.run = fused_run_len(a.L);
   a.tag = next_tag();
-  fused_kernel<<<dim3(a.P, NB), FT, smem, st>>>(a);
+  FShard sh{};
+  fused_kernel<<<dim3(a.P, NB), FT, smem, st>>>(a, sh);
+  HMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// shard mode: P tile CTAs + PG reducer CTAs per sequence, all resident at once.  Local flags (tiles, groups, boundary
+// vectors) carry a per-launch tag, the peer tables the step tag (the same on every rank); nothing is cleared between steps.
+int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
+                       unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st) {
+  const size_t smem = fused_smem_bytes(a.L);
+  int rc = ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem);
+  if (rc) return rc;
+  a.run = fused_run_len(a.L);
+  a.tag = next_tag();   // local flags (tiles, groups, boundary vectors): unique per launch whatever the workspace held before
+  FShard sh{};
+  sh.world = world; sh.rank = rank; sh.PG = cdiv(a.P, G); sh.tag = tag;
+  sh.Gt = Gt; sh.gflg = gflg; sh.bvflg = bvflg;
+  for (int r = 0; r < world; ++r) {
+    sh.pr.blocks[r] = reinterpret_cast<float*>(static_cast<uintptr_t>(peer_blocks[r]));
+    sh.pr.flags[r] = reinterpret_cast<unsigned*>(static_cast<uintptr_t>(peer_flags[r]));
+  }
+  sh.pr.rank = rank; sh.pr.world = world; sh.pr.tag = tag;
+  const size_t half = (size_t)(tag & 1u) * world * NB;
+  sh.my_blocks = sh.pr.blocks[rank] + half * MAT;
+  sh.my_flags = sh.pr.flags[rank] + half;
+  fused_kernel<<<dim3(a.P + sh.PG, NB), FT, smem, st>>>(a, sh);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

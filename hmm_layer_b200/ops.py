@@ -431,6 +431,32 @@ def genepred_shard_finalize_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, co
     return res
 
 
+def genepred_shard_fused_chunk(k, B, T_local, device=None):
+    """Chunk length of the one-launch shard step for (k, B, T_local) on `device`, 0 when the shard does not fit one launch."""
+    lib = _lib.load()
+    with torch.cuda.device(device if device is not None else torch.cuda.current_device()):
+        return int(lib.hmm_b200_genepred_shard_fused_chunk(k, B, T_local))
+
+
+def genepred_shard_run_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, workspace, step_tag, peer_blocks, peer_flags,
+                         rank, world, end_hints=None, training=False, no_loglik=False, out=None):
+    """The whole sharded step in ONE launch (include/hmm_b200.h, hmm_b200_genepred_shard_run_x): posterior of the local
+    positions + log-likelihood of the whole sequences; the blocks travel by peer stores inside the kernel."""
+    lib = _lib.load()
+    k, B, T, inputs, halo, A, pi, Bfull, codon, end_hints = _shard_common(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, end_hints)
+    dev = inputs.device
+    with torch.cuda.device(dev):
+        out = out or {}
+        res = {"post": out.get("post") if out.get("post") is not None else torch.empty((k, B, T, 15), dtype=torch.float32, device=dev),
+               "loglik": out.get("loglik") if out.get("loglik") is not None else torch.empty((k, B), dtype=torch.float32, device=dev)}
+        flags = (TRAINING if training else 0) | (NO_LOGLIK if no_loglik else 0)
+        _lib.check(lib.hmm_b200_genepred_shard_run_x(
+            _ptr(inputs), k, B, T, seq_off, seq_total, _ptr(halo), _ptr(A), _ptr(pi), _ptr(Bfull), _ptr(codon), _ptr(end_hints),
+            flags, peer_blocks, peer_flags, rank, world, step_tag, _ptr(res["post"]), _ptr(res["loglik"]),
+            _ptr(workspace), workspace.numel(), _stream()))
+    return res
+
+
 def genepred_emission(inputs, Bfull, codon, end_hints=None, training=False):
     lib = _lib.load()
     if inputs.dim() != 4 or inputs.shape[-1] != 20:

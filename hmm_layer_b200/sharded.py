@@ -76,11 +76,13 @@ def sequence_sharded_run(shard, halo, seq_off, seq_total, A, pi, Bfull, codon, g
 class ShardContext:
     """Persistent state of a rank for repeated sequence-sharded evaluations of one shard shape: the zeroed workspace, the
     step counter and -- when the ranks' devices can map each other's memory (torch symmetric memory: CUDA VMM handles
-    over NVLink) -- the block / flag tables every rank's kernels store into directly.  4 launches per step, no
-    collective call on the data path; without peer mapping the blocks travel by ONE NCCL all-gather between the two
-    halves (5 launches).  `run` must be called by every rank of the group, in lockstep."""
+    over NVLink) -- the block / flag tables every rank's kernels store into directly: ONE launch per step when the
+    shard's tiles fit the device at once and only the posterior is wanted (hmm_b200_genepred_shard_run_x), else 4 launches;
+    no collective call on the data path either way (a rank may take either route, the tables are the same).  Without peer
+    mapping the blocks travel by ONE NCCL all-gather between the two halves (5 launches).  `run` must be called by every
+    rank of the group, in lockstep."""
 
-    def __init__(self, shard, halo, seq_off, seq_total, A, pi, Bfull, codon, group=None, use_peer_memory=True):
+    def __init__(self, shard, halo, seq_off, seq_total, A, pi, Bfull, codon, group=None, use_peer_memory=True, one_launch=True):
         import ctypes
         from . import _lib
         if not dist.is_initialized():
@@ -94,6 +96,7 @@ class ShardContext:
         self.ws = torch.zeros(max(_lib.load().hmm_b200_genepred_workspace_size(k, B, T), 256), dtype=torch.uint8, device=dev)
         self.tag = 0
         self.peer_blocks = self.peer_flags = None
+        self.one_launch = False
         n_blk, n_flg = 2 * self.world * self.NB * 256, 2 * self.world * self.NB
         self.n_blk = n_blk
         self.exchange = "NCCL all_gather_into_tensor (1 KB per rank and sequence) between the two kernel pairs"
@@ -115,6 +118,9 @@ class ShardContext:
                 dist.barrier(group)            # every rank's table is zero before anybody stores into it
                 self.exchange = "peer stores over NVLink into symmetric memory, inside the kernels (no collective call)"
                 self.launches_per_step = 4
+                if one_launch and ops.genepred_shard_fused_chunk(k, B, T, dev) > 0:
+                    self.one_launch = True
+                    self.launches_per_step = 1    # posterior-only steps; alpha / beta requests take the 4-launch route
             except Exception as e:             # no peer mapping on this system: the NCCL route
                 self.peer_blocks = self.peer_flags = None
                 self.exchange += f" [peer memory unavailable: {type(e).__name__}: {e}]"
@@ -125,6 +131,10 @@ class ShardContext:
         A, pi, Bfull, codon = self.params
         self.tag += 1
         tag = self.tag
+        if self.one_launch and want_post and not (want_alpha or want_beta):
+            return ops.genepred_shard_run_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
+                                            self.peer_blocks, self.peer_flags, self.rank, self.world, end_hints=end_hints,
+                                            training=training, no_loglik=no_loglik, out=out)
         if self.peer_blocks is not None:
             ops.genepred_shard_reduce_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
                                         peer_blocks=self.peer_blocks, peer_flags=self.peer_flags, rank=self.rank, world=self.world,

@@ -1,7 +1,8 @@
 """Tests that need at least two GPUs (skipped otherwise; `gpurun --gpus 2`):
   * the sequence-sharded path on REAL ranks over NCCL / NVLink: every shard's posterior against the fp64 oracle, for
-    both exchange routes (peer stores into symmetric memory inside the kernels; the NCCL all-gather fallback) and the
-    plain three-call route (shard_reduce / all_gather / shard_finalize);
+    the exchange routes (peer stores into symmetric memory inside the kernels, as ONE launch per step where the shard
+    fits and as four launches; the NCCL all-gather fallback) and the plain three-call route (shard_reduce / all_gather /
+    shard_finalize);
   * one process driving two devices in turn (the library's per-device state)."""
 import os
 import socket
@@ -37,8 +38,8 @@ def _rank_main(rank, world, port, B, T, seed, outdir, chunk_len):
     shard, halo, off, tot = sharded.slice_with_halo(x, rank, world)
     shard, halo = shard.to(dev), halo.to(dev)
     res = {}
-    for name, peer in (("peer", True), ("nccl", False)):
-        ctx = sharded.ShardContext(shard, halo, off, tot, A, pi, Bfull, tab, use_peer_memory=peer)
+    for name, peer, one in (("peer", True, True), ("peer4", True, False), ("nccl", False, False)):
+        ctx = sharded.ShardContext(shard, halo, off, tot, A, pi, Bfull, tab, use_peer_memory=peer, one_launch=one)
         for _ in range(3):                      # repeated steps: tags, table halves, the self-resetting counter
             r = ctx.run(shard, want_post=True)
         res[name] = (r["post"].cpu().numpy(), r["loglik"].cpu().numpy(), ctx.exchange, ctx.launches_per_step)
@@ -65,7 +66,7 @@ def test_sequence_sharded_on_real_ranks_matches_oracle(tmp_path, B, T, chunk_len
     ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
     parts = [dict(np.load(tmp_path / f"rank{r}.npz")) for r in range(world)]
     print(parts[0]["info"])
-    for route in ("peer", "nccl", "plain"):
+    for route in ("peer", "peer4", "nccl", "plain"):
         post = np.concatenate([p[f"{route}_0"] for p in parts], axis=2)
         for p in parts:
             np.testing.assert_array_equal(p[f"{route}_1"], parts[0][f"{route}_1"])      # the same log-likelihood on every rank

@@ -112,3 +112,67 @@ def test_two_level_boundary_scan_long_tile_lists():
     same = run_gpu(x, A, pi, Bfull, tab, want_post=True)                # default chunk length: single-level scan
     np.testing.assert_allclose(same["loglik"], got["loglik"], rtol=1e-6)
     np.testing.assert_allclose(np.exp(same["post"]), np.exp(got["post"]), atol=2e-5)
+
+
+def _virtual_tables(world, NB):
+    """Block / flag tables of `world` virtual ranks on this device (the layout ShardContext keeps in symmetric memory:
+    [2 halves][world][NB] blocks of 256 floats, then the same of flags), as ctypes pointer arrays in rank order."""
+    import ctypes
+    n_blk, n_flg = 2 * world * NB * 256, 2 * world * NB
+    tables = [torch.zeros(n_blk + n_flg, dtype=torch.float32, device="cuda") for _ in range(world)]
+    arr = ctypes.c_ulonglong * world
+    return tables, arr(*[t.data_ptr() for t in tables]), arr(*[t.data_ptr() + 4 * n_blk for t in tables])
+
+
+@pytest.mark.parametrize("B,T,world,hints", [(2, 4000, 2, False), (1, 40_001, 3, True), (3, 2500, 8, False), (1, 150_000, 2, False),
+                                             (2, 64, 4, True), (2, 1000, 1, False)])
+def test_one_launch_shard_step_matches_oracle(B, T, world, hints):
+    """hmm_b200_genepred_shard_run_x on virtual ranks of one device: the four-launch route first publishes every rank's
+    block for the step tag (so no launch waits for a kernel that is not running), then each rank's one-launch step of the
+    SAME tag re-publishes its block and folds ranks -> groups -> tiles inside the kernel.  150 000 positions on two ranks =
+    several tile groups per rank (the cross-group fold); T = 64 on 4 ranks = shards shorter than a chunk."""
+    x = syn.gene_inputs(1, B, T, seed=700 + T, p_n=0.01)
+    A, pi, Bfull, tab = gene_params(pi_random=True)
+    eh = None
+    if hints:
+        rng = np.random.default_rng(5)
+        eh = rng.uniform(0.2, 1.0, size=(1, B, 2, 15)).astype(np.float32)
+    ref = oracle_gene(x.numpy(), A, pi, Bfull, tab, end_hints=eh)
+    Ad, pid, Bd, tabd = dev(A), dev(pi), dev(Bfull), ops.prepare_codon(dev(tab))
+    ehd = dev(eh) if eh is not None else None
+    xd = x.cuda()
+    shards = [sharded.slice_with_halo(xd, r, world) for r in range(world)]
+    tables, pb, pf = _virtual_tables(world, B)
+    import hmm_layer_b200._lib as L
+    lib = L.load()
+    posts, lls = [None] * world, [None] * world
+    for tag in (1, 2, 3):                       # both table halves, stale flags of tag - 2 in place
+        wss = []
+        for r, (s, h, off, tot) in enumerate(shards):
+            ws = torch.zeros(max(lib.hmm_b200_genepred_workspace_size(1, B, s.shape[2]), 256), dtype=torch.uint8, device="cuda")
+            ops.genepred_shard_reduce_x(s, h, off, tot, Ad, pid, Bd, tabd, ws, tag, peer_blocks=pb, peer_flags=pf, rank=r,
+                                        world=world, end_hints=ehd)
+            wss.append(ws)
+        for r, (s, h, off, tot) in enumerate(shards):
+            if ops.genepred_shard_fused_chunk(1, B, s.shape[2]) == 0:
+                pytest.skip("shard does not fit one launch on this device")
+            res = ops.genepred_shard_run_x(s, h, off, tot, Ad, pid, Bd, tabd, wss[r], tag, pb, pf, r, world, end_hints=ehd)
+            posts[r], lls[r] = res["post"], res["loglik"]
+        torch.cuda.synchronize()
+    got = {"post": np.concatenate([p.cpu().numpy() for p in posts], axis=2), "loglik": lls[0].cpu().numpy()}
+    for ll in lls[1:]:
+        assert np.array_equal(ll.cpu().numpy(), got["loglik"])
+    check_post(got, ref)
+
+
+def test_one_launch_shard_step_rejects_what_does_not_fit():
+    from hmm_layer_b200._lib import HmmB200Error
+    assert ops.genepred_shard_fused_chunk(1, 1, 2_000_000) == 0
+    B, T = 1, 2_000_000
+    x = torch.zeros((1, B, T, 20), device="cuda")
+    A, pi, Bfull, tab = gene_params()
+    tables, pb, pf = _virtual_tables(1, B)
+    import hmm_layer_b200._lib as L
+    ws = torch.zeros(L.load().hmm_b200_genepred_workspace_size(1, B, T), dtype=torch.uint8, device="cuda")
+    with pytest.raises(HmmB200Error, match="do not fit one launch"):
+        ops.genepred_shard_run_x(x, None, 0, T, dev(A), dev(pi), dev(Bfull), ops.prepare_codon(dev(tab)), ws, 1, pb, pf, 0, 1)
