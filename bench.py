@@ -382,7 +382,7 @@ def run_config4(args, rank, world, local):
         dist.destroy_process_group()
 
 
-def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None):
+def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None, one_launch=True):
     """Device-resident forward+posterior of ONE sequence of T positions cut into `world` contiguous shards (one per rank;
     world == 1: the chunked scan on one GPU).  Returns (ms per step: max over ranks, log-likelihood, launches per step,
     name of the exchange).  Must be called by every rank of the group."""
@@ -396,7 +396,7 @@ def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None):
         nbuf = max(2, min(8, int(2 * 126e6 * world / (140.0 * T)) + 1))
     xs = [shard.to(dev).clone() for _ in range(nbuf)]
     halo_d = halo.to(dev)
-    ctx = sharded.ShardContext(xs[0], halo_d, off, tot, A, pi, Bfull, codon) if world > 1 else None
+    ctx = sharded.ShardContext(xs[0], halo_d, off, tot, A, pi, Bfull, codon, one_launch=one_launch) if world > 1 else None
 
     def step(i):
         if world == 1:

@@ -79,7 +79,7 @@ def load():
     lib.hmm_b200_genepred_shard_finalize_x.argtypes = [c_fp, ci, ci, ci, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_uint,
                                                        c_fp, c_fp, ci, ci, ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp,
                                                        ctypes.c_size_t, c_fp]
-    lib.hmm_b200_genepred_shard_fused_chunk.argtypes = [ci, ci, ci]
+    lib.hmm_b200_genepred_shard_fused_chunk.argtypes = [ci, ci, ci, ci]
     lib.hmm_b200_genepred_shard_run_x.argtypes = [c_fp, ci, ci, ci, ci, ci, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_uint,
                                                   c_fp, c_fp, ci, ci, ctypes.c_uint, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
     lib.hmm_b200_dense_workspace_size.restype = ctypes.c_size_t

@@ -1667,7 +1667,7 @@ static Layout layout_for(int NB, int T, int L) { return layout(NB, cdiv(cdiv(T, 
 // Chunk length of the single-launch path: every tile of the call must be resident at once (a tile waits inside the
 // kernel for the other tiles of its sequence), so the smallest chunk length whose tile count fits the device; 0 = the
 // call does not qualify.  A tuning override (set_tuning) is honoured when it fits.
-constexpr int FUSED_MIN_L = 12, FUSED_MAX_TILES_PER_SEQ = 64;
+constexpr int FUSED_MIN_L = 12, FUSED_MAX_TILES_PER_SEQ = 64, FUSED_SCAN_SLOTS = 24;   // (FSCAN of gene15_fused.cu)
 static int choose_fused_L(int NB, int T) {
   if (g_fused_mode == 1) return 0;
   static const bool env_off = getenv("HMM_B200_FUSED") && atoi(getenv("HMM_B200_FUSED")) == 0;
@@ -2225,10 +2225,10 @@ int shard_finalize_x(const float* inputs, int num_models, int batch, int T, int 
 }
 
 // ---- sequence sharding in ONE launch per step: the single-launch kernel with reducer CTAs (gene15_fused.cu) ----------
-// Chunk length for a shard of T positions: the tile CTAs and the reducer CTAs (one per 32 tiles) of every sequence must be
-// resident at once; 0 = the shard does not qualify (the 4-launch route above takes it).
-int shard_fused_chunk(int NB, int T) {
-  if (g_fused_mode == 1 || NB <= 0 || T <= 0) return 0;
+// Chunk length for a shard of T positions: the tile CTAs and the reducer CTAs (one per 32 tiles + one) of every sequence must
+// be resident at once; 0 = the shard does not qualify (the 4-launch route above takes it).
+int shard_fused_chunk(int NB, int T, int world) {
+  if (g_fused_mode == 1 || NB <= 0 || T <= 0 || world <= 0 || world > MAX_PEERS) return 0;
   static const bool env_off = getenv("HMM_B200_FUSED") && atoi(getenv("HMM_B200_FUSED")) == 0;
   if (env_off) return 0;
   const int sms = num_sms();
@@ -2238,8 +2238,8 @@ int shard_fused_chunk(int NB, int T) {
     const int cap = fused_capacity(L);
     if (cap <= 0) break;
     const int P = cdiv(cdiv(T, L), G), PG = cdiv(P, G);
-    const long long ctas = (long long)NB * (P + PG);
-    if (PG > G || ctas > cap) continue;
+    const long long ctas = (long long)NB * (P + PG + 1);   // tiles, group reducers, the block reducer
+    if (PG > G || world + PG > FUSED_SCAN_SLOTS || ctas > cap) continue;   // (ranks' blocks + group matrices share the scan slots)
     const double cost = (44.0 + 0.85 * L) * (ctas <= sms ? 1.0 : 1.36);   // choose_fused_L's model
     if (cost < best) { best = cost; bestL = L; }
   }
@@ -2260,7 +2260,7 @@ int shard_run_x(const float* inputs, int num_models, int batch, int T, int seq_o
   HMM_REQUIRE(peer_blocks && peer_flags && world > 0 && world <= MAX_PEERS && rank >= 0 && rank < world && tag != 0,
               "genepred shard_run_x: bad peer tables (world %d, rank %d, tag %u)", world, rank, tag);
   const int NB = num_models * batch;
-  const int L = shard_fused_chunk(NB, T);
+  const int L = shard_fused_chunk(NB, T, world);
   HMM_REQUIRE(L > 0, "genepred shard_run_x: %d sequences x %d positions do not fit one launch on this device (use shard_reduce_x / "
               "shard_finalize_x; hmm_b200_genepred_shard_fused_chunk tells beforehand)", NB, T);
   a.seq_off = seq_off; a.seq_total = seq_total; a.halo = halo;
@@ -2511,8 +2511,8 @@ int hmm_b200_genepred_shard_finalize_x(const float* inputs, int num_models, int 
                                        workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
-int hmm_b200_genepred_shard_fused_chunk(int num_models, int batch, int T_local) {
-  return hmm::gene15::shard_fused_chunk(num_models * batch, T_local);
+int hmm_b200_genepred_shard_fused_chunk(int num_models, int batch, int T_local, int world) {
+  return hmm::gene15::shard_fused_chunk(num_models * batch, T_local, world);
 }
 
 int hmm_b200_genepred_shard_run_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,

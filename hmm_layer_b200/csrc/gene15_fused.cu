@@ -34,7 +34,6 @@ namespace gene15 {
 
 typedef unsigned long long u64;
 constexpr int FT = 256;        // threads per CTA
-constexpr int FRUN = 5;        // longest run of positions per emission thread (L <= 40)
 constexpr int FRING = 6;       // emission rows in flight per recursion thread (an L2 round trip is ~4 recursion steps)
 constexpr int FSCAN = 24;      // tile matrices of one sequence staged in shared memory for the top-level scan
 
@@ -72,6 +71,7 @@ struct FSmem {
   unsigned long long bar;   // mbarrier: the codon tables have landed
   float ll;
   float pad_[1];
+  int edge_hi[4];        // codes of positions T, T + 1 (the next shard's first nucleotides, 4 outside the sequence); 2 pads
   union {                // phase 1: last pass-state emissions of every run; phases 4-5: boundary vectors of the tree nodes
     float carry[FT / 32][8];
     struct { float hvf[HEAP][QP]; float hvr[HEAP][QP]; } v;
@@ -84,10 +84,12 @@ struct FSmem {
   };
 };
 
-// Sequence-shard mode (multi-GPU): the launch carries extra "reducer" CTAs (blockIdx.x >= P), one per group of G tiles,
-// that do what shard_product_kernel + shard_scan_kernel do as kernels of their own (gene15.cu) while the tile CTAs wait:
-// group product, the shard's block into every rank's table over NVLink, the cross-rank / cross-group fold, the boundary
-// vectors of the group's tiles.  world == 0: not sharded (no reducers, the top-level scan of phase 4 instead).
+// Sequence-shard mode (multi-GPU): the launch carries extra "reducer" CTAs (blockIdx.x >= P) that do what
+// shard_product_kernel + shard_scan_kernel do as kernels of their own (gene15.cu) while the tile CTAs wait.  One per group
+// of G tiles: the group's product tree, then -- once the ranks' blocks are there -- the fold over ranks and groups and the
+// down-sweep of its tree to the boundary vectors of its tiles.  One more per sequence: the product of the group matrices
+// = the shard's block, stored into every rank's table over NVLink.  world == 0: not sharded (no reducers, the top-level
+// scan of phase 4 instead).
 struct FShard {
   int world, rank, PG;
   unsigned tag;                // step tag of the peer tables: the same on every rank (local flags carry Args::tag, per launch)
@@ -182,7 +184,76 @@ __device__ __forceinline__ void codon_factors_reg(const Args& a, const EmisSmem&
   for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
 }
 
-__device__ void shard_reducer(const Args& a, const FShard& sh, FSmem& S, float* U);
+// Down-sweep of a 32-leaf product tree in heap order (gene15.cu, finalize_kernel): from the vectors at the root (forward
+// vector entering the tree's span in hvf[1] / hef[1], backward vector behind it in hvr[1] / her[1]) to those of every leaf.
+// First half of the CTA's warps forward, second half backward; a half warp handles one node.
+__device__ __forceinline__ void down_sweep(FSmem& S, const float* H, long long* dbg, int cta) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
+  (void)dbg; (void)cta;
+  {
+    const int wpd = FT >> 6;
+    const int dir = warp >= wpd ? 1 : 0;
+    const int wd = warp - dir * wpd;
+    const int row = min(hl, Q - 1);
+    for (int lo = 1; lo < G; lo <<= 1) {
+      for (int k0 = lo + 2 * wd; k0 < 2 * lo; k0 += 2 * wpd) {
+        const int k = k0 + hi;
+        const bool act = k < 2 * lo;
+        const int kc = act ? k : k0;
+        if (dir == 0) {
+          const float v = S.v.hvf[kc][hl];
+          const int e = S.hef[kc];
+          const float* blk = H + (size_t)(2 * kc) * MAT;
+          const float u = (hl < Q) ? v * blk[row * QP + 15] : 0.f;
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float s = half_sum(u);
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < Q; ++j) {
+            const float uj = __shfl_sync(0xffffffffu, u, j, 16);
+            const float cc = blk[j * QP + hl];
+            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.v.hvf[2 * k][hl] = v;
+            S.v.hvf[2 * k + 1][hl] = (hl < Q) ? (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.hef[2 * k] = e; S.hef[2 * k + 1] = e + clamp_exp(ex) + Eb; }
+          }
+        } else {
+          const float v = S.v.hvr[kc][hl];
+          const int e = S.her[kc];
+          const float* blk = H + (size_t)(2 * kc + 1) * MAT;
+          const float sp = blk[15 + row * QP];
+          const int Eb = __float_as_int(blk[MAT - 1]);
+          const float u = (hl < Q) ? v : 0.f;
+          const float s = half_sum((hl < Q) ? blk[15 * QP + hl] * v : 0.f);
+          const float* rp = blk + row * QP;
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int j = 0; j < QP; ++j) {
+            const int kk = (hl + j) & 15;
+            const float uj = __shfl_sync(0xffffffffu, u, kk, 16);
+            const float cc = rp[kk];
+            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
+          }
+          const int ex = pexp(s);
+          if (act) {
+            S.v.hvr[2 * k + 1][hl] = v;
+            S.v.hvr[2 * k][hl] = (hl < Q) ? sp * (acc0 + acc1) * pow2neg(ex) : 0.f;
+            if (hl == 0) { S.her[2 * k + 1] = e; S.her[2 * k] = e + clamp_exp(ex) + Eb; }
+          }
+        }
+      }
+      if (dir == 0) named_barrier_sync(2, wpd * 32); else named_barrier_sync(3, wpd * 32);
+#ifdef HMM_FUSED_FINE_MARKS
+      if (dbg && tid == 0) dbg[(size_t)(4096 + cta) * 16 + 31 - __clz(lo)] = clock_fenced();
+#endif
+    }
+  }
+}
+
+__device__ __forceinline__ void shard_reducer(const Args& a, const FShard& sh);
 
 __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard sh) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -191,7 +262,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
   const int L = a.L, T = a.T, CS = L * QP + 4, P = a.P;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
   if ((int)blockIdx.x >= P) {      // shard mode: a reducer CTA
-    shard_reducer(a, sh, S, U);
+    shard_reducer(a, sh);
     return;
   }
   const bool seq_start = (a.seq_off == 0);   // position 0 of this launch is the start of the whole sequence
@@ -252,6 +323,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
       mbar_expect_tx(&S.bar, (unsigned)(T5_FLOATS * sizeof(float)));
       bulk_g2s(&S.sp.T5[0][0][0], a.codon5, (unsigned)(T5_FLOATS * sizeof(float)), &S.bar);
     }
+    if (tid >= 32 && tid < 34) S.edge_hi[tid - 32] = edge(T + tid - 32);
     if (tid < 23) {
       float aw;
       if (tid < 7) aw = __ldg(Am + SRC1[tid] * Q + tid);
@@ -406,7 +478,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
         xn[3] = f3;
         code_prev = code_cur;
         code_cur = code_next;
-        code_next = v2 ? code_of(f3.w, f4.x, f4.y, f4.z, f4.w) : edge(t_lo + i + 64);
+        code_next = v2 ? code_of(f3.w, f4.x, f4.y, f4.z, f4.w) : ((unsigned)(t_lo + i + 64 - T) < 2u ? S.edge_hi[t_lo + i + 64 - T] : 4);
       }
     }
     if (lane == 0) {
@@ -560,6 +632,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
     if (warp == 1) {
       const unsigned* f = sh.bvflg + (size_t)n * sh.PG + p / G;
       if (lane == 0) while (ld_acquire_u32(f) != a.tag) __nanosleep(64);
+      if (a.dbg && lane == 0) a.dbg[(size_t)cta * 16 + 11] = gtimer();
       __syncwarp();
       const float* bv = (hi == 0 ? a.bvf : a.bvr) + tile * QP;
       const float bvv = __ldcg(bv + hl);
@@ -634,68 +707,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
 #ifdef HMM_FUSED_FINE_MARKS
   if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 9] = clock_fenced();
 #endif
-  {
-    // down-sweep (gene15.cu, finalize_kernel): first half of the warps forward, second half backward
-    const int wpd = FT >> 6;
-    const int dir = warp >= wpd ? 1 : 0;
-    const int wd = warp - dir * wpd;
-    const int row = min(hl, Q - 1);
-    for (int lo = 1; lo < G; lo <<= 1) {
-      for (int k0 = lo + 2 * wd; k0 < 2 * lo; k0 += 2 * wpd) {
-        const int k = k0 + hi;
-        const bool act = k < 2 * lo;
-        const int kc = act ? k : k0;
-        if (dir == 0) {
-          const float v = S.v.hvf[kc][hl];
-          const int e = S.hef[kc];
-          const float* blk = H + (size_t)(2 * kc) * MAT;
-          const float u = (hl < Q) ? v * blk[row * QP + 15] : 0.f;
-          const int Eb = __float_as_int(blk[MAT - 1]);
-          const float s = half_sum(u);
-          float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-          for (int j = 0; j < Q; ++j) {
-            const float uj = __shfl_sync(0xffffffffu, u, j, 16);
-            const float cc = blk[j * QP + hl];
-            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
-          }
-          const int ex = pexp(s);
-          if (act) {
-            S.v.hvf[2 * k][hl] = v;
-            S.v.hvf[2 * k + 1][hl] = (hl < Q) ? (acc0 + acc1) * pow2neg(ex) : 0.f;
-            if (hl == 0) { S.hef[2 * k] = e; S.hef[2 * k + 1] = e + clamp_exp(ex) + Eb; }
-          }
-        } else {
-          const float v = S.v.hvr[kc][hl];
-          const int e = S.her[kc];
-          const float* blk = H + (size_t)(2 * kc + 1) * MAT;
-          const float sp = blk[15 + row * QP];
-          const int Eb = __float_as_int(blk[MAT - 1]);
-          const float u = (hl < Q) ? v : 0.f;
-          const float s = half_sum((hl < Q) ? blk[15 * QP + hl] * v : 0.f);
-          const float* rp = blk + row * QP;
-          float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-          for (int j = 0; j < QP; ++j) {
-            const int kk = (hl + j) & 15;
-            const float uj = __shfl_sync(0xffffffffu, u, kk, 16);
-            const float cc = rp[kk];
-            if (j & 1) acc1 = fmaf(uj, cc, acc1); else acc0 = fmaf(uj, cc, acc0);
-          }
-          const int ex = pexp(s);
-          if (act) {
-            S.v.hvr[2 * k + 1][hl] = v;
-            S.v.hvr[2 * k][hl] = (hl < Q) ? sp * (acc0 + acc1) * pow2neg(ex) : 0.f;
-            if (hl == 0) { S.her[2 * k + 1] = e; S.her[2 * k] = e + clamp_exp(ex) + Eb; }
-          }
-        }
-      }
-      if (dir == 0) named_barrier_sync(2, wpd * 32); else named_barrier_sync(3, wpd * 32);
-#ifdef HMM_FUSED_FINE_MARKS
-      if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 31 - __clz(lo)] = clock_fenced();
-#endif
-    }
-  }
+  down_sweep(S, H, a.dbg, cta);
   __syncthreads();   // boundary vectors complete, tree dead: U becomes Y
   HMM_MARK(cta, 7);
 
@@ -841,119 +853,177 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// shard mode: reducer CTA of group g of sequence n (the bodies of shard_product_kernel / shard_scan_kernel, gene15.cu,
-// driven by tagged flags instead of kernel boundaries)
+// shard mode: the reducer CTAs of sequence n (the work of shard_product_kernel / shard_scan_kernel, gene15.cu, driven by
+// tagged flags instead of kernel boundaries).  blockIdx.x in [P, P + PG): the reducer of tile group g;  P + PG: the
+// sequence's block reducer (product of the group matrices -> every rank's table).
 // ------------------------------------------------------------------------------------------------------------
-__device__ __noinline__ void shard_reducer(const Args& a, const FShard& sh, FSmem& S, float* U) {
-  const int P = a.P, PG = sh.PG, NB = gridDim.y;
-  const int g = (int)blockIdx.x - P, n = blockIdx.y, m = n / a.batch;
-  const int tid = threadIdx.x, lane = tid & 31, hl = lane & 15, hi = lane >> 4;
-  const int nb = min(G, P - g * G);
-  float* H = U;   // heap order: leaves [G, 2G), root at 1
-  // 1. the group's tile matrices, as their CTAs publish them
-  for (int b = nb + (tid >> 5); b < G; b += FT / 32) identity_block(H + (G + b) * MAT, lane);
-  if (tid < nb) {
-    const unsigned* f = a.flg + (size_t)n * P + (size_t)g * G + tid;
-    while (ld_acquire_u32(f) != a.tag) __nanosleep(200);
-  }
-  __syncthreads();
-  {
-    const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
-    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
-    for (int i = tid; i < nb * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
-  }
-  __syncthreads();
-  // 2. group product -> Gt, tagged
-  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
-  if (tid < MAT / 4) reinterpret_cast<float4*>(sh.Gt + ((size_t)n * PG + g) * MAT)[tid] = reinterpret_cast<const float4*>(H + MAT)[tid];
-  __syncthreads();
-  if (tid == 0) {
-    __threadfence();
-    st_release_u32(sh.gflg + (size_t)n * PG + g, a.tag);
-  }
-  // every reducer needs all group matrices of its sequence (cross-group fold); the last one also multiplies them
-  if (tid < PG) {
-    const unsigned* f = sh.gflg + (size_t)n * PG + tid;
-    while (ld_acquire_u32(f) != a.tag) __nanosleep(100);
-  }
-  __syncthreads();
-  if (g == PG - 1) {
-    // 3. the shard's block = product of the group matrices (tree over the next power of two), into every rank's table
-    int W = 1;
-    while (W < PG) W <<= 1;
-    if (PG > 1) {
+#define RMARK(k) do { if (a.dbg && tid == 0) a.dbg[(size_t)cta * 16 + (k)] = gtimer(); } while (0)
+
+// Both reducers run their body twice: pass 0 on identity blocks, with no wait and nothing published, while the tiles are
+// still at work -- it pulls the instructions of the pass that counts into the SM's instruction caches (a reducer is the
+// only CTA of the launch that runs this code on its SM, and it runs it once: cold, the chain tiles -> vectors took about
+// twice as long).
+
+// product of the sequence's group matrices = the shard's block, stored with the step tag into the table of every rank
+__device__ __forceinline__ void shard_block_reducer(const Args& a, const FShard& sh, float* H) {
+  const int PG = sh.PG, NB = gridDim.y, n = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  RMARK(0);
+  int W = 1;
+  while (W < PG) W <<= 1;
+  for (int pass = 0; pass < 2; ++pass) {
+    const bool real = pass == 1;
+    for (int b = (real ? PG : 0) + (tid >> 5); b < W; b += FT / 32) identity_block(H + (W + b) * MAT, lane);   // leaves [W, 2W), root at 1
+    if (real) {
+      if (tid < PG) {
+        const unsigned* f = sh.gflg + (size_t)n * PG + tid;
+        while (ld_acquire_u32(f) != a.tag) __nanosleep(40);
+      }
+      __syncthreads();
+      RMARK(1);
       const float4* src = reinterpret_cast<const float4*>(sh.Gt + (size_t)n * PG * MAT);
       float4* dst = reinterpret_cast<float4*>(H + (size_t)W * MAT);
       for (int i = tid; i < PG * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
-      for (int b = PG + (tid >> 5); b < W; b += FT / 32) identity_block(H + (W + b) * MAT, lane);
-      __syncthreads();
-      for (int np = W / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
     }
-    const float4* root = reinterpret_cast<const float4*>(H + MAT);
-    const size_t half = (size_t)(sh.tag & 1u) * sh.world * NB;
-    for (int i = tid; i < sh.world * (MAT / 4); i += FT) {
-      const int r = i / (MAT / 4), j = i - r * (MAT / 4);
-      reinterpret_cast<float4*>(sh.pr.blocks[r] + (half + (size_t)sh.rank * NB + n) * MAT)[j] = root[j];
-    }
-    __threadfence_system();
     __syncthreads();
-    if (tid < sh.world) st_release_sys_u32(sh.pr.flags[tid] + half + (size_t)sh.rank * NB + n, sh.tag);
+    for (int np = W / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
   }
-  __syncthreads();
-  // 4. stage the group matrices and this group's tile matrices (U: [gm: G blocks][tm: G blocks]), wait for the ranks' blocks
-  float* gm = U;
-  float* tm = U + (size_t)G * MAT;
-  {
-    const float4* gs = reinterpret_cast<const float4*>(sh.Gt + (size_t)n * PG * MAT);
-    for (int i = tid; i < PG * (MAT / 4); i += FT) reinterpret_cast<float4*>(gm)[i] = __ldcg(gs + i);
-    const float4* ts = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
-    for (int i = tid; i < nb * (MAT / 4); i += FT) reinterpret_cast<float4*>(tm)[i] = __ldcg(ts + i);
-  }
-  if (tid < sh.world) {
-    const unsigned* f = sh.my_flags + (size_t)tid * NB + n;
-    while (ld_acquire_sys_u32(f) != sh.tag) __nanosleep(100);
-  }
-  __syncthreads();
+  RMARK(2);
+  const float4* root = reinterpret_cast<const float4*>(H + MAT);
+  const size_t half = (size_t)(sh.tag & 1u) * sh.world * NB;
   for (int i = tid; i < sh.world * (MAT / 4); i += FT) {
-    const int r = i / (MAT / 4), j = i - r * (MAT / 4);
-    reinterpret_cast<float4*>(&S.tiles[r][0])[j] = __ldcg(reinterpret_cast<const float4*>(sh.my_blocks + ((size_t)r * NB + n) * MAT) + j);
+    const int r = i >> 6, j = i & 63;
+    reinterpret_cast<float4*>(sh.pr.blocks[r] + (half + (size_t)sh.rank * NB + n) * MAT)[j] = root[j];
+  }
+  // the barrier puts every store of the CTA in front of the releasing threads' stores (a release is cumulative)
+  __syncthreads();
+  if (tid < sh.world) st_release_sys_u32(sh.pr.flags[tid] + half + (size_t)sh.rank * NB + n, sh.tag);
+  RMARK(3);
+}
+
+__device__ __forceinline__ void shard_reducer(const Args& a, const FShard& sh) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  FSmem& S = *reinterpret_cast<FSmem*>(smem);
+  float* H = reinterpret_cast<float*>(smem + ((sizeof(FSmem) + 127) / 128) * 128);   // heap order: leaves [G, 2G), root at 1
+  const int P = a.P, PG = sh.PG, NB = gridDim.y;
+  const int g = (int)blockIdx.x - P, n = blockIdx.y, m = n / a.batch;
+  if (g == PG) { shard_block_reducer(a, sh, H); return; }
+  const int tid = threadIdx.x, lane = tid & 31, hl = lane & 15, hi = lane >> 4;
+  const int nb = min(G, P - g * G);
+  const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+  RMARK(0);
+  for (int pass = 0; pass < 2; ++pass) {
+    const bool real = pass == 1;
+    // 1. the group's tile matrices, as their CTAs publish them
+    for (int b = (real ? nb : 0) + (tid >> 5); b < G; b += FT / 32) identity_block(H + (G + b) * MAT, lane);
+    if (real) {
+      // (a warp takes tiles w, w + 8, ...: one lane polls the tile's flag, the warp requests its matrix -- the copies run
+      // while the slower tiles are still awaited)
+      const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+      float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+      for (int b = tid >> 5; b < nb; b += FT / 32) {
+        if (lane == 0) {
+          const unsigned* f = a.flg + (size_t)n * P + (size_t)g * G + b;
+          while (ld_acquire_u32(f) != a.tag) __nanosleep(32);
+        }
+        __syncwarp();
+        cp_async16m(dst + b * (MAT / 4) + lane, src + b * (MAT / 4) + lane);
+        cp_async16m(dst + b * (MAT / 4) + 32 + lane, src + b * (MAT / 4) + 32 + lane);
+      }
+      cp_async_commit_m();
+      cp_async_wait_m<0>();
+      RMARK(1);
+    }
+    __syncthreads();
+    // 2. the group's product tree (kept: the down-sweep of step 5 walks it) -> its root to Gt, tagged
+    for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+    int nranks = 1, ngroups = 2;   // pass 0: three identity blocks
+    if (real) {
+      nranks = sh.world; ngroups = PG;
+      if (tid < MAT / 4) reinterpret_cast<float4*>(sh.Gt + ((size_t)n * PG + g) * MAT)[tid] = reinterpret_cast<const float4*>(H + MAT)[tid];
+      __syncthreads();
+      if (tid == 0) st_release_u32(sh.gflg + (size_t)n * PG + g, a.tag);   // (cumulative over the CTA's stores: the barrier)
+      RMARK(2);
+      // 3. the other groups' matrices (S.tiles[world + s]) and the ranks' blocks (S.tiles[r]) as they arrive
+      if (tid < PG && tid != g) {
+        const unsigned* f = sh.gflg + (size_t)n * PG + tid;
+        while (ld_acquire_u32(f) != a.tag) __nanosleep(40);
+      }
+      __syncthreads();
+      RMARK(3);
+      const float4* gs = reinterpret_cast<const float4*>(sh.Gt + (size_t)n * PG * MAT);
+      float4* dst = reinterpret_cast<float4*>(&S.tiles[sh.world][0]);
+      for (int i = tid; i < PG * (MAT / 4); i += FT)
+        if ((i >> 6) != g) dst[i] = __ldcg(gs + i);
+      if (tid < sh.world) {
+        const unsigned* f = sh.my_flags + (size_t)tid * NB + n;
+        while (ld_acquire_sys_u32(f) != sh.tag) __nanosleep(40);
+      }
+      __syncthreads();
+      RMARK(4);
+      for (int i = tid; i < sh.world * (MAT / 4); i += FT) {
+        const int r = i >> 6, j = i & 63;
+        reinterpret_cast<float4*>(&S.tiles[r][0])[j] = __ldcg(reinterpret_cast<const float4*>(sh.my_blocks + ((size_t)r * NB + n) * MAT) + j);
+      }
+    } else if (tid < 96) {
+      identity_block(&S.tiles[tid >> 5][0], lane);
+    }
+    __syncthreads();
+    // 4. folds (TotalProbabilityCell.py:30-49 across ranks, then across this rank's groups), ONE loop: lanes 0-15 forward,
+    // lanes 16-31 backward; both halves run to the longer trip count and commit only their own steps
+    if (tid < 32) {
+      const int rank = real ? sh.rank : 0, gg = real ? g : 0;
+      HV h;
+      h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
+      h.e = 0;
+      HV mine = h;
+      auto ranks_done = [&]() {   // the forward half has crossed every rank: the log-likelihood; back to this rank's entry
+        const float tot = half_sum(h.v);
+        if (real && lane == 0) {   // every reducer of the sequence stores the same value: its own tiles read it behind its own flag
+          const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+          a.llws[n] = ll;
+          if (g == 0 && a.loglik) a.loglik[n] = ll;
+        }
+        if (hi == 0) h = mine;
+      };
+      const int nf = nranks + ngroups - 1;
+      for (int it = 0; it < nf; ++it) {
+        int slot;
+        bool commit;
+        if (it < nranks) {
+          if (hi == 0 && it == rank) mine = h;
+          slot = hi == 0 ? it : nranks - 1 - it;
+          commit = hi == 0 ? true : slot > rank;
+        } else {
+          if (it == nranks) ranks_done();
+          const int s = hi == 0 ? it - nranks : ngroups - 1 - (it - nranks);   // forward: groups 0 .. g-1; backward: PG-1 .. g+1
+          commit = hi == 0 ? s < gg : s > gg;
+          slot = nranks + s;
+        }
+        matvec_raw(S.tiles[slot], hl, hi, commit, h);
+      }
+      if (ngroups == 1) ranks_done();
+      if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? h.v : 0.f; if (hl == 0) S.hef[1] = h.e; }
+      else         { S.v.hvr[1][hl] = (hl < Q) ? h.v : 0.f; if (hl == 0) S.her[1] = h.e; }
+    }
+    __syncthreads();
+    if (real) RMARK(5);
+    // 5. down the group's tree to the vectors of its tiles
+    down_sweep(S, H, nullptr, 0);
+    __syncthreads();
+  }
+  for (int i = tid; i < nb * QP; i += FT) {
+    const int b = i >> 4, c = i & 15;
+    const size_t o = ((size_t)n * P + (size_t)g * G + b) * QP + c;
+    a.bvf[o] = c < Q ? S.v.hvf[G + b][c] : __int_as_float(S.hef[G + b]);
+    a.bvr[o] = c < Q ? S.v.hvr[G + b][c] : __int_as_float(S.her[G + b]);
   }
   __syncthreads();
-  if (tid >= 32) return;
-  // 5. folds (TotalProbabilityCell.py:30-49 across ranks, then groups, then this group's tiles): lanes 0-15 forward,
-  // lanes 16-31 backward; both halves run every loop to the longer trip count and commit only their own steps
-  HV h;
-  h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
-  h.e = 0;
-  HV mine = h;
-  for (int it = 0; it < sh.world; ++it) {
-    if (hi == 0 && it == sh.rank) mine = h;
-    const int s = hi == 0 ? it : sh.world - 1 - it;
-    matvec_raw(S.tiles[s], hl, hi, hi == 0 ? true : s > sh.rank, h);
-  }
-  {
-    const float tot = half_sum(h.v);
-    if (lane == 0) {   // every reducer of the sequence stores the same value: its own tiles read it behind its own flag
-      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
-      a.llws[n] = ll;
-      if (g == 0 && a.loglik) a.loglik[n] = ll;
-    }
-    if (hi == 0) h = mine;
-  }
-  for (int it = 0; it < PG; ++it) {
-    const int s = hi == 0 ? it : PG - 1 - it;
-    matvec_raw(gm + (size_t)s * MAT, hl, hi, hi == 0 ? s < g : s > g, h);
-  }
-  float* vout = (hi == 0 ? a.bvf : a.bvr) + ((size_t)n * P + (size_t)g * G) * QP;
-  for (int it = 0; it < nb; ++it) {
-    const int s = hi == 0 ? it : nb - 1 - it;
-    vout[(size_t)s * QP + hl] = (hl < Q) ? h.v : __int_as_float(h.e);
-    matvec_raw(tm + (size_t)s * MAT, hl, hi, true, h);
-  }
-  __threadfence();
-  __syncwarp();
-  if (lane == 0) st_release_u32(sh.bvflg + (size_t)n * PG + g, a.tag);
+  if (tid == 0) st_release_u32(sh.bvflg + (size_t)n * PG + g, a.tag);
+  RMARK(6);
 }
+#undef RMARK
 
 // ------------------------------------------------------------------------------------------------------------
 // host side
@@ -1003,7 +1073,7 @@ int launch_fused(Args a, int NB, cudaStream_t st) {
   return 0;
 }
 
-// shard mode: P tile CTAs + PG reducer CTAs per sequence, all resident at once.  Local flags (tiles, groups, boundary
+// shard mode: P tile CTAs + PG group reducers + 1 block reducer per sequence, all resident at once.  Local flags (tiles, groups, boundary
 // vectors) carry a per-launch tag, the peer tables the step tag (the same on every rank); nothing is cleared between steps.
 int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
                        unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st) {
@@ -1014,6 +1084,7 @@ int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, co
   a.tag = next_tag();   // local flags (tiles, groups, boundary vectors): unique per launch whatever the workspace held before
   FShard sh{};
   sh.world = world; sh.rank = rank; sh.PG = cdiv(a.P, G); sh.tag = tag;
+  HMM_REQUIRE(sh.PG <= G && world + sh.PG <= FSCAN, "genepred shard step: %d tile groups among %d ranks exceed the reducer's staging", sh.PG, world);
   sh.Gt = Gt; sh.gflg = gflg; sh.bvflg = bvflg;
   for (int r = 0; r < world; ++r) {
     sh.pr.blocks[r] = reinterpret_cast<float*>(static_cast<uintptr_t>(peer_blocks[r]));
@@ -1023,7 +1094,7 @@ int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, co
   const size_t half = (size_t)(tag & 1u) * world * NB;
   sh.my_blocks = sh.pr.blocks[rank] + half * MAT;
   sh.my_flags = sh.pr.flags[rank] + half;
-  fused_kernel<<<dim3(a.P + sh.PG, NB), FT, smem, st>>>(a, sh);
+  fused_kernel<<<dim3(a.P + sh.PG + 1, NB), FT, smem, st>>>(a, sh);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -431,11 +431,12 @@ def genepred_shard_finalize_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, co
     return res
 
 
-def genepred_shard_fused_chunk(k, B, T_local, device=None):
-    """Chunk length of the one-launch shard step for (k, B, T_local) on `device`, 0 when the shard does not fit one launch."""
+def genepred_shard_fused_chunk(k, B, T_local, world, device=None):
+    """Chunk length of the one-launch shard step for (k, B, T_local) among `world` ranks on `device`, 0 when the shard
+    does not fit one launch."""
     lib = _lib.load()
     with torch.cuda.device(device if device is not None else torch.cuda.current_device()):
-        return int(lib.hmm_b200_genepred_shard_fused_chunk(k, B, T_local))
+        return int(lib.hmm_b200_genepred_shard_fused_chunk(k, B, T_local, world))
 
 
 def genepred_shard_run_x(inputs, halo, seq_off, seq_total, A, pi, Bfull, codon, workspace, step_tag, peer_blocks, peer_flags,

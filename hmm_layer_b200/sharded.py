@@ -118,7 +118,7 @@ class ShardContext:
                 dist.barrier(group)            # every rank's table is zero before anybody stores into it
                 self.exchange = "peer stores over NVLink into symmetric memory, inside the kernels (no collective call)"
                 self.launches_per_step = 4
-                if one_launch and ops.genepred_shard_fused_chunk(k, B, T, dev) > 0:
+                if one_launch and ops.genepred_shard_fused_chunk(k, B, T, self.world, dev) > 0:
                     self.one_launch = True
                     self.launches_per_step = 1    # posterior-only steps; alpha / beta requests take the 4-launch route
             except Exception as e:             # no peer mapping on this system: the NCCL route

@@ -306,14 +306,14 @@ int hmm_b200_genepred_shard_finalize_x(const float* inputs, int num_models, int 
 
 /* Sequence sharding in ONE launch per step (the single-launch kernel of hmm_b200_genepred_run with reducer CTAs): every
  * tile of the shard computes emission, chunk matrices and its tile matrix; one extra CTA per 32 tiles multiplies them,
- * the last one stores the shard's block into every rank's table (peer stores over NVLink, tagged flags as
+ * one more multiplies those and stores the shard's block into every rank's table (peer stores over NVLink, tagged flags as
  * shard_reduce_x), all of them wait for the other ranks' blocks and fold ranks -> groups -> tiles (the role of
  * TotalProbabilityCell.py:30-49 across devices) while the tile CTAs wait inside the kernel; then recursion and output
  * as in the unsharded kernel.  Posterior (+ log-likelihood) only, peer tables required; interchangeable rank by rank
  * with shard_reduce_x + shard_finalize_x of the same step (same tables, same tags).
  * hmm_b200_genepred_shard_fused_chunk: the chunk length the launch would use, 0 when the shard does not fit one launch
  * on the current device (all of its CTAs must be resident at once) -- then shard_run_x fails with HMM_B200_EINVAL. */
-int hmm_b200_genepred_shard_fused_chunk(int num_models, int batch, int T_local);
+int hmm_b200_genepred_shard_fused_chunk(int num_models, int batch, int T_local, int world);
 
 int hmm_b200_genepred_shard_run_x(const float* inputs, int num_models, int batch, int T_local, int seq_off, int seq_total,
                                   const float* halo, const float* A, const float* pi, const float* Bfull, const float* codon5,

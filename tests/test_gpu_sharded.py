@@ -154,7 +154,7 @@ def test_one_launch_shard_step_matches_oracle(B, T, world, hints):
                                         world=world, end_hints=ehd)
             wss.append(ws)
         for r, (s, h, off, tot) in enumerate(shards):
-            if ops.genepred_shard_fused_chunk(1, B, s.shape[2]) == 0:
+            if ops.genepred_shard_fused_chunk(1, B, s.shape[2], world) == 0:
                 pytest.skip("shard does not fit one launch on this device")
             res = ops.genepred_shard_run_x(s, h, off, tot, Ad, pid, Bd, tabd, wss[r], tag, pb, pf, r, world, end_hints=ehd)
             posts[r], lls[r] = res["post"], res["loglik"]
@@ -167,7 +167,7 @@ def test_one_launch_shard_step_matches_oracle(B, T, world, hints):
 
 def test_one_launch_shard_step_rejects_what_does_not_fit():
     from hmm_layer_b200._lib import HmmB200Error
-    assert ops.genepred_shard_fused_chunk(1, 1, 2_000_000) == 0
+    assert ops.genepred_shard_fused_chunk(1, 1, 2_000_000, 1) == 0
     B, T = 1, 2_000_000
     x = torch.zeros((1, B, T, 20), device="cuda")
     A, pi, Bfull, tab = gene_params()
