@@ -18,7 +18,7 @@ EXPORTS = [
     "hmm_b200_genepred_params", "hmm_b200_genepred_params_grad",
     "hmm_b200_genepred_emission", "hmm_b200_emission_general", "hmm_b200_genepred_shard_reduce", "hmm_b200_genepred_shard_finalize",
     "hmm_b200_genepred_shard_reduce_x", "hmm_b200_genepred_shard_finalize_x",
-    "hmm_b200_genepred_shard_fused_chunk", "hmm_b200_genepred_shard_run_x",
+    "hmm_b200_genepred_shard_fused_chunk", "hmm_b200_genepred_shard_run_x", "hmm_b200_genepred_run_noalloc",
     "hmm_b200_dense_workspace_size", "hmm_b200_dense_run", "hmm_b200_dense_workspace_size_onehot", "hmm_b200_dense_run_onehot", "hmm_b200_cell_step",
 ]
 
@@ -51,6 +51,8 @@ def load():
     lib.hmm_b200_genepred_prepare_codon.argtypes = [c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_run.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp, c_fp, c_fp,
                                           ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp, ctypes.c_size_t, c_fp]
+    lib.hmm_b200_genepred_run_noalloc.argtypes = [c_fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_fp, c_fp, c_fp, c_fp, c_fp,
+                                                  ctypes.c_uint, c_fp, c_fp, c_fp, c_fp, c_fp]
     lib.hmm_b200_genepred_host_scratch_size.restype = ctypes.c_size_t
     lib.hmm_b200_genepred_host_scratch_size.argtypes = [ctypes.c_int] * 3
     lib.hmm_b200_genepred_run_host.argtypes = lib.hmm_b200_genepred_run.argtypes

@@ -2366,6 +2366,56 @@ int params_grad(const float* tk, const float* sk, const float* ek, int num_model
   return 0;
 }
 
+// ---- forward + posterior without any allocation: the workspace is a static device array ----------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every device
+// that loads the library holds HMM_B200_NOALLOC_SCRATCH_BYTES of it until the process exits.  In host code the array's
+// name is only a stand-in: its device address is looked up once per device (that device current) and handed to run().
+}  // namespace gene15
+}  // namespace hmm
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[HMM_B200_NOALLOC_SCRATCH_BYTES];
+
+namespace hmm {
+namespace gene15 {
+
+static int noalloc_scratch(void** out) {
+  static void* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  HMM_CUDA_OK(cudaGetDevice(&dev));
+  HMM_REQUIRE(dev >= 0 && dev < kMaxDevices, "genepred_run_noalloc: device %d beyond the %d this library keeps state for", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lk(state_mutex());
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    HMM_CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // the address on the CURRENT device
+    HMM_REQUIRE(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "genepred_run_noalloc: bad scratch address %p", p);
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+int run_noalloc(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
+                const float* codon5, const float* hints, unsigned flags, float* out_post, float* out_alpha, float* out_beta,
+                float* loglik, cudaStream_t st) {
+  HMM_REQUIRE(num_models > 0 && batch > 0 && T > 0, "genepred_run_noalloc: num_models, batch and T must be positive (got %d,%d,%d)",
+              num_models, batch, T);
+  const size_t need = workspace_size(num_models, batch, T);
+  if (need > (size_t)HMM_B200_NOALLOC_SCRATCH_BYTES) {
+    set_error("genepred_run_noalloc: %d x %d sequences of %d positions need %zu bytes of scratch, the static array holds %zu "
+              "(HMM_B200_NOALLOC_SCRATCH_BYTES); use hmm_b200_genepred_run with a caller-owned workspace",
+              num_models, batch, T, need, (size_t)HMM_B200_NOALLOC_SCRATCH_BYTES);
+    return HMM_B200_EWORKSPACE;
+  }
+  void* ws = nullptr;
+  int rc = noalloc_scratch(&ws);
+  if (rc) return rc;
+  // The array keeps the last call's contents.  What must start at zero -- the per-sequence arrival counters of the
+  // two-kernel route -- is cleared by run() on `st` in every call that uses them; the flags of the single-launch route
+  // carry a per-call tag and need no clearing; everything else is written before it is read.
+  return run(inputs, num_models, batch, T, A, pi, Bfull, codon5, hints, flags, out_post, out_alpha, out_beta, loglik, ws,
+             (size_t)HMM_B200_NOALLOC_SCRATCH_BYTES, st);
+}
+
 }  // namespace gene15
 }  // namespace hmm
 
@@ -2523,6 +2573,13 @@ int hmm_b200_genepred_shard_run_x(const float* inputs, int num_models, int batch
   return hmm::gene15::shard_run_x(inputs, num_models, batch, T_local, seq_off, seq_total, halo, A, pi, Bfull, codon5, end_hints,
                                   flags, peer_block_tables, peer_flag_tables, rank, world, step_tag, out_post, loglik, workspace,
                                   workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int hmm_b200_genepred_run_noalloc(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
+                                  const float* Bfull, const float* codon5, const float* end_hints, unsigned flags,
+                                  float* out_post, float* out_alpha, float* out_beta, float* loglik, void* stream) {
+  return hmm::gene15::run_noalloc(inputs, num_models, batch, T, A, pi, Bfull, codon5, end_hints, flags, out_post, out_alpha,
+                                  out_beta, loglik, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -321,6 +321,22 @@ int hmm_b200_genepred_shard_run_x(const float* inputs, int num_models, int batch
                                   const unsigned long long* peer_flag_tables, int rank, int world, unsigned step_tag,
                                   float* out_post, float* loglik, void* workspace, size_t workspace_bytes, void* stream);
 
+/* hmm_b200_genepred_run without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, outputs and results as hmm_b200_genepred_run; the scratch
+ * is a static device array inside the library (HMM_B200_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library
+ * until the process exits), whose address is resolved once per device.  The call itself issues no cudaMalloc / cudaFree
+ * or allocating library routine.
+ * Limit: hmm_b200_genepred_workspace_size(num_models, batch, T) <= HMM_B200_NOALLOC_SCRATCH_BYTES (about 110 000
+ * positions in total); larger problems fail with HMM_B200_EWORKSPACE and a message in hmm_b200_last_error().
+ * Every call on a device shares the one array: calls that overlap on the GPU (two streams, two threads) race and give
+ * wrong results -- serialise them (one stream, or events).  The array keeps the previous call's contents; the call
+ * clears what has to start at zero on `stream`. */
+#define HMM_B200_NOALLOC_SCRATCH_BYTES (64u << 20)
+int hmm_b200_genepred_run_noalloc(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi,
+                                  const float* Bfull, const float* codon5, const float* end_hints, unsigned flags,
+                                  float* out_post, float* out_alpha, float* out_beta, float* loglik, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
