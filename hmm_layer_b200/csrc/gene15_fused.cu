@@ -1067,6 +1067,11 @@ int launch_fused(Args a, int NB, cudaStream_t st) {
   if (rc) return rc;
   a.run = fused_run_len(a.L);
   a.tag = next_tag();
+  // Under CUDA graph capture the tag is baked into the graph and every replay would find its own flags of the previous
+  // replay: a captured launch clears the tile flags first (a memset node in front of the kernel node).
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { (void)cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+  if (cap == cudaStreamCaptureStatusActive) HMM_CUDA_OK(cudaMemsetAsync(a.flg, 0, (size_t)NB * a.P * sizeof(unsigned), st));
   FShard sh{};
   fused_kernel<<<dim3(a.P, NB), FT, smem, st>>>(a, sh);
   HMM_CUDA_OK(cudaGetLastError());

@@ -82,3 +82,35 @@ def test_fused_repeated_calls_are_bit_identical_and_config2_full_size():
     ref = oracle_gene(x.numpy(), A, pi, Bfull, tab)
     rep = check_post(got, ref)
     assert rep["argmax_mismatch"] == 0
+
+
+def test_run_under_cuda_graph_capture_replays_correctly():
+    """hmm_b200_genepred_run captured into a CUDA graph and replayed on new inputs (the single-launch kernel's flags carry a
+    per-launch tag that a graph would replay unchanged: a captured launch clears them first) -- posterior and
+    log-likelihood of every replay equal the eager call's, for the single-launch route and the two-kernel route."""
+    A, pi, Bfull, tab = [dev(v) for v in gene_params(pi_random=True)]
+    tab5 = ops.prepare_codon(tab)
+    B, T = 4, 6000
+    xs = [syn.gene_inputs(1, B, T, seed=40 + i, p_n=0.01).cuda() for i in range(3)]
+    for fused in (True, False):
+        ops.set_fused(fused)
+        try:
+            eager = []
+            for x in xs:
+                r = ops.genepred_run(x, A, pi, Bfull, tab5, want_post=True)
+                eager.append((r["post"].clone(), r["loglik"].clone()))
+            static_x = xs[0].clone()
+            out = {"post": torch.empty((1, B, T, 15), device="cuda")}
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                r = ops.genepred_run(static_x, A, pi, Bfull, tab5, want_post=True, out=out)
+            for rep in range(2):
+                for x, (post, ll) in zip(xs, eager):
+                    static_x.copy_(x)
+                    g.replay()
+                    torch.cuda.synchronize()
+                    assert torch.equal(r["post"], post), (fused, rep)
+                    assert torch.equal(r["loglik"], ll), (fused, rep)
+        finally:
+            ops.set_fused(True)
