@@ -1954,7 +1954,11 @@ static int g_host_slices = 0;   // 0 = by batch size; HMM_HOST_SLICES overrides 
 static int host_slice_len(int batch) {
   static const int env = getenv("HMM_HOST_SLICES") ? atoi(getenv("HMM_HOST_SLICES")) : 0;
   int ns = env > 0 ? env : g_host_slices;
-  if (ns <= 0) ns = batch >= 16 ? 4 : (batch >= 4 ? 2 : 1);   // measured on config 2: 2, 4 and 8 slices within 1 %
+  // measured on config 2 (profiles/r2n_e2e_breakdown.txt, r2n_direct.txt): 2 to 6 slices, uniform or ramped towards the
+  // ends, land within 2 % (0.735-0.755 ms), 8 are slower (every cross-stream hop costs microseconds).  Letting the kernels
+  // store straight into the caller's pinned buffers instead of the download copies does not pay either: the stores run at
+  // 51 GB/s alone but starve the concurrent upload (copy-engine traffic both ways arbitrates better): 0.725 ms at best.
+  if (ns <= 0) ns = batch >= 16 ? 4 : (batch >= 4 ? 2 : 1);
   if (ns > batch) ns = batch;
   return cdiv(batch, ns);
 }
