@@ -44,6 +44,14 @@ def _compute_device(inputs, cell):
     return torch.device("cuda", torch.cuda.current_device())
 
 
+def _set_plain(module, name, value):
+    """module.name = value for a derived quantity that is a plain attribute (not a Parameter / buffer / submodule)"""
+    if name in module._parameters or name in module._buffers or name in module._modules:
+        setattr(module, name, value)
+    else:
+        module.__dict__[name] = value
+
+
 def _gene_param_tensors(cell, dev):
     """Kernel-ready (A, pi, Bfull, codon5) of the fused gene model on `dev`, rebuilt from the parameters on every call
     like the reference's recurrent_init (MsaHmmCell.py:41-50) -- one launch of the parameter kernel when the kernels
@@ -55,12 +63,12 @@ def _gene_param_tensors(cell, dev):
         if gp is not None and gp[0].device == dev:
             return gp
     elif _fused_params_ok(cell, em, tr) and em.emission_kernel.device == dev:
-        with torch.no_grad():
-            A, pi, Bfull = ops.GeneParams.apply(tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)
-        # what recurrent_init would have left on the plugins (values identical to make_A / make_initial_distribution)
-        tr.A, tr.A_transposed = A, A.transpose(1, 2)
-        cell.init_dist = pi.reshape(1, cell.num_models, -1)
-        em.B = None
+        A, pi, Bfull = ops.genepred_params(tr.transition_kernel, tr.starting_distribution_kernel, em.emission_kernel)
+        # what recurrent_init would have left on the plugins (values identical to make_A / make_initial_distribution);
+        # plain attributes go straight into the instance dictionaries (nn.Module.__setattr__ costs 5 us apiece)
+        _set_plain(tr, "A", A); _set_plain(tr, "A_transposed", A.transpose(1, 2))
+        _set_plain(cell, "init_dist", pi.reshape(1, cell.num_models, -1))
+        _set_plain(em, "B", None)
         return (A, pi, Bfull, em.codon5(dev))
     else:
         cell.recurrent_init()

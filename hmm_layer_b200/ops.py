@@ -233,6 +233,25 @@ def genepred_grad(inputs, A, pi, Bfull, codon, log_post, log_alpha_hat, grad_log
     return res
 
 
+def genepred_params(tk, sk, ek):
+    """A (k,15,15), pi (k,15), Bfull (k,15,15) from the kernels in one launch, no autograd bookkeeping (the inference path
+    of the layer: the parameters are rebuilt on every call like the reference's recurrent_init, so the Python in front of
+    the first upload counts).  GeneParams below is the differentiable form."""
+    lib = _lib.load()
+    k, dev = ek.shape[0], ek.device
+    A = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+    pi = torch.empty((k, 15), dtype=torch.float32, device=dev)
+    Bfull = torch.empty((k, 15, 15), dtype=torch.float32, device=dev)
+    tk, sk, ek = tk.detach(), sk.detach(), ek.detach()
+    if not (tk.is_contiguous() and sk.is_contiguous() and ek.is_contiguous() and tk.dtype == sk.dtype == ek.dtype == torch.float32
+            and tk.device == sk.device == dev):
+        tk, sk, ek = _req(tk.to(dev), "transition_kernel"), _req(sk.to(dev), "start_kernel"), _req(ek, "emission_kernel")
+    with torch.cuda.device(dev):
+        _lib.check(lib.hmm_b200_genepred_params(tk.data_ptr(), sk.data_ptr(), ek.data_ptr(), k, A.data_ptr(), pi.data_ptr(),
+                                                Bfull.data_ptr(), _stream(dev)))
+    return A, pi, Bfull
+
+
 class GeneParams(torch.autograd.Function):
     """(transition kernel (1,23), starting distribution kernel (1,1,15), emission kernel (k,13,15)) -> A (k,15,15),
     pi (k,15), Bfull (k,15,15) of the 15-state gene model in one launch, with its backward in one launch
