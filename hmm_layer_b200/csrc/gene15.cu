@@ -2159,7 +2159,7 @@ int shard_reduce_x(const float* inputs, int num_models, int batch, int T, int se
     return 0;
   }
   const size_t smg = (size_t)HEAP * MAT * sizeof(float);
-  rc = ensure_dynamic_smem(shard_product_kernel, 14, smg); if (rc) return rc;
+  rc = ensure_dynamic_smem(shard_product_kernel, 24, smg); if (rc) return rc;
   {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(PG, NB); cfg.blockDim = dim3(K1_THREADS); cfg.dynamicSmemBytes = smg; cfg.stream = st;
@@ -2206,7 +2206,7 @@ int shard_finalize_x(const float* inputs, int num_models, int batch, int T, int 
     HMM_CUDA_OK(cudaGetLastError());
     return 0;
   }
-  rc = ensure_dynamic_smem(shard_scan_kernel, 15, sizeof(XSmem)); if (rc) return rc;
+  rc = ensure_dynamic_smem(shard_scan_kernel, 25, sizeof(XSmem)); if (rc) return rc;
   {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(PG, NB); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = sizeof(XSmem); cfg.stream = st;
@@ -2329,11 +2329,19 @@ int grad(const float* inputs, int num_models, int batch, int T, const float* A, 
 }
 
 static size_t viterbi_psi_words(int T) { return (size_t)((T + 2) / 4 + 1) * 16; }   // words per sequence
+// chunked (max,+) scan (gene15_viterbi.cu)
+bool viterbi_scan_applies(int T);
+size_t viterbi_scan_scratch_bytes(int NB);
+int launch_viterbi_scan(const float* E, const float* A, const float* pi, int NB, int batch, int T, void* scratch,
+                        unsigned char* path, float* score, cudaStream_t st);
 
 size_t viterbi_workspace_size(int num_models, int batch, int T) {
   if (num_models <= 0 || batch <= 0 || T <= 0) return 0;
   const size_t NBT = (size_t)num_models * batch * T;
-  return align_up(NBT * Q * sizeof(float), 256) + align_up((size_t)num_models * batch * viterbi_psi_words(T) * 4, 256);
+  size_t second = (size_t)num_models * batch * viterbi_psi_words(T) * 4;           // back-pointer table of viterbi_kernel
+  const size_t scan = viterbi_scan_scratch_bytes(num_models * batch);                // chunk matrices of the scan
+  if (scan > second) second = scan;
+  return align_up(NBT * Q * sizeof(float), 256) + align_up(second, 256);
 }
 
 int viterbi(const float* inputs, int num_models, int batch, int T, const float* A, const float* pi, const float* Bfull,
@@ -2350,6 +2358,7 @@ int viterbi(const float* inputs, int num_models, int batch, int T, const float* 
   unsigned* psi = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(workspace) + align_up((size_t)num_models * batch * T * Q * sizeof(float), 256));
   int rc = emission(inputs, num_models, batch, T, Bfull, codon5, hints, flags | EMIT_LOG_FLOORED, E, st);
   if (rc) return rc;
+  if (viterbi_scan_applies(T)) return launch_viterbi_scan(E, A, pi, num_models * batch, batch, T, psi, path, score, st);
   viterbi_kernel<<<num_models * batch, 32, 0, st>>>(E, A, pi, batch, T, psi, viterbi_psi_words(T), path, score);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
