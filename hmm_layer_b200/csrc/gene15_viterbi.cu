@@ -17,6 +17,7 @@
 //                          (3) one thread chains the 64 maps backwards from the best final state.  (4) thread = chunk walks its
 //                          back-pointers from its now known end state; the path leaves coalesced.
 // The emissions come from emission_kernel's log-floored buffer as before.
+#include <cooperative_groups.h>
 #include "gene15_dev.cuh"
 
 namespace hmm {
@@ -24,8 +25,11 @@ namespace gene15 {
 
 constexpr int VC = 64;              // chunks per sequence (at most)
 constexpr int VROW_THREADS = 256;   // rows kernel: 16 chunks x 16 lanes
-constexpr int VCH_THREADS = 1024;   // chunks kernel: 64 chunks x 16 lanes
+constexpr int VCL = 4;              // CTAs (one cluster) per sequence in the chunks kernel
+constexpr int VCPC = VC / VCL;      // chunks per CTA
+constexpr int VCH_THREADS = VCPC * 16;   // chunks kernel: half warp = chunk
 constexpr int VPF = 8;              // emission rows requested ahead in the in-chunk recursion
+constexpr int VRING = 8;            // ... and in the rows kernel
 
 // in-edges of every state in ascending source order (ESRC / EDST of gene15_dev.cuh regrouped by destination)
 __device__ constexpr int VIN_CNT[Q] = {2, 2, 2, 2, 2, 3, 2, 1, 1, 1, 1, 1, 1, 1, 1};
@@ -48,7 +52,6 @@ __global__ void __launch_bounds__(VROW_THREADS) viterbi_rows_kernel(const float*
   const int n = blockIdx.y, m = n / batch, tid = threadIdx.x;
   const int c_raw = blockIdx.x * (VROW_THREADS / 16) + (tid >> 4), i = tid & 15;
   const bool valid = c_raw < C;
-  const unsigned hmask = 0xffffu << (tid & 16);   // the two half warps of a warp walk chunks of different lengths: each syncs itself
   const int c = valid ? c_raw : C - 1;   // a half warp behind the last chunk repeats it (the shuffles are warp-wide), stores nothing
   float la[Q][3];
 #pragma unroll
@@ -68,41 +71,55 @@ __global__ void __launch_bounds__(VROW_THREADS) viterbi_rows_kernel(const float*
     for (int j = 0; j < Q; ++j) d[j] = (j == ii) ? 0.f : -INFINITY;
     t0 = c * L;
   }
-  const int t1 = min(T, (c + 1) * L);
+  const int t1 = min(T, (c + 1) * L), tb = c * L;
   double off = 0.0;
+  // Every warp walks the same L step slots (step slot s = position tb + s), so that the two chunks of a warp stay in one
+  // instruction stream and the shuffles are plain full-mask ones; a slot outside the chunk's positions (slot 0 of chunk 0,
+  // the slots behind a short last chunk) computes and does not commit.
   auto renorm = [&]() {
     float mx = d[0];
 #pragma unroll
     for (int j = 1; j < Q; ++j) mx = fmaxf(mx, d[j]);
-    mx = half_max(mx, hmask);
+    mx = half_max(mx);
     if (mx > -INFINITY) {
 #pragma unroll
       for (int j = 0; j < Q; ++j) d[j] -= mx;
       off += (double)mx;
     }
   };
-  float e[Q], en[Q];
-  if (t0 < t1) {
+  // emissions: lane j of the half warp fetches E_t(j) (one coalesced 60-byte row per step) VRING steps ahead of its use, the
+  // 15 values of a step come by shuffles: one load per step and thread instead of fifteen, and the latency is covered
+  const int jl = min(i, Q - 1);
+  auto eload = [&](int sl) { const int t = tb + sl; return (sl < L && t < T) ? __ldg(Eseq + (size_t)t * Q + jl) : 0.f; };
+  float ring[VRING];
 #pragma unroll
-    for (int j = 0; j < Q; ++j) e[j] = __ldg(Eseq + (size_t)t0 * Q + j);
-  }
-  for (int t = t0; t < t1; ++t) {
-    const int tn = min(t + 1, t1 - 1);
+  for (int u = 0; u < VRING; ++u) ring[u] = eload(u);
+  for (int sb = 0; sb < L; sb += VRING) {
+    const bool mine = tb + sb >= t0 && tb + sb + VRING <= t1;
+    const bool full = __all_sync(0xffffffffu, mine);   // warp-uniform: every slot of the block is a step of both chunks
 #pragma unroll
-    for (int j = 0; j < Q; ++j) en[j] = __ldg(Eseq + (size_t)tn * Q + j);
-    float nd[Q];
+    for (int u = 0; u < VRING; ++u) {
+      const int t = tb + sb + u;
+      float nd[Q];
 #pragma unroll
-    for (int j = 0; j < Q; ++j) {
-      float b = d[VIN_SRC[j][0]] + la[j][0];
-      if (VIN_CNT[j] > 1) b = fmaxf(b, d[VIN_SRC[j][1]] + la[j][1]);
-      if (VIN_CNT[j] > 2) b = fmaxf(b, d[VIN_SRC[j][2]] + la[j][2]);
-      nd[j] = b + e[j];
+      for (int j = 0; j < Q; ++j) {
+        float b = d[VIN_SRC[j][0]] + la[j][0];
+        if (VIN_CNT[j] > 1) b = fmaxf(b, d[VIN_SRC[j][1]] + la[j][1]);
+        if (VIN_CNT[j] > 2) b = fmaxf(b, d[VIN_SRC[j][2]] + la[j][2]);
+        nd[j] = b + __shfl_sync(0xffffffffu, ring[u], j, 16);
+      }
+      if (full) {
+#pragma unroll
+        for (int j = 0; j < Q; ++j) d[j] = nd[j];
+      } else {
+        const bool on = t >= t0 && t < t1;
+#pragma unroll
+        for (int j = 0; j < Q; ++j) d[j] = on ? nd[j] : d[j];
+      }
+      ring[u] = eload(sb + u + VRING);
     }
-#pragma unroll
-    for (int j = 0; j < Q; ++j) { d[j] = nd[j]; e[j] = en[j]; }
-    if (((t - t0) & 15) == 15) renorm();
+    renorm();   // every VRING steps
   }
-  renorm();
   if (valid && i < Q) {
     float* row = Mv + (((size_t)n * VC + c) * 16 + i) * 16;
 #pragma unroll
@@ -120,8 +137,14 @@ struct VSmemHead {
   unsigned char insrc[Q][4];    // VIN_SRC for the replay's data-dependent look-ups
 };
 __host__ __device__ inline int viterbi_lp(int L) { return L | 1; }   // odd pitch: the replay's 64-bit reads hit 32 different banks
+// the back-pointer region first holds the sequence's chunk matrices (64 KB, phase 1), so it is at least that large
+__host__ __device__ inline size_t viterbi_psi_bytes(int L) {
+  const size_t p = (size_t)(VCPC / 2) * viterbi_lp(L) * sizeof(uint2), m = (size_t)VC * 256 * sizeof(float);
+  return ((p > m ? p : m) + 15) / 16 * 16;
+}
 __host__ __device__ inline size_t viterbi_smem_bytes(int T, int L) {
-  return ((sizeof(VSmemHead) + 15) / 16) * 16 + (size_t)(VC / 2) * viterbi_lp(L) * sizeof(uint2) + (((size_t)T + 15) / 16) * 16;
+  (void)T;
+  return ((sizeof(VSmemHead) + 15) / 16) * 16 + viterbi_psi_bytes(L) + (((size_t)VCPC * L + 15) / 16) * 16;
 }
 
 __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const float* __restrict__ E, const float* __restrict__ A,
@@ -132,52 +155,72 @@ __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const fl
   VSmemHead& S = *reinterpret_cast<VSmemHead*>(vsm);
   const int Lp = viterbi_lp(L);
   uint2* psi = reinterpret_cast<uint2*>(vsm + ((sizeof(VSmemHead) + 15) / 16) * 16);   // [pair of chunks][step]: bit masks of the 2 x 15 arg bits
-  unsigned char* obuf = reinterpret_cast<unsigned char*>(psi + (size_t)(VC / 2) * Lp);
-  const int n = blockIdx.x, m = n / batch, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  unsigned char* obuf = reinterpret_cast<unsigned char*>(psi) + viterbi_psi_bytes(L);
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = blockIdx.x;            // CTA `rank` of the sequence's cluster owns chunks [rank * VCPC, (rank + 1) * VCPC)
+  const int n = blockIdx.y, m = n / batch, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const float* Eseq = E + (size_t)n * T * Q;
   if (tid < Q * 4) S.insrc[tid >> 2][tid & 3] = (unsigned char)((tid & 3) < 3 ? VIN_SRC[tid >> 2][tid & 3] : 0);
+#ifdef HMM_VIT_MARKS
+  long long mk[8];
+  int nmk = 0;
+#define VMARK() do { if (tid == 0) mk[nmk++] = clock_fenced(); } while (0)
+#else
+#define VMARK() do { } while (0)
+#endif
+  VMARK();
 
-  // (1) fold the chunk matrices: v enters chunk c; lane = state j
+  // (1) fold the chunk matrices: v enters chunk c; lane = state j.  The matrices are staged in shared memory first (all
+  // loads in flight at once; the region becomes the back-pointer table afterwards)
+  {
+    float4* dst = reinterpret_cast<float4*>(psi);
+    const float4* src = reinterpret_cast<const float4*>(Mv + (size_t)n * VC * 256);
+    for (int k = tid; k < C * 64; k += VCH_THREADS) dst[k] = __ldg(src + k);
+  }
+  __syncthreads();
+  VMARK();
   if (warp == 0) {
-    const int j = min(lane, 15);
-    const float* M0 = Mv + (size_t)n * VC * 256;
-    float v = (lane < Q) ? __ldg(M0 + j) : -INFINITY;   // row 0 of chunk 0
-    double offset = __ldg(offs + (size_t)n * VC);
-    float mc[Q], mn[Q];
-    if (C > 1) {
+    const int j = lane & 15;
+    const float* M0 = reinterpret_cast<const float*>(psi);
+    float v = ((lane & 15) < Q) ? M0[lane & 15] : -INFINITY;   // row 0 of chunk 0
+    double offset = 0.0;
+    for (int c = lane; c < C; c += 32) offset += __ldg(offs + (size_t)n * VC + c);   // the constants taken out of the chunks' rows
 #pragma unroll
-      for (int i = 0; i < Q; ++i) mc[i] = __ldg(M0 + (size_t)1 * 256 + i * 16 + j);
-    }
+    for (int o = 16; o >= 1; o >>= 1) offset += __shfl_xor_sync(0xffffffffu, offset, o);
+    // both half warps hold v (lane j and lane 16 + j the same value); the lower half takes source states 0-7, the upper 8-14
+    const int hi = lane >> 4, i0 = hi * 8;
     for (int c = 1; c < C; ++c) {
       if (lane < 16) S.vin[c][lane] = v;
-      const int cn = min(c + 1, C - 1);
+      const float* Mc = M0 + (size_t)c * 256 + i0 * 16 + j;
+      float b0 = -INFINITY, b1 = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < Q; ++i) mn[i] = __ldg(M0 + (size_t)cn * 256 + i * 16 + j);
-      float b0 = -INFINITY, b1 = -INFINITY, b2 = -INFINITY;
-#pragma unroll
-      for (int i = 0; i < Q; ++i) {
-        const float cand = __shfl_sync(0xffffffffu, v, i) + mc[i];
-        if (i % 3 == 0) b0 = fmaxf(b0, cand); else if (i % 3 == 1) b1 = fmaxf(b1, cand); else b2 = fmaxf(b2, cand);
+      for (int k = 0; k < 8; ++k) {
+        const float vi = __shfl_sync(0xffffffffu, v, i0 + k);      // (i0 + k == 15 in the upper half: the -inf of lane 15)
+        const float cand = vi + Mc[min(k, 14 - i0) * 16];
+        if (k & 1) b1 = fmaxf(b1, cand); else b0 = fmaxf(b0, cand);
       }
-      v = (lane < Q) ? fmaxf(fmaxf(b0, b1), b2) : -INFINITY;
-      offset += __ldg(offs + (size_t)n * VC + c);
-      float mx = v;
+      float b = fmaxf(b0, b1);
+      b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, 16));
+      v = (j < Q) ? b : -INFINITY;
+      if ((c & 3) == 3 || c == C - 1) {   // take the maximum out now and then (the magnitudes grow by a chunk's spread at most)
+        float mx = v;
 #pragma unroll
-      for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      if (mx > -INFINITY) { v -= mx; offset += (double)mx; }
-#pragma unroll
-      for (int i = 0; i < Q; ++i) mc[i] = mn[i];
+        for (int o = 8; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if (mx > -INFINITY) { v -= mx; offset += (double)mx; }
+      }
     }
     float mx = v;
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0 && score) score[n] = (float)(offset + (double)mx);
+    if (lane == 0 && score && rank == 0) score[n] = (float)(offset + (double)mx);
   }
   __syncthreads();
+  VMARK();
 
   // (2) the recursion inside every chunk: half warp = chunk, lane = state
   {
-    const int c = warp * 2 + (lane >> 4), j = lane & 15;
+    const int c = rank * VCPC + warp * 2 + (lane >> 4), j = lane & 15;
     const bool chunk_ok = c < C, live = chunk_ok && j < Q;
     const int jj = min(j, Q - 1);
     const int s0 = VIN_SRC[jj][0], s1 = VIN_SRC[jj][1], s2 = VIN_SRC[jj][2], cnt = VIN_CNT[jj];
@@ -195,7 +238,10 @@ __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const fl
     float ea[VPF], eb[VPF];
 #pragma unroll
     for (int u = 0; u < VPF; ++u) ea[u] = eload(u);
-    auto block = [&](const float (&use)[VPF], float (&fill)[VPF], int sb) {
+    // one block of VPF steps.  `full`: every step of the block is a real step of both chunks of the warp (all but the
+    // first block of chunk 0 and the blocks at a chunk's / the sequence's end) -- no activity predicates then.  Dead lanes
+    // (state 15, chunks behind the last) carry -inf on every in-edge: their comparisons pick source 0 and set no bits.
+    auto block = [&](const float (&use)[VPF], float (&fill)[VPF], int sb, bool full) {
 #pragma unroll
       for (int u = 0; u < VPF; ++u) fill[u] = eload(sb + VPF + u);
 #pragma unroll
@@ -205,21 +251,33 @@ __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const fl
         const float c1 = __shfl_sync(0xffffffffu, d, s1, 16) + la1;
         const float c2 = __shfl_sync(0xffffffffu, d, s2, 16) + la2;
         const float best = fmaxf(fmaxf(c0, c1), c2);
-        const int arg = (c0 == best) ? 0 : (c1 == best) ? 1 : 2;
-        const int srcl = arg == 0 ? s0 : (arg == 1 ? s1 : s2);
+        const bool p0 = c0 == best, p1 = c1 == best;
+        const int srcl = p0 ? s0 : (p1 ? s1 : s2);
         const int o2 = __shfl_sync(0xffffffffu, org, srcl, 16);
-        const bool on = act(s);
-        const unsigned m0 = __ballot_sync(0xffffffffu, on && live && (arg & 1));
-        const unsigned m1 = __ballot_sync(0xffffffffu, on && live && (arg & 2));
-        if (on) { d = best + use[u]; org = o2; }
-        if (lane == 0 && s < L) psi[(size_t)warp * Lp + s] = make_uint2(m0, m1);
+        if (full) {
+          const unsigned m0 = __ballot_sync(0xffffffffu, !p0 && p1);
+          const unsigned m1 = __ballot_sync(0xffffffffu, !p0 && !p1);
+          d = best + use[u];
+          org = o2;
+          if (lane == 0) psi[(size_t)warp * Lp + s] = make_uint2(m0, m1);
+        } else {
+          const bool on = act(s);
+          const unsigned m0 = __ballot_sync(0xffffffffu, on && !p0 && p1);
+          const unsigned m1 = __ballot_sync(0xffffffffu, on && !p0 && !p1);
+          if (on) { d = best + use[u]; org = o2; }
+          if (lane == 0 && s < L) psi[(size_t)warp * Lp + s] = make_uint2(m0, m1);
+        }
       }
       const float mx = half_max(d);
       if (mx > -INFINITY) d -= mx;
     };
+    auto is_full = [&](int sb) {   // warp-uniform
+      const bool mine = !chunk_ok || (tb + sb >= 1 && tb + sb + VPF <= T && sb + VPF <= L);
+      return __all_sync(0xffffffffu, mine);
+    };
     for (int sb = 0; sb < L; sb += 2 * VPF) {
-      block(ea, eb, sb);
-      block(eb, ea, sb + VPF);
+      block(ea, eb, sb, is_full(sb));
+      block(eb, ea, sb + VPF, is_full(sb + VPF));
     }
     if (live) S.maps[c][j] = (unsigned char)org;
     // best final state (lowest index on ties): the last chunk's half warp
@@ -233,21 +291,34 @@ __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const fl
     }
     if (c == C - 1 && j == 0) S.endst[C - 1] = bs;
   }
-  __syncthreads();
+  // the maps of the other CTAs' chunks and the final state come over distributed shared memory
+  cluster.sync();
+  for (int k = tid; k < C * 4; k += VCH_THREADS) {
+    const int c = k >> 2, r = c / VCPC;
+    if (r != rank) {
+      const unsigned* remote = reinterpret_cast<const unsigned*>(cluster.map_shared_rank(&S.maps[0][0], r));
+      reinterpret_cast<unsigned*>(&S.maps[0][0])[k] = remote[k];
+    }
+  }
+  if (tid == 0 && (C - 1) / VCPC != rank) S.endst[C - 1] = *cluster.map_shared_rank(&S.endst[C - 1], (C - 1) / VCPC);
+  cluster.sync();   // (nobody reads this CTA's shared memory any more: it may run ahead and exit)
+  VMARK();
   // (3) the state at every chunk's last position, from the last chunk backwards
   if (tid == 0) {
     int s = S.endst[C - 1];
     for (int c = C - 1; c >= 1; --c) { s = S.maps[c][s]; S.endst[c - 1] = s; }
   }
   __syncthreads();
+  VMARK();
   // (4) thread = chunk: back along the chunk's pointers
-  if (tid < C) {
-    const int c = tid, tb = c * L, sh = (c & 1) * 16;
-    const uint2* pp = psi + (size_t)(c >> 1) * Lp;
+  const int pos0 = rank * VCPC * L;       // first position of this CTA
+  if (tid < VCPC && rank * VCPC + tid < C) {
+    const int lc = tid, c = rank * VCPC + lc, tb = c * L, sh = (lc & 1) * 16;
+    const uint2* pp = psi + (size_t)(lc >> 1) * Lp;
     int s = S.endst[c];
     const int s_hi = min(L, T - tb) - 1, s_lo = (c == 0) ? 1 : 0;
     for (int k = s_hi; k >= s_lo; --k) {
-      obuf[tb + k] = (unsigned char)s;
+      obuf[tb - pos0 + k] = (unsigned char)s;
       const uint2 w = pp[k];
       const int arg = (int)((w.x >> (sh + s)) & 1u) | ((int)((w.y >> (sh + s)) & 1u) << 1);
       s = S.insrc[s][arg];
@@ -255,15 +326,24 @@ __global__ void __launch_bounds__(VCH_THREADS, 1) viterbi_chunks_kernel(const fl
     if (c == 0) obuf[0] = (unsigned char)s;
   }
   __syncthreads();
-  unsigned char* out = path + (size_t)n * T;
-  for (int t = tid; t < T; t += VCH_THREADS) out[t] = obuf[t];
+  VMARK();
+  unsigned char* out = path + (size_t)n * T + pos0;
+  const int cnt = max(0, min(T - pos0, VCPC * L));
+  for (int t = tid; t < cnt; t += VCH_THREADS) out[t] = obuf[t];
+#ifdef HMM_VIT_MARKS
+  VMARK();
+  if (tid == 0 && n == 0)
+    printf("viterbi_chunks_kernel cycles: stage %lld, fold %lld, in-chunk %lld, chain %lld, replay %lld, out %lld\n", mk[1] - mk[0],
+           mk[2] - mk[1], mk[3] - mk[2], mk[4] - mk[3], mk[5] - mk[4], mk[6] - mk[5]);
+#endif
+#undef VMARK
 }
 
 // ---- host side ----
 enum { SLOT_VITERBI = 26 };
 bool viterbi_scan_applies(int T) {
   static const bool off = getenv("HMM_B200_VITERBI_SCAN") && atoi(getenv("HMM_B200_VITERBI_SCAN")) == 0;
-  return !off && T >= 1024 && T <= 32768;
+  return !off && T >= 1024 && T <= 131072;
 }
 size_t viterbi_scan_scratch_bytes(int NB) { return (size_t)NB * VC * 256 * sizeof(float) + (size_t)NB * VC * sizeof(double); }
 
@@ -276,7 +356,15 @@ int launch_viterbi_scan(const float* E, const float* A, const float* pi, int NB,
   int rc = ensure_dynamic_smem(viterbi_chunks_kernel, SLOT_VITERBI, smem);
   if (rc) return rc;
   viterbi_rows_kernel<<<dim3(cdiv(C, VROW_THREADS / 16), NB), VROW_THREADS, 0, st>>>(E, A, pi, batch, T, L, C, Mv, offs);
-  viterbi_chunks_kernel<<<NB, VCH_THREADS, smem, st>>>(E, A, pi, batch, T, L, C, Mv, offs, path, score);
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(VCL, NB); cfg.blockDim = dim3(VCH_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = VCL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, viterbi_chunks_kernel, E, A, pi, batch, T, L, C, (const float*)Mv, (const double*)offs, path, score));
+  }
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

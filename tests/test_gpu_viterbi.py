@@ -1,5 +1,5 @@
 """GPU parity of the gene-HMM Viterbi kernels (hmm_b200_genepred_viterbi: the chunked (max,+) scan of gene15_viterbi.cu for
-1024 <= T <= 32768, the one-warp-per-sequence kernel otherwise) against the fp64 oracle (oracle/hmm_oracle.py
+1024 <= T <= 131072, the one-warp-per-sequence kernel otherwise) against the fp64 oracle (oracle/hmm_oracle.py
 viterbi: max-product form of the reference recursion; the reference itself ships no Viterbi).  State paths must match
 EXACTLY (BASELINE north_star) on the seeded cases; at BASELINE config-2 size the check is through the path's own log
 joint probability recomputed in fp64 (equal to the kernel's score, never above the posterior log-likelihood, every step
@@ -21,7 +21,7 @@ def dev(x):
 
 
 @pytest.mark.parametrize("B,T", [(4, 1000), (3, 2049), (2, 4097), (5, 1), (3, 2), (2, 17), (1, 6000), (2, 1024), (2, 1025),
-                                 (3, 9999), (1, 32768), (1, 32769), (2, 1023)])
+                                 (3, 9999), (1, 32768), (1, 32769), (2, 1023), (1, 100_003), (1, 131_073)])
 def test_viterbi_path_exact(B, T):
     x = syn.gene_inputs(1, B, T, seed=300 + T)
     A, pi, Bfull, tab = gene_params(pi_random=True)
