@@ -2285,8 +2285,38 @@ int emission(const float* inputs, int num_models, int batch, int T, const float*
   int rc = fill_args(a, inputs, num_models, batch, T, nullptr, nullptr, Bfull, codon5, hints, flags);
   if (rc) return rc;
   HMM_REQUIRE(inputs && out_E, "genepred_emission: null inputs / output");
-  set_L(a, 32);
-  const size_t sm = ((sizeof(EmisSmem) + 15) / 16) * 16 + (size_t)G * (a.L * QP + 4) * sizeof(float) + (((size_t)G * a.L + 4 + 15) / 16) * 16;
+  // Tile length (positions per CTA = 32 L; the results do not depend on it): the one that needs the fewest waves of resident
+  // CTAs -- at config 2, L = 32 gives 320 CTAs for 296 places (a second wave of 24 CTAs doubles the time), L = 36 gives 288.
+  auto smem_for = [](int L) {
+    return ((sizeof(EmisSmem) + 15) / 16) * 16 + (size_t)G * (L * QP + 4) * sizeof(float) + (((size_t)G * L + 4 + 15) / 16) * 16;
+  };
+  int bestL = 32;
+  {
+    static int per_sm[kMaxDevices][MAX_L + 1] = {};   // resident CTAs per SM by tile length (0: not asked yet, -1: does not fit)
+    const int dev = current_device(), sms = num_sms();
+    double best = 1e300;
+    for (int L = 24; L <= MAX_L; L += 2) {
+      int c;
+      { std::lock_guard<std::mutex> lk(state_mutex()); c = per_sm[dev][L]; }
+      if (c == 0) {
+        c = -1;
+        if (smem_for(L) <= (size_t)227 * 1024 && set_smem(emission_kernel, SLOT_EM, smem_for(L)) == 0) {
+          int v = 0;
+          if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, emission_kernel, 512, smem_for(L)) == cudaSuccess && v > 0) c = v;
+          else (void)cudaGetLastError();
+        }
+        std::lock_guard<std::mutex> lk(state_mutex());
+        per_sm[dev][L] = c;
+      }
+      if (c <= 0) continue;
+      const long long tiles = (long long)num_models * batch * cdiv(cdiv(T, L), G);
+      const long long waves = (tiles + (long long)c * sms - 1) / ((long long)c * sms);
+      const double cost = (double)waves * (L + 6) * (c > 1 ? 1.0 + 0.5 * (c - 1) : 1.0);   // co-resident CTAs share the SM's issue slots
+      if (cost < best) { best = cost; bestL = L; }
+    }
+  }
+  set_L(a, bestL);
+  const size_t sm = smem_for(a.L);
   rc = set_smem(emission_kernel, SLOT_EM, sm); if (rc) return rc;
   emission_kernel<<<dim3(a.P, num_models * batch), 512, sm, st>>>(a, out_E);
   HMM_CUDA_OK(cudaGetLastError());

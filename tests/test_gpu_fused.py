@@ -114,3 +114,27 @@ def test_run_under_cuda_graph_capture_replays_correctly():
                     assert torch.equal(r["loglik"], ll), (fused, rep)
         finally:
             ops.set_fused(True)
+
+
+def test_two_streams_run_the_single_launch_kernel_concurrently():
+    """Two streams issue config-2-sized calls at the same time.  Every CTA of the single-launch kernel waits inside the
+    kernel for the other tiles of its sequence, so a launch must be resident as a whole: the launches are cooperative
+    (the driver places a grid completely or not yet), and concurrent callers neither deadlock nor disturb each other."""
+    A, pi, Bfull, tab = [dev(v) for v in gene_params(pi_random=True)]
+    tab5 = ops.prepare_codon(tab)
+    B, T = 32, 9999
+    xs = [syn.gene_inputs(1, B, T, seed=70 + i, p_n=0.01).cuda() for i in range(2)]
+    ref = [ops.genepred_run(x, A, pi, Bfull, tab5, want_post=True) for x in xs]
+    ref = [(r["post"].clone(), r["loglik"].clone()) for r in ref]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [[None] * 6, [None] * 6]
+    for it in range(6):
+        for k, st in enumerate(streams):
+            with torch.cuda.stream(st):     # (a workspace per stream: ops keys its cache by stream)
+                outs[k][it] = ops.genepred_run(xs[k], A, pi, Bfull, tab5, want_post=True)
+    torch.cuda.synchronize()
+    for k in range(2):
+        for it in range(6):
+            assert torch.equal(outs[k][it]["post"], ref[k][0]), (k, it)
+            assert torch.equal(outs[k][it]["loglik"], ref[k][1]), (k, it)
