@@ -691,6 +691,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
   // workspace now, under the down-sweep
 #ifdef HMM_FUSED_FINE_MARKS
   if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 8] = clock_fenced();
+  if (a.dbg && tid == 0) a.dbg[(size_t)(4096 + cta) * 16 + 12] = clock_fenced();
 #endif
   const int r_ci = lane, r_c = c0 + r_ci;
   const int r_len = (warp < 2 && r_ci < nch) ? min(L, T - r_c * L) : 0;

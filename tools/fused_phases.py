@@ -50,3 +50,6 @@ if fine[:, 9].any():
     f = fine[:nc]
     seq = np.stack([f[:, 8], f[:, 9], f[:, 0], f[:, 1], f[:, 2], f[:, 3], f[:, 4], d[:, 7]], 1)
     print("   fine marks (cycles): prologue, level 1, 2, 4, 8, 16, final barrier:", [int(np.median(x)) for x in np.diff(seq, axis=1).T])
+    # thread 0's mark 6 is read in front of the barrier that ends the top-level scan (warp 1): the gap to the first fine mark
+    # is the scan itself, so "publish+wait+scan" above is publish + wait + staging and "down-sweep" includes the scan
+    print("   top-level scan (mark 6 -> first fine mark):", int(np.median(f[:, 8] - d[:, 6])), " two adjacent fine marks:", int(np.median(f[:, 12] - f[:, 8])))
