@@ -194,7 +194,10 @@ int hmm_b200_genepred_params_grad(const float* transition_kernel, const float* s
  * prepares log_A_dense for it (:46-47) but ships no implementation; this is the max-product form of the recursion
  * MsaHmmCell.py:73-106 over the same floored emissions / initial distribution, ties to the lowest state index.
  *   path   (num_models, batch, T) uint8 state indices      score (num_models, batch) log joint of the path, or NULL
- * The emission tensor is materialised in the workspace (this path is latency-bound: T dependent steps per sequence).
+ * The log emissions are materialised in the workspace.  Sequences of 1024 to 131072 positions are decoded by a chunked
+ * (max,+) scan (64 chunks per sequence: chunk transfer matrices, a fold, the recursion inside every chunk, back-pointers in
+ * shared memory; a cluster of 4 CTAs per sequence), shorter or longer ones by one warp per sequence (T dependent steps).
+ * A must carry the 23-edge topology of the single-copy gene model (entries outside it are ignored).
  * --------------------------------------------------------------------------------------------------------- */
 size_t hmm_b200_genepred_viterbi_workspace_size(int num_models, int batch, int T);
 
