@@ -1559,6 +1559,7 @@ __global__ void __launch_bounds__(64) params_grad_kernel(const float* __restrict
 int fused_capacity(int L);
 int fused_run_len(int L);
 int launch_fused(Args a, int NB, cudaStream_t st);
+constexpr int FUSED_NOT_RESIDENT = 1001;   // launch_fused: the cooperative launch was refused for size (gene15_fused.cu)
 int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
                        unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st);
 static int g_fused_mode = 0; // 0: whenever the call qualifies, 1: never (two-kernel path)
@@ -1865,6 +1866,7 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
     if (Lf > 0 && (nb == NB || num_models == 1 || batch % nb == 0)) {   // a slice must not straddle two models
       ProfEvents* pe = nullptr;
       if (g_prof) { rc = prof_events(&pe); if (rc) return rc; g_prof_dev = current_device(); pe->n = 0; cudaEventRecord(pe->ev[pe->n++], st); }
+      bool fused_refused = false;
       for (int n0 = 0; n0 < NB; n0 += nb) {
         const int cnt = NB - n0 < nb ? NB - n0 : nb;
         Args s = a;
@@ -1881,10 +1883,15 @@ int run(const float* inputs, int num_models, int batch, int T, const float* A, c
         if (rc) return rc;
         s.out_post = out_post + (size_t)n0 * T * Q; s.out_alpha = nullptr; s.out_beta = nullptr;
         s.loglik = loglik ? loglik + n0 : nullptr;
-        rc = launch_fused(s, cnt, st); if (rc) return rc;
+        rc = launch_fused(s, cnt, st);
+        if (rc == FUSED_NOT_RESIDENT && n0 == 0) { fused_refused = true; break; }   // nothing launched yet: the two-kernel path below
+        if (rc) return rc == FUSED_NOT_RESIDENT ? HMM_B200_ECUDA : rc;
       }
-      if (pe) cudaEventRecord(pe->ev[pe->n++], st);
-      return 0;
+      if (!fused_refused) {
+        if (pe) cudaEventRecord(pe->ev[pe->n++], st);
+        return 0;
+      }
+      if (pe) pe->n = 0;
     }
   }
   set_L(a, choose_L(NB, T, full));

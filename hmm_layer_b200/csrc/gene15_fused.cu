@@ -1066,6 +1066,7 @@ static unsigned next_tag() {
 // a cooperative launch makes the driver guarantee it (or fail) also when other streams have kernels on the device (two
 // plain launches from two streams could each get half of their CTAs placed and wait for ever).  No measurable cost: 61.7
 // vs 61.8 us at config 2.
+constexpr int FUSED_NOT_RESIDENT = 1001;   // internal: the cooperative launch was refused for size (not a C ABI code)
 static int launch_coresident(const Args& a, const FShard& sh, dim3 grid, size_t smem, cudaStream_t st) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = dim3(FT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -1073,7 +1074,16 @@ static int launch_coresident(const Args& a, const FShard& sh, dim3 grid, size_t 
   at[0].id = cudaLaunchAttributeCooperative;
   at[0].val.cooperative = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  HMM_CUDA_OK(cudaLaunchKernelEx(&cfg, fused_kernel, a, sh));
+  const char* refuse = getenv("HMM_B200_TEST_REFUSE_COOP");   // test hook: behave as if the device had refused the grid
+  const cudaError_t e = (refuse && refuse[0] == '1') ? cudaErrorCooperativeLaunchTooLarge : cudaLaunchKernelEx(&cfg, fused_kernel, a, sh);
+  if (e == cudaErrorCooperativeLaunchTooLarge) {
+    // fewer CTAs fit than the occupancy query promised (a reduced SM share under MPS, a smaller shared-memory carve-out):
+    // the caller takes the path that needs no co-residency
+    (void)cudaGetLastError();
+    set_error("genepred: %u x %u CTAs of the single-launch kernel cannot be resident at once on this device", grid.x, grid.y);
+    return FUSED_NOT_RESIDENT;
+  }
+  HMM_CUDA_OK(e);
   HMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -1114,7 +1124,8 @@ int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, co
   const size_t half = (size_t)(tag & 1u) * world * NB;
   sh.my_blocks = sh.pr.blocks[rank] + half * MAT;
   sh.my_flags = sh.pr.flags[rank] + half;
-  return launch_coresident(a, sh, dim3(a.P + sh.PG + 1, NB), smem, st);
+  rc = launch_coresident(a, sh, dim3(a.P + sh.PG + 1, NB), smem, st);
+  return rc == FUSED_NOT_RESIDENT ? HMM_B200_EINVAL : rc;   // (the message says why; the 4-launch route needs no co-residency)
 }
 
 }  // namespace gene15

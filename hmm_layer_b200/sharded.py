@@ -127,14 +127,23 @@ class ShardContext:
         if self.peer_blocks is None:
             self.block = torch.empty((self.NB, 256), dtype=torch.float32, device=dev)
 
+    def _run_one_launch(self, shard, A, pi, Bfull, codon, tag, end_hints, training, no_loglik, out):
+        return ops.genepred_shard_run_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
+                                        self.peer_blocks, self.peer_flags, self.rank, self.world, end_hints=end_hints,
+                                        training=training, no_loglik=no_loglik, out=out)
+
     def run(self, shard, end_hints=None, training=False, no_loglik=False, want_post=True, want_alpha=False, want_beta=False, out=None):
         A, pi, Bfull, codon = self.params
         self.tag += 1
         tag = self.tag
         if self.one_launch and want_post and not (want_alpha or want_beta):
-            return ops.genepred_shard_run_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
-                                            self.peer_blocks, self.peer_flags, self.rank, self.world, end_hints=end_hints,
-                                            training=training, no_loglik=no_loglik, out=out)
+            try:
+                return self._run_one_launch(shard, A, pi, Bfull, codon, tag, end_hints, training, no_loglik, out)
+            except Exception as e:       # the device refused to hold the whole grid at once (MPS share, carve-out): 4 launches
+                if "resident at once" not in str(e):
+                    raise
+                # (nothing was launched and no rank depends on this rank's route: the tables and tags are the same)
+                self.one_launch, self.launches_per_step = False, 4
         if self.peer_blocks is not None:
             ops.genepred_shard_reduce_x(shard, self.halo, self.seq_off, self.seq_total, A, pi, Bfull, codon, self.ws, tag,
                                         peer_blocks=self.peer_blocks, peer_flags=self.peer_flags, rank=self.rank, world=self.world,

@@ -138,3 +138,26 @@ def test_two_streams_run_the_single_launch_kernel_concurrently():
         for it in range(6):
             assert torch.equal(outs[k][it]["post"], ref[k][0]), (k, it)
             assert torch.equal(outs[k][it]["loglik"], ref[k][1]), (k, it)
+
+
+def test_refused_cooperative_launch_falls_back_to_the_two_kernel_path(monkeypatch):
+    """When the device cannot hold the whole grid at once (reduced SM share under MPS, a smaller shared-memory carve-out) the
+    cooperative launch is refused for size: the call then runs the two-kernel path, which needs no co-residency.  The refusal
+    is simulated through the library's test hook."""
+    A, pi, Bfull, tab = [dev(v) for v in gene_params(pi_random=True)]
+    tab5 = ops.prepare_codon(tab)
+    x = syn.gene_inputs(1, 6, 5000, seed=91, p_n=0.01).cuda()
+    ops.set_fused(False)
+    try:
+        two = ops.genepred_run(x, A, pi, Bfull, tab5, want_post=True)
+        two = (two["post"].clone(), two["loglik"].clone())
+    finally:
+        ops.set_fused(True)
+    monkeypatch.setenv("HMM_B200_TEST_REFUSE_COOP", "1")
+    got = ops.genepred_run(x, A, pi, Bfull, tab5, want_post=True)
+    torch.cuda.synchronize()
+    assert torch.equal(got["post"], two[0]) and torch.equal(got["loglik"], two[1])
+    monkeypatch.delenv("HMM_B200_TEST_REFUSE_COOP")
+    fused = ops.genepred_run(x, A, pi, Bfull, tab5, want_post=True)
+    torch.cuda.synchronize()
+    assert (fused["post"].exp() - two[0].exp()).abs().max() < 2e-5
