@@ -666,7 +666,11 @@ __device__ __forceinline__ void matvec_raw(const float* __restrict__ blk, int hl
     d = ok ? d : 0.f;
     if (k & 1) { acc1 = fmaf(uk, c, acc1); s1 = fmaf(uk, d, s1); } else { acc0 = fmaf(uk, c, acc0); s0 = fmaf(uk, d, s0); }
   }
-  const int ex = pexp(s0 + s1);
+  // The exponent taken out must be the SAME in the 16 lanes of a half warp (h.e is read from one lane, h.v from all).  The
+  // backward half adds its terms in a lane-dependent (rotated) order, so its sums can differ in the last bit and, next to a
+  // power of two, in the exponent: every lane uses lane 0's sum.
+  const float ssum = __shfl_sync(0xffffffffu, s0 + s1, 0, 16);
+  const int ex = pexp(ssum);
   const float out = (bwd ? sp : 1.f) * (acc0 + acc1) * pow2neg(ex);
   if (commit) {
     h.v = (hl < Q) ? out : 0.f;

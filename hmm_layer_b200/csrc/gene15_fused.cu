@@ -184,6 +184,37 @@ __device__ __forceinline__ void codon_factors_reg(const Args& a, const EmisSmem&
   for (int s = 0; s < 9; ++s) cod[s] = fl[s] * fr[s];
 }
 
+// One step of the top-level scan with a whole warp on one direction: both half warps hold the vector (lane hl and lane
+// 16 + hl the same value), each takes 8 of the 16 source slots and the halves are added by one exchange (matvec_raw,
+// gene15_dev.cuh, is the one-half-warp form).  The exponent taken out comes from lane 0's sum, so that it is the same in every lane.
+__device__ __forceinline__ void matvec_split(const float* __restrict__ blk, int hl, int hi, bool bwd, HV& h) {
+  const int row = min(hl, Q - 1);
+  const float sp = blk[row * QP + 15];
+  const int Eb = __float_as_int(blk[MAT - 1]);
+  const float u = (hl < Q) ? (bwd ? h.v : h.v * sp) : 0.f;
+  float acc0 = 0.f, acc1 = 0.f, s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int kq = 8 * hi + k;
+    const int kk = bwd ? ((hl + kq) & 15) : kq;
+    const float uk = __shfl_sync(0xffffffffu, u, kk, 16);
+    const bool ok = kk < Q;                      // slot 15 holds scales / exponent bits, never a matrix entry
+    float c = bwd ? blk[row * QP + kk] : blk[kk * QP + hl];
+    float d = bwd ? blk[15 * QP + kk] : 1.f;
+    c = ok ? c : 0.f;
+    d = ok ? d : 0.f;
+    if (k & 1) { acc1 = fmaf(uk, c, acc1); s1 = fmaf(uk, d, s1); } else { acc0 = fmaf(uk, c, acc0); s0 = fmaf(uk, d, s0); }
+  }
+  float acc = acc0 + acc1, ssum = s0 + s1;
+  acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+  ssum += __shfl_xor_sync(0xffffffffu, ssum, 16);
+  ssum = __shfl_sync(0xffffffffu, ssum, 0);
+  const int ex = pexp(ssum);
+  const float out = (bwd ? sp : 1.f) * acc * pow2neg(ex);
+  h.v = (hl < Q) ? out : 0.f;
+  h.e += clamp_exp(ex) + Eb;
+}
+
 // Down-sweep of a 32-leaf product tree in heap order (gene15.cu, finalize_kernel): from the vectors at the root (forward
 // vector entering the tree's span in hvf[1] / hef[1], backward vector behind it in hvr[1] / her[1]) to those of every leaf.
 // First half of the CTA's warps forward, second half backward; a half warp handles one node.
@@ -659,27 +690,34 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
     for (int i = tid; i < P * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
     __syncthreads();
   }
-  if (!sharded && warp == 1) {
-    // top-level scan (TotalProbabilityCell.py:30-49 in scaled probability space): lanes 0-15 run pi . M_0 ... M_{P-1}
-    // (snapshot on entering tile p; the end gives the log-likelihood), lanes 16-31 run M_{P-1} ... M_{p+1} . 1
-    float llv = 0.f;
-    HV bnd;
-    if (staged) {
-      HV h, snap;
-      h.v = (hl < Q) ? (hi == 0 ? __ldg(a.pi + (size_t)m * Q + hl) : 1.f) : 0.f;
-      h.e = 0;
-      snap = h;
-      const int steps = hi == 0 ? P : P - 1 - p;
+  if (staged && (warp == 1 || warp == 2)) {
+    // top-level scan (TotalProbabilityCell.py:30-49 in scaled probability space) on the staged matrices: warp 1 runs
+    // pi . M_0 ... M_{P-1} (snapshot on entering tile p; the end gives the log-likelihood), warp 2 runs M_{P-1} ... M_{p+1} . 1;
+    // in either warp the two half warps share every step (8 source states each, matvec_split)
+    const bool bwd = warp == 2;
+    HV h;
+    h.v = (hl < Q) ? (bwd ? 1.f : __ldg(a.pi + (size_t)m * Q + hl)) : 0.f;
+    h.e = 0;
+    if (!bwd) {
+      HV snap = h;
       for (int it = 0; it < P; ++it) {
-        if (hi == 0 && it == p) snap = h;
-        matvec_raw(S.tiles[hi == 0 ? it : P - 1 - it], hl, hi, it < steps, h);
+        if (it == p) snap = h;
+        matvec_split(S.tiles[it], hl, hi, false, h);
       }
       const float tot = half_sum(h.v);
-      llv = (float)((double)h.e * LN2D + (double)logf(tot));   // meaningful in the forward half only
-      bnd = hi == 0 ? snap : h;
+      const float llv = (float)((double)h.e * LN2D + (double)logf(tot));
+      if (lane == 0 && p == 0 && a.loglik) a.loglik[n] = llv;
+      if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? snap.v : 0.f; if (hl == 0) S.hef[1] = snap.e; }
+      if (lane == 0) S.ll = llv;
     } else {
-      bnd = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
+      for (int it = P - 1; it > p; --it) matvec_split(S.tiles[it], hl, hi, true, h);
+      if (hi == 0) { S.v.hvr[1][hl] = (hl < Q) ? h.v : 0.f; if (hl == 0) S.her[1] = h.e; }
     }
+  }
+  if (!sharded && !staged && warp == 1) {
+    // more tiles than the staging area holds: the same scan straight from L2, both directions in one warp
+    float llv = 0.f;
+    const HV bnd = scan_tiles_global(a.Mt + (size_t)n * P * MAT, P, p, a.pi + (size_t)m * Q, hl, hi, &llv);
     if (lane == 0 && p == 0 && a.loglik) a.loglik[n] = llv;
     if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.hef[1] = bnd.e; }
     else         { S.v.hvr[1][hl] = (hl < Q) ? bnd.v : 0.f; if (hl == 0) S.her[1] = bnd.e; }
