@@ -1560,6 +1560,7 @@ int fused_capacity(int L);
 int fused_run_len(int L);
 int launch_fused(Args a, int NB, cudaStream_t st);
 constexpr int FUSED_NOT_RESIDENT = 1001;   // launch_fused: the cooperative launch was refused for size (gene15_fused.cu)
+int launch_boundary_groups(const Args& a, int NB, float* Gt, unsigned* gflg, cudaStream_t st);
 int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
                        unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st);
 static int g_fused_mode = 0; // 0: whenever the call qualifies, 1: never (two-kernel path)
@@ -1809,6 +1810,11 @@ static int launch_boundary(const Args& a, const Layout& l, int NB, int mode, flo
   }
   unsigned char* ws = static_cast<unsigned char*>(workspace);
   float* Gt = reinterpret_cast<float*>(ws + l.Gt);
+  if (mode == 0 && !groups_ready && a.in_f == nullptr && a.in_r == nullptr) {
+    // one cooperative launch instead of three kernels when the groups fit the device at once (gene15_fused.cu)
+    rc = launch_boundary_groups(a, NB, Gt, reinterpret_cast<unsigned*>(ws + l.gflg), st);
+    if (rc != FUSED_NOT_RESIDENT) return rc;
+  }
   float* gvf = reinterpret_cast<float*>(ws + l.gvf);
   float* gvr = reinterpret_cast<float*>(ws + l.gvr);
   const int PG = cdiv(a.P, G);

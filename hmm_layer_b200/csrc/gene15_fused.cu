@@ -1065,6 +1065,90 @@ __device__ __forceinline__ void shard_reducer(const Args& a, const FShard& sh) {
 #undef RMARK
 
 // ------------------------------------------------------------------------------------------------------------
+// Boundary vectors of every tile for long tile lists (the two-kernel path behind products_kernel: config 5's 1 Mbp has 869
+// tiles in 28 groups) in ONE launch, the reducer scheme of the shard mode without ranks: one CTA per group of 32 tile
+// matrices builds the group's product tree and publishes its root; every CTA then folds the sequence's group matrices up to
+// its own group from either end (two warps, matvec_split) and sweeps its tree down to the tiles' vectors.  Replaces
+// group_reduce_kernel + boundary_kernel + group_down_kernel (gene15.cu: 43 us of the 233 at 1 Mbp).  All CTAs of the launch
+// are resident at once (cooperative launch).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int BG_MAX_GROUPS = 96;
+__host__ __device__ inline size_t bg_smem_bytes(int PG) {
+  return ((sizeof(FSmem) + 127) / 128) * 128 + ((size_t)HEAP + PG) * MAT * sizeof(float);
+}
+__global__ void __launch_bounds__(FT) boundary_groups_kernel(const Args a, float* __restrict__ Gt, unsigned* __restrict__ gflg,
+                                                             unsigned tag) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  FSmem& S = *reinterpret_cast<FSmem*>(smem);
+  float* H = reinterpret_cast<float*>(smem + ((sizeof(FSmem) + 127) / 128) * 128);   // heap order: leaves [G, 2G), root at 1
+  float* GM = H + (size_t)HEAP * MAT;                                                 // the sequence's group matrices
+  const int g = blockIdx.x, n = blockIdx.y, PG = gridDim.x, P = a.P, m = n / a.batch;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
+  const int nb = min(G, P - g * G);
+  // 1. the group's product tree
+  {
+    const float4* src = reinterpret_cast<const float4*>(a.Mt + ((size_t)n * P + (size_t)g * G) * MAT);
+    float4* dst = reinterpret_cast<float4*>(H + G * MAT);
+    for (int i = tid; i < nb * (MAT / 4); i += FT) dst[i] = __ldg(src + i);
+    for (int b = nb + warp; b < G; b += FT / 32) identity_block(H + (G + b) * MAT, lane);
+  }
+  __syncthreads();
+  for (int np = G / 2; np >= 1; np >>= 1) tree_level_tc(H + 2 * np * MAT, H + np * MAT, np);
+  // 2. publish the group matrix
+  if (tid < MAT / 4) reinterpret_cast<float4*>(Gt + ((size_t)n * PG + g) * MAT)[tid] = reinterpret_cast<const float4*>(H + MAT)[tid];
+  __syncthreads();
+  if (tid == 0) st_release_u32(gflg + (size_t)n * PG + g, tag);
+  // 3. the other groups' matrices
+  for (int q = tid; q < PG; q += FT) {
+    const unsigned* f = gflg + (size_t)n * PG + q;
+    while (ld_acquire_u32(f) != tag) __nanosleep(64);
+  }
+  __syncthreads();
+  {
+    const float4* src = reinterpret_cast<const float4*>(Gt + (size_t)n * PG * MAT);
+    float4* dst = reinterpret_cast<float4*>(GM);
+    for (int i = tid; i < PG * (MAT / 4); i += FT) dst[i] = __ldcg(src + i);
+  }
+  __syncthreads();
+  // 4. folds (TotalProbabilityCell.py:30-49 in scaled probability space): warp 1 from the left up to this group (group 0's
+  // CTA to the end: the log-likelihood), warp 2 from the right down to the group behind this one
+  if (warp == 1) {
+    HV h;
+    h.v = (hl < Q) ? __ldg(a.pi + (size_t)m * Q + hl) : 0.f;
+    h.e = 0;
+    const int steps = g == 0 ? PG : g;
+    HV snap = h;
+    for (int s = 0; s < steps; ++s) {
+      if (s == g) snap = h;
+      matvec_split(GM + (size_t)s * MAT, hl, hi, false, h);
+    }
+    if (g != 0) snap = h;
+    if (g == 0 && !a.ll_external) {
+      const float tot = half_sum(h.v);
+      const float ll = (float)((double)h.e * LN2D + (double)logf(tot));
+      if (lane == 0) { a.llws[n] = ll; if (a.loglik) a.loglik[n] = ll; }
+    }
+    if (hi == 0) { S.v.hvf[1][hl] = (hl < Q) ? snap.v : 0.f; if (hl == 0) S.hef[1] = snap.e; }
+  } else if (warp == 2) {
+    HV h;
+    h.v = (hl < Q) ? 1.f : 0.f;
+    h.e = 0;
+    for (int s = PG - 1; s > g; --s) matvec_split(GM + (size_t)s * MAT, hl, hi, true, h);
+    if (hi == 0) { S.v.hvr[1][hl] = (hl < Q) ? h.v : 0.f; if (hl == 0) S.her[1] = h.e; }
+  }
+  __syncthreads();
+  // 5. down the group's tree to the vectors of its tiles
+  down_sweep(S, H, nullptr, 0);
+  __syncthreads();
+  for (int i = tid; i < nb * QP; i += FT) {
+    const int b = i >> 4, c = i & 15;
+    const size_t o = ((size_t)n * P + (size_t)g * G + b) * QP + c;
+    a.bvf[o] = c < Q ? S.v.hvf[G + b][c] : __int_as_float(S.hef[G + b]);
+    a.bvr[o] = c < Q ? S.v.hvr[G + b][c] : __int_as_float(S.her[G + b]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
 enum { SLOT_FUSED = 23 };
@@ -1164,6 +1248,36 @@ int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, co
   sh.my_flags = sh.pr.flags[rank] + half;
   rc = launch_coresident(a, sh, dim3(a.P + sh.PG + 1, NB), smem, st);
   return rc == FUSED_NOT_RESIDENT ? HMM_B200_EINVAL : rc;   // (the message says why; the 4-launch route needs no co-residency)
+}
+
+
+// boundary vectors of long tile lists in one cooperative launch; FUSED_NOT_RESIDENT: does not apply (caller takes the three
+// kernels of gene15.cu)
+int launch_boundary_groups(const Args& a, int NB, float* Gt, unsigned* gflg, cudaStream_t st) {
+  static const bool off = getenv("HMM_B200_BOUNDARY_GROUPS") && atoi(getenv("HMM_B200_BOUNDARY_GROUPS")) == 0;
+  const int PG = cdiv(a.P, G);
+  if (off || PG < 2 || PG > BG_MAX_GROUPS) return FUSED_NOT_RESIDENT;
+  const size_t smem = bg_smem_bytes(PG);
+  if (smem > (size_t)227 * 1024) return FUSED_NOT_RESIDENT;
+  int rc = ensure_dynamic_smem(boundary_groups_kernel, 27, smem);
+  if (rc) return rc;
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, boundary_groups_kernel, FT, smem) != cudaSuccess) { (void)cudaGetLastError(); return FUSED_NOT_RESIDENT; }
+  if ((long long)NB * PG > (long long)per_sm * device_sm_count()) return FUSED_NOT_RESIDENT;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(PG, NB); cfg.blockDim = dim3(FT); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeCooperative;
+  at[0].val.cooperative = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  const unsigned tag = next_tag();
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) { (void)cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+  if (cap == cudaStreamCaptureStatusActive) HMM_CUDA_OK(cudaMemsetAsync(gflg, 0, (size_t)NB * PG * sizeof(unsigned), st));   // (replays reuse the tag)
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, boundary_groups_kernel, a, Gt, gflg, tag);
+  if (e == cudaErrorCooperativeLaunchTooLarge) { (void)cudaGetLastError(); return FUSED_NOT_RESIDENT; }
+  HMM_CUDA_OK(e);
+  return 0;
 }
 
 }  // namespace gene15
