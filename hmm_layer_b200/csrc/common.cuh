@@ -75,7 +75,7 @@ inline int device_sm_count() {
 }
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the CURRENT device only: remembered per (device, slot);
 // slots are library-wide kernel ids (see SMEM_SLOT_* in the callers)
-constexpr int kSmemSlots = 32;   // gene15 0-8, dense_tc 9, seq_kernel builds 11-22, fused 23, shard kernels 24-25, viterbi 26, boundary groups 27
+constexpr int kSmemSlots = 32;   // gene15 0-8, dense_tc 9, seq_kernel builds 11-22, fused 23, shard kernels 24-25, viterbi 26, boundary groups 27, fused (shard build) 28
 template <typename K>
 inline int ensure_dynamic_smem(K kernel, int slot, size_t bytes) {
   static size_t done[kMaxDevices][kSmemSlots] = {};

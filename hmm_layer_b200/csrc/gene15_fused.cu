@@ -286,13 +286,15 @@ __device__ __forceinline__ void down_sweep(FSmem& S, const float* H, long long* 
 
 __device__ __forceinline__ void shard_reducer(const Args& a, const FShard& sh);
 
+// SHARD = false: the plain single-launch kernel (no reducer code, no halo look-ups, no shard branch in phase 4 in its image)
+template <bool SHARD>
 __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard sh) {
   extern __shared__ __align__(128) unsigned char smem[];
   FSmem& S = *reinterpret_cast<FSmem*>(smem);
   float* U = reinterpret_cast<float*>(smem + ((sizeof(FSmem) + 127) / 128) * 128);
   const int L = a.L, T = a.T, CS = L * QP + 4, P = a.P;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, hl = lane & 15, hi = lane >> 4;
-  if ((int)blockIdx.x >= P) {      // shard mode: a reducer CTA
+  if (SHARD && (int)blockIdx.x >= P) {      // shard mode: a reducer CTA
     shard_reducer(a, sh);
     return;
   }
@@ -318,7 +320,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
   // whether tile position i is a row of this sequence whose code a step of this warp needs
   auto row_of = [&](int i) { return reinterpret_cast<const float4*>(seq + (size_t)(t_lo + i) * SIN); };
   // code of a position outside this launch's rows: the neighbour shard's nucleotide (halo) or 4 outside the sequence
-  auto edge = [&](int t) { return (a.halo != nullptr && t >= -2 && t < T + 2) ? nuc_code(a, n, t) : 4; };
+  auto edge = [&](int t) { return (SHARD && a.halo != nullptr && t >= -2 && t < T + 2) ? nuc_code(a, n, t) : 4; };
   if (wact) {
     {
       const float4* row = row_of(min(wb + lane, npos - 1));
@@ -657,7 +659,7 @@ __global__ void __launch_bounds__(FT, 2) fused_kernel(const Args a, const FShard
     if (a.dbg) a.dbg[(size_t)cta * 16 + 10] = gtimer();
   }
   const bool add_ll = (a.flags & HMM_B200_NO_LOGLIK) != 0;
-  const bool sharded = sh.world > 0;
+  const bool sharded = SHARD && sh.world > 0;
   if (sharded) {
     // shard mode: the group's reducer CTA publishes this tile's boundary vectors (cross-rank, cross-group, in-group folds)
     if (warp == 1) {
@@ -1151,7 +1153,7 @@ __global__ void __launch_bounds__(FT) boundary_groups_kernel(const Args a, float
 // ------------------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------------------
-enum { SLOT_FUSED = 23 };
+enum { SLOT_FUSED = 23, SLOT_FUSED_SHARD = 28 };
 
 // CTAs of the fused kernel that can be resident at once on the current device for chunk length L (0: does not fit)
 int fused_capacity(int L) {
@@ -1164,9 +1166,10 @@ int fused_capacity(int L) {
   }
   const size_t smem = fused_smem_bytes(L);
   int cap = -1;
-  if (smem <= (size_t)227 * 1024 && ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem) == 0) {
+  if (smem <= (size_t)227 * 1024 && ensure_dynamic_smem(fused_kernel<false>, SLOT_FUSED, smem) == 0 &&
+      ensure_dynamic_smem(fused_kernel<true>, SLOT_FUSED_SHARD, smem) == 0) {
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_kernel, FT, smem) == cudaSuccess && per_sm > 0)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fused_kernel<true>, FT, smem) == cudaSuccess && per_sm > 0)
       cap = per_sm * device_sm_count();
     else
       (void)cudaGetLastError();
@@ -1197,7 +1200,7 @@ static int launch_coresident(const Args& a, const FShard& sh, dim3 grid, size_t 
   at[0].val.cooperative = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   const char* refuse = getenv("HMM_B200_TEST_REFUSE_COOP");   // test hook: behave as if the device had refused the grid
-  const cudaError_t e = (refuse && refuse[0] == '1') ? cudaErrorCooperativeLaunchTooLarge : cudaLaunchKernelEx(&cfg, fused_kernel, a, sh);
+  const cudaError_t e = (refuse && refuse[0] == '1') ? cudaErrorCooperativeLaunchTooLarge : (sh.world > 0 ? cudaLaunchKernelEx(&cfg, fused_kernel<true>, a, sh) : cudaLaunchKernelEx(&cfg, fused_kernel<false>, a, sh));
   if (e == cudaErrorCooperativeLaunchTooLarge) {
     // fewer CTAs fit than the occupancy query promised (a reduced SM share under MPS, a smaller shared-memory carve-out):
     // the caller takes the path that needs no co-residency
@@ -1212,7 +1215,7 @@ static int launch_coresident(const Args& a, const FShard& sh, dim3 grid, size_t 
 
 int launch_fused(Args a, int NB, cudaStream_t st) {
   const size_t smem = fused_smem_bytes(a.L);
-  int rc = ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem);
+  int rc = ensure_dynamic_smem(fused_kernel<false>, SLOT_FUSED, smem);
   if (rc) return rc;
   a.run = fused_run_len(a.L);
   a.tag = next_tag();
@@ -1230,7 +1233,7 @@ int launch_fused(Args a, int NB, cudaStream_t st) {
 int launch_fused_shard(Args a, int NB, const unsigned long long* peer_blocks, const unsigned long long* peer_flags, int rank, int world,
                        unsigned tag, float* Gt, unsigned* gflg, unsigned* bvflg, cudaStream_t st) {
   const size_t smem = fused_smem_bytes(a.L);
-  int rc = ensure_dynamic_smem(fused_kernel, SLOT_FUSED, smem);
+  int rc = ensure_dynamic_smem(fused_kernel<true>, SLOT_FUSED_SHARD, smem);
   if (rc) return rc;
   a.run = fused_run_len(a.L);
   a.tag = next_tag();   // local flags (tiles, groups, boundary vectors): unique per launch whatever the workspace held before
