@@ -382,6 +382,43 @@ def run_config4(args, rank, world, local):
         dist.destroy_process_group()
 
 
+def secondary_config4(rank, world, dev, barrier):
+    """BASELINE config 4 beside the headline (the full line: --config 4): learnMSA-size dense HMM, 8 heads x q = 1003,
+    batch 512 x len 600 per GPU, one-hot inputs gathered inside the tcgen05 step kernel: forward log-likelihood and forward +
+    backward + posterior, device-resident, a few steps each."""
+    import torch.distributed as dist
+    import hmm_layer_b200 as H
+    from hmm_layer_b200 import ops, synthetic as syn
+    k, L, B, T = 8, 500, 512, 600
+    q = 2 * L + 3
+    A, pi, Bm = syn.profile_model(k, L)
+    cell = H.MsaHmmCell([L] * k, dim=24, emitter=H.DenseEmitter(Bm), transitioner=H.DenseTransitioner(A, pi)).to(dev)
+    cell.onehot_inputs = True
+    cell.recurrent_init()
+    sym = syn.profile_inputs(k, B, T, seed=2100 + rank).argmax(-1).to(torch.uint8).to(dev)
+    Bt = cell.emitter[0].onehot_table().contiguous()
+    Ad, pid = A.to(dev), pi.to(dev)
+    out = {}
+    for name, kw, n in (("forward_loglik", {}, 5), ("forward_backward_posterior", {"want_post": True}, 2)):
+        for _ in range(2):
+            ops.dense_run_onehot(sym, Bt, Ad, pid, **kw)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record()
+        for _ in range(n):
+            ops.dense_run_onehot(sym, Bt, Ad, pid, **kw)
+        e1.record(); barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / n], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name] = float(t.item())
+    cells = syn.cells(k, B, T, q)
+    peak, src = tensor_peak()
+    return {"workload": "learnMSA multi-head dense HMM, 8 heads x model length 500 (q=1003), batch 512 x len 600 per GPU, one-hot inputs",
+            "ms_forward_loglik": out["forward_loglik"], "ms_forward_backward_posterior": out["forward_backward_posterior"],
+            "cells_per_s": world * cells / (out["forward_loglik"] * 1e-3),
+            "frac_of_bf16_peak": 2.0 * cells / (out["forward_loglik"] * 1e-3) / 1e12 / peak, "peak_source": src}
+
+
 def measure_c5(T, rank, world, dev, params, steps=50, warm=5, nbuf=None, one_launch=True):
     """Device-resident forward+posterior of ONE sequence of T positions cut into `world` contiguous shards (one per rank;
     world == 1: the chunked scan on one GPU).  Returns (ms per step: max over ranks, log-likelihood, launches per step,
@@ -725,6 +762,11 @@ def main():
             del x3, o3
         except Exception as e:
             secondary["config3"] = {"error": f"{type(e).__name__}: {e}"}
+        try:
+            secondary["config4"] = secondary_config4(rank, world, dev, barrier)
+        except Exception as e:
+            secondary["config4"] = {"error": f"{type(e).__name__}: {e}"}
+        torch.cuda.empty_cache()
 
     t = torch.tensor([ms_e2e], dtype=torch.float64, device=dev)
     if world > 1:
