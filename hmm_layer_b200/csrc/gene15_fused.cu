@@ -15,16 +15,20 @@
 //                   the scalar operand): 15 FFMA2 per position for two rows.
 //   3 tree          the 5-level product tree of gene15.cu (mma.sync TF32 x 3), kept in shared memory.
 //   4 exchange      the tile matrix goes to the workspace with a per-call tag; one warp polls the tags of the sequence's
-//                   tiles (ld.acquire), scans the tile matrices (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49)
-//                   and the tree is swept down to the chunk boundary vectors.
+//                   tiles (ld.acquire), the sequence's tile matrices are staged in shared memory and scanned by two warps,
+//                   forward and backward (the role of TotalProbabilityCell, TotalProbabilityCell.py:30-49), and the tree is
+//                   swept down to the chunk boundary vectors.
 //   5 recursion     the exact recursions of MsaHmmCell.py:73-106 inside every chunk, both directions meeting in the middle
-//                   (gene15.cu, K2); emission rows arrive through a 4-deep cp.async ring per thread, so that only the
-//                   own rows / posterior products (Y) need shared memory: 103 KB per CTA instead of 153.
+//                   (gene15.cu, K2); emission rows arrive through a 6-deep cp.async ring per thread, so that only the
+//                   own rows / posterior products (Y) need shared memory: 110 KB per CTA instead of 153.
 //   6 output        log posterior through a per-warp staging buffer, coalesced.
 //
 // Against the two-kernel path: no product tree / emission rows re-read through bulk copies, no second launch, no second
 // wave (finalize_kernel fits one CTA per SM), half the FMA issue slots in phases 1 and 2.
 // The same arithmetic as gene15.cu in the same order (floors, scales as exact powers of two): see the comments there.
+// The launches are cooperative (launch_coresident): the in-kernel waits need the whole grid resident.
+// Also in this file: the shard mode of the kernel (reducer CTAs: one launch per sequence-sharded step, template SHARD) and
+// boundary_groups_kernel (boundary vectors of long tile lists behind products_kernel in one launch).
 #include <atomic>
 #include <chrono>
 #include "gene15_dev.cuh"
