@@ -32,3 +32,21 @@ def test_abi_version_and_workspace_query_need_no_gpu():
     assert lib.hmm_b200_set_tuning(32, 100, 0) != 0    # finalize threads must be a multiple of 32
     assert lib.hmm_b200_set_tuning(32, 256, 0) == 0
     assert lib.hmm_b200_set_tuning(0, 0, 0) == 0
+
+
+def test_no_alloc_test_file_is_collected_last():
+    """tests/test_zz_no_alloc.py must stay the last file pytest collects (a failure there must
+    not hide other tests); pytest collects a directory's files in name order."""
+    import glob
+    import os
+    files = sorted(os.path.basename(f) for f in glob.glob(os.path.join(os.path.dirname(__file__), "test_*.py")))
+    assert files[-1] == "test_zz_no_alloc.py", files[-3:]
+
+
+def test_header_states_the_static_scratch_limit():
+    import os
+    import re
+    h = open(os.path.join(os.path.dirname(__file__), "..", "include", "hmm_b200.h")).read()
+    m = re.search(r"#define\s+HMM_B200_NOALLOC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", h)
+    assert m and (int(m.group(1)) << int(m.group(2))) == 64 << 20
+    assert "no counterpart in the reference" in h.lower()
